@@ -1,0 +1,1235 @@
+// chb_api.cu -- libchoreo_b200.so: plan construction, kernel launchers and the C ABI of include/choreo_b200.h.
+//
+// Built by nvcc for sm_100a (product).  The same translation unit also compiles with
+//   g++ -x c++ -DCHB_HOSTSIM
+// into tests/hostsim/libchb_hostsim.so, where "device memory" is malloc and every kernel launch is a loop over
+// blocks running the CTA programs of chb_core.cuh sequentially.  That build is test infrastructure for the
+// GPU-less build container (index arithmetic / host logic); the product loader never loads it.
+#include "../../include/choreo_b200.h"
+#include "chb_core.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#ifndef CHB_HOSTSIM
+#include <cuda_runtime.h>
+#include "chb_fused.cuh"
+#endif
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+static int chb_fail(int code, const std::string &msg) {
+    g_last_error = msg;
+    return code;
+}
+#define CHB_REQUIRE(cond, code, msg)          \
+    do {                                      \
+        if (!(cond)) return chb_fail(code, msg); \
+    } while (0)
+
+#ifndef CHB_HOSTSIM
+#define CHB_CUDA(call)                                                                              \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess)                                                                      \
+            return chb_fail(CHB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));      \
+    } while (0)
+typedef cudaStream_t chb_stream_t;
+#else
+typedef void *chb_stream_t;
+#endif
+
+// ------------------------------------------------------------------------------------------------
+// plan
+// ------------------------------------------------------------------------------------------------
+struct HostTables {
+    int G = 0, nbody = 0, nloop = 0, nsegm = 0, nbin = 0, nint_min = 0, gns = 0, law = 0;
+    double law_params[4] = {0, 0, 0, 0};
+    std::vector<int64_t> loopnb, ncm, nsub, nnz, nppl, nnz_k, nnz_k_shifts, co_in_shifts, basis_shifts, alg_iint,
+        alg_timerev, bodyloop, seg_body, seg_iintrel, seg_timerev, bin_src, bin_tgt;
+    std::vector<int32_t> shortcut, co_in, seg_isid, bin_isid;
+    std::vector<double> loopmass, basis, alg_rot, seg_rot, bin_rot, bin_fac;
+};
+
+struct chb_plan {
+    int device = 0;
+    HostTables T;
+    int64_t nint = 0;
+    bool ready = false;
+    std::vector<void *> level_allocs;  // device allocations owned by the current nint level
+    std::vector<ChbLoop> h_loops;      // host mirror (device pointers inside)
+    ChbSys sys;                        // passed by value to kernels
+    int64_t chunk_user = 0;
+    int fused_enabled = 1;
+    int fused_active = 0;
+    int64_t launches = 0;
+    size_t smem_limit = 0;  // max dynamic shared memory per block (opt-in)
+    int num_sms = 0;
+    // per-op launch geometry
+    int fft_threads = 256;
+    size_t fft_smem = 0;  // dynamic smem of the transform kernels
+    std::vector<int> loop_in_smem;
+    int pair_threads = 256;
+    size_t pair_smem[3] = {0, 0, 0};
+    // staging for chb_run_host
+    std::mutex host_mutex;
+    void *stage_dev = nullptr;
+    size_t stage_dev_bytes = 0;
+    void *stage_pin = nullptr;
+    size_t stage_pin_bytes = 0;
+#ifndef CHB_HOSTSIM
+    ChbFusedPlan fused;
+#endif
+};
+
+// ---- memory shims --------------------------------------------------------------------------------
+static int dev_alloc(chb_plan *p, size_t bytes, void **out) {
+    if (bytes == 0) bytes = 16;
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaSetDevice(p->device));
+    CHB_CUDA(cudaMalloc(out, bytes));
+#else
+    (void)p;
+    *out = malloc(bytes);
+    CHB_REQUIRE(*out, CHB_ERR_CUDA, "malloc failed");
+#endif
+    return CHB_OK;
+}
+static void dev_free(void *ptr) {
+#ifndef CHB_HOSTSIM
+    cudaFree(ptr);
+#else
+    free(ptr);
+#endif
+}
+static int dev_upload(void *dst, const void *src, size_t bytes) {
+    if (bytes == 0) return CHB_OK;
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+#else
+    memcpy(dst, src, bytes);
+#endif
+    return CHB_OK;
+}
+template <class T>
+static int level_upload(chb_plan *p, const std::vector<T> &v, const T **out) {
+    void *d = nullptr;
+    int rc = dev_alloc(p, v.size() * sizeof(T), &d);
+    if (rc) return rc;
+    p->level_allocs.push_back(d);
+    rc = dev_upload(d, v.data(), v.size() * sizeof(T));
+    if (rc) return rc;
+    *out = (const T *)d;
+    return CHB_OK;
+}
+static void free_level(chb_plan *p) {
+    for (void *q : p->level_allocs) dev_free(q);
+    p->level_allocs.clear();
+    p->h_loops.clear();
+    p->ready = false;
+}
+
+// ------------------------------------------------------------------------------------------------
+// C ABI: misc
+// ------------------------------------------------------------------------------------------------
+extern "C" int chb_abi_version(void) { return CHB_ABI_VERSION; }
+extern "C" const char *chb_last_error_string(void) { return g_last_error.c_str(); }
+
+extern "C" int chb_device_count(void) {
+#ifndef CHB_HOSTSIM
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    int ok = 0;
+    for (int i = 0; i < n; ++i) {
+        cudaDeviceProp pr;
+        if (cudaGetDeviceProperties(&pr, i) == cudaSuccess && pr.major == 10) ++ok;
+    }
+    return ok;
+#else
+    return 1;
+#endif
+}
+
+template <class T>
+static void copy_in(std::vector<T> &dst, const T *src, size_t n) {
+    dst.assign(src, src + n);
+}
+
+extern "C" int chb_plan_create(const chb_tables *t, int device, chb_plan **out) {
+    CHB_REQUIRE(t && out, CHB_ERR_INVALID_ARGUMENT, "chb_plan_create: NULL argument");
+    CHB_REQUIRE(t->geodim >= 1 && t->geodim <= CHB_MAX_G, CHB_ERR_UNSUPPORTED,
+                "chb_plan_create: geodim must be in [1,4]");
+    CHB_REQUIRE(t->nloop >= 1 && t->nsegm >= 1 && t->nbin >= 0 && t->nint_min >= 1 && t->nbody >= 1,
+                CHB_ERR_INVALID_ARGUMENT, "chb_plan_create: bad sizes");
+    CHB_REQUIRE(t->inter_law == CHB_LAW_GRAVITY || t->inter_law == CHB_LAW_POWER, CHB_ERR_UNSUPPORTED,
+                "chb_plan_create: only gravity_pot and power_law_pot are supported on the device");
+#ifndef CHB_HOSTSIM
+    {
+        int n = 0;
+        cudaError_t e = cudaGetDeviceCount(&n);
+        if (e != cudaSuccess || n == 0) {
+            cudaGetLastError();
+            return chb_fail(CHB_ERR_NO_DEVICE, "chb_plan_create: no CUDA device visible (there is no CPU fallback)");
+        }
+        CHB_REQUIRE(device >= 0 && device < n, CHB_ERR_INVALID_ARGUMENT, "chb_plan_create: bad device index");
+        cudaDeviceProp pr;
+        CHB_CUDA(cudaGetDeviceProperties(&pr, device));
+        CHB_REQUIRE(pr.major == 10, CHB_ERR_NO_DEVICE,
+                    "chb_plan_create: device is not compute capability 10.x (library is built for sm_100a only)");
+    }
+#endif
+    chb_plan *p = new chb_plan();
+    p->device = device;
+    HostTables &T = p->T;
+    T.G = t->geodim;
+    T.nbody = t->nbody;
+    T.nloop = t->nloop;
+    T.nsegm = t->nsegm;
+    T.nbin = t->nbin;
+    T.nint_min = t->nint_min;
+    T.gns = t->greater_nstore ? 1 : 0;
+    T.law = t->inter_law;
+    for (int i = 0; i < 4; ++i) T.law_params[i] = t->inter_law_params[i];
+    const int nl = T.nloop, G = T.G;
+    copy_in(T.loopnb, t->loopnb, nl);
+    copy_in(T.loopmass, t->loopmass, nl);
+    copy_in(T.ncm, t->ncoeff_min, nl);
+    copy_in(T.nsub, t->n_sub_fft, nl);
+    copy_in(T.shortcut, t->shortcut, nl);
+    copy_in(T.nnz, t->nnz, nl);
+    copy_in(T.nppl, t->nppl, nl);
+    copy_in(T.nnz_k_shifts, t->nnz_k_shifts, nl + 1);
+    copy_in(T.co_in_shifts, t->co_in_shifts, nl + 1);
+    copy_in(T.basis_shifts, t->params_basis_shifts, nl + 1);
+    copy_in(T.nnz_k, t->nnz_k, (size_t)T.nnz_k_shifts[nl]);
+    copy_in(T.co_in, t->co_in, (size_t)T.co_in_shifts[nl]);
+    copy_in(T.basis, t->params_basis, (size_t)(2 * T.basis_shifts[nl]));
+    copy_in(T.alg_iint, t->alg_iint, nl);
+    copy_in(T.alg_timerev, t->alg_timerev, nl);
+    copy_in(T.alg_rot, t->alg_spacerot, (size_t)nl * G * G);
+    copy_in(T.bodyloop, t->bodyloop, T.nbody);
+    copy_in(T.seg_body, t->gensegm_to_body, T.nsegm);
+    copy_in(T.seg_iintrel, t->gensegm_to_iintrel, T.nsegm);
+    copy_in(T.seg_timerev, t->inter_timerev, T.nsegm);
+    copy_in(T.seg_rot, t->inter_spacerot, (size_t)T.nsegm * G * G);
+    copy_in(T.seg_isid, t->inter_spacerot_isid, T.nsegm);
+    copy_in(T.bin_src, t->bin_source, T.nbin);
+    copy_in(T.bin_tgt, t->bin_target, T.nbin);
+    copy_in(T.bin_rot, t->bin_spacerot, (size_t)T.nbin * G * G);
+    copy_in(T.bin_isid, t->bin_spacerot_isid, T.nbin);
+    copy_in(T.bin_fac, t->bin_prodchargesum, T.nbin);
+    // consistency checks (the reference would hit undefined behaviour instead, asserts compiled out: setup.py:237-239)
+    std::string err;
+    for (int il = 0; il < nl && err.empty(); ++il) {
+        int64_t nnz = T.nnz[il], nppl = T.nppl[il];
+        if (nnz < 0 || nppl < 0 || nnz > CHB_MAX_NNZ || nppl > CHB_MAX_NPPL || nnz * nppl > CHB_MAX_C)
+            err = "loop with nnz*nppl beyond compiled limits";
+        else if (T.nnz_k_shifts[il + 1] - T.nnz_k_shifts[il] != nnz)
+            err = "nnz_k_shifts inconsistent with nnz";
+        else if (T.basis_shifts[il + 1] - T.basis_shifts[il] != (int64_t)G * nnz * nppl)
+            err = "params_basis_shifts inconsistent";
+        else if (T.nsub[il] != 1 && T.nsub[il] != 2)
+            err = "Impossible value for n_sub_fft (allowed: 1 or 2)";
+        else if (T.ncm[il] < 1 || T.loopnb[il] < 1 || !(T.loopmass[il] != 0.0))
+            err = "bad ncoeff_min / loopnb / loopmass";
+        else if (T.shortcut[il] == CHB_RFFT) {
+            bool ok = nnz == 1 && nppl == 2 * G && T.nnz_k[T.nnz_k_shifts[il]] == 0 && T.nsub[il] == 1;
+            if (!ok) err = "RFFT shortcut requires nnz=1, nnz_k=[0], nppl=2*geodim, n_sub_fft=1";
+        } else if (T.shortcut[il] != CHB_GENERAL_SYM)
+            err = "unknown shortcut";
+        if (err.empty() && nnz > 0 && T.nnz_k[T.nnz_k_shifts[il]] == 0) {
+            if (T.co_in_shifts[il + 1] - T.co_in_shifts[il] != nppl) err = "co_in must have nppl entries when nnz_k[0]==0";
+        }
+    }
+    for (int s = 0; s < T.nsegm && err.empty(); ++s) {
+        if (T.seg_body[s] < 0 || T.seg_body[s] >= T.nbody) err = "gensegm_to_body out of range";
+        else if (T.bodyloop[T.seg_body[s]] < 0 || T.bodyloop[T.seg_body[s]] >= nl) err = "bodyloop out of range";
+        else if (T.seg_timerev[s] != 1 && T.seg_timerev[s] != -1) err = "InterTimeRev must be +-1";
+        else if (T.seg_iintrel[s] < 0) err = "gensegm_to_iintrel negative";
+    }
+    for (int b = 0; b < T.nbin && err.empty(); ++b) {
+        if (T.bin_src[b] < 0 || T.bin_src[b] >= T.nsegm || T.bin_tgt[b] < 0 || T.bin_tgt[b] >= T.nsegm)
+            err = "BinSourceSegm/BinTargetSegm out of range";
+    }
+    if (!err.empty()) {
+        delete p;
+        return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_plan_create: " + err);
+    }
+#ifndef CHB_HOSTSIM
+    {
+        cudaDeviceProp pr;
+        cudaGetDeviceProperties(&pr, device);
+        p->smem_limit = pr.sharedMemPerBlockOptin;
+        p->num_sms = pr.multiProcessorCount;
+    }
+#else
+    p->smem_limit = 227 * 1024;
+    p->num_sms = 148;
+#endif
+    memset(&p->sys, 0, sizeof(p->sys));
+    *out = p;
+    return CHB_OK;
+}
+
+extern "C" int chb_plan_destroy(chb_plan *p) {
+    if (!p) return CHB_OK;
+    free_level(p);
+    if (p->stage_dev) dev_free(p->stage_dev);
+#ifndef CHB_HOSTSIM
+    if (p->stage_pin) cudaFreeHost(p->stage_pin);
+#else
+    if (p->stage_pin) free(p->stage_pin);
+#endif
+    delete p;
+    return CHB_OK;
+}
+
+// ---- FFT planning -----------------------------------------------------------------------------------
+static bool factorize(int M, std::vector<int> &fac) {
+    fac.clear();
+    int m = M;
+    while (m % 4 == 0) { fac.push_back(4); m /= 4; }
+    while (m % 2 == 0) { fac.push_back(2); m /= 2; }
+    for (int p = 3; p <= CHB_MAX_PRIME && m > 1; p += 2)
+        while (m % p == 0) { fac.push_back(p); m /= p; }
+    if (m != 1) return false;
+    if ((int)fac.size() > CHB_MAX_FAC) return false;
+    return true;
+}
+
+static void exact_root(long long num, long long den, double *c, double *s) {
+    // exp(-2 pi i num/den): exact integer octant reduction, then long double cos/sin on [0, pi/4]
+    num %= den;
+    if (num < 0) num += den;
+    const long double tau = 6.283185307179586476925286766559005768L;
+    const long long a = 8 * num;  // theta = 2 pi a / (8 den)
+    const int oct = (int)(a / den);
+    long long phi;
+    switch (oct) {
+        default:
+        case 0: phi = a; break;
+        case 1: phi = 2 * den - a; break;
+        case 2: phi = a - 2 * den; break;
+        case 3: phi = 4 * den - a; break;
+        case 4: phi = a - 4 * den; break;
+        case 5: phi = 6 * den - a; break;
+        case 6: phi = a - 6 * den; break;
+        case 7: phi = 8 * den - a; break;
+    }
+    const long double ang = tau * (long double)phi / (long double)(8 * den);
+    const long double cp = cosl(ang), sp = sinl(ang);
+    long double cr, sr;
+    switch (oct) {
+        default:
+        case 0: cr = cp; sr = sp; break;
+        case 1: cr = sp; sr = cp; break;
+        case 2: cr = -sp; sr = cp; break;
+        case 3: cr = -cp; sr = sp; break;
+        case 4: cr = -cp; sr = -sp; break;
+        case 5: cr = -sp; sr = -cp; break;
+        case 6: cr = sp; sr = -cp; break;
+        case 7: cr = cp; sr = -sp; break;
+    }
+    *c = (double)cr;
+    *s = (double)(-sr);  // exp(-i theta)
+}
+
+struct FftCache {
+    const cd *roots;
+    const int *rev;
+    std::vector<int> fac;
+};
+
+extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_nint: NULL plan");
+    HostTables &T = p->T;
+    if (nint <= 0 || nint % (2 * (int64_t)T.nint_min) != 0)
+        return chb_fail(CHB_ERR_INVALID_NINT, "Provided nint " + std::to_string(nint) + " should be divisible by " +
+                                                  std::to_string(2 * T.nint_min));
+    CHB_REQUIRE(nint < (1LL << 30), CHB_ERR_UNSUPPORTED, "chb_plan_set_nint: nint too large");
+    for (int il = 0; il < T.nloop; ++il)
+        CHB_REQUIRE(nint % (2 * T.ncm[il]) == 0, CHB_ERR_INVALID_NINT, "nint not divisible by 2*ncoeff_min_loop");
+    free_level(p);
+    const int G = T.G, nl = T.nloop;
+    const int segm_size = (int)(nint / T.nint_min);
+    const int segm_store = segm_size + (T.gns ? 1 : 0);
+
+    std::map<int, FftCache> fft_cache;
+    std::vector<ChbLoop> loops(nl);
+    long long mom_off = 0, scratch_off = 0;
+    std::vector<int> seg_loop(T.nsegm);
+    for (int s = 0; s < T.nsegm; ++s) seg_loop[s] = (int)T.bodyloop[T.seg_body[s]];
+
+    for (int il = 0; il < nl; ++il) {
+        ChbLoop &L = loops[il];
+        memset(&L, 0, sizeof(L));
+        L.shortcut = T.shortcut[il];
+        L.n_sub_fft = (int)T.nsub[il];
+        L.nnz = (int)T.nnz[il];
+        L.nppl = (int)T.nppl[il];
+        L.C = L.nnz * L.nppl;
+        L.ncm = (int)T.ncm[il];
+        L.npr = (int)(nint / (2 * T.ncm[il]));
+        L.ncomp = (L.n_sub_fft == 2) ? L.npr + 1 : 2 * L.npr;
+        L.ninter = L.ncomp + ((L.n_sub_fft == 1 && T.gns) ? 1 : 0);
+        L.has_k0 = (L.nnz > 0 && T.nnz_k[T.nnz_k_shifts[il]] == 0) ? 1 : 0;
+        L.nseq = (L.shortcut == CHB_RFFT) ? G : L.C;
+        L.stride = L.npr + 1;
+        L.mom_off = mom_off;
+        L.loopmul = 1.0 / sqrt((double)T.loopnb[il] * T.loopmass[il] * 4.0 * M_PI * M_PI);
+        int ncor = 0;
+        for (int j = 0; j < L.nppl; ++j) {
+            int keep = 1;
+            if (L.has_k0) keep = T.co_in[T.co_in_shifts[il] + j] ? 1 : 0;
+            L.co_in[j] = keep;
+            L.co_prefix[j] = ncor;
+            ncor += keep;
+        }
+        L.nco_in = L.has_k0 ? (L.nppl - ncor) : 0;
+        mom_off += (long long)L.npr * L.C - L.nco_in;
+        for (int ik = 0; ik < L.nnz; ++ik) {
+            L.nnz_k[ik] = (int)T.nnz_k[T.nnz_k_shifts[il] + ik];
+            double c, s;
+            exact_root(L.nnz_k[ik], L.ncm, &c, &s);
+            L.wmir[ik] = mk(c, -s);  // exp(+2 pi i nnz_k/ncm)
+        }
+        const double *bas = T.basis.data() + 2 * T.basis_shifts[il];
+        for (int g = 0; g < G; ++g)
+            for (int c = 0; c < L.C; ++c) {
+                L.bre[g][c] = bas[2 * ((long long)g * L.C + c)];
+                L.bim[g][c] = bas[2 * ((long long)g * L.C + c) + 1];
+            }
+        L.has_alg = (segm_size != segm_store && L.nnz > 0 && L.n_sub_fft == 1) ? 1 : 0;
+        L.alg_src = T.alg_timerev[il] == 1 ? (int)(T.alg_iint[il] * segm_size)
+                                            : (int)((T.alg_iint[il] + 1) * segm_size - 1);
+        if (L.has_alg && (L.alg_src < 0 || L.alg_src >= L.ncomp)) {
+            free_level(p);
+            return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_nint: ALG source row out of range");
+        }
+        for (int i = 0; i < G * G; ++i) L.alg_rot[i] = T.alg_rot[(size_t)il * G * G + i];
+        L.scratch_off = scratch_off;
+        L.smem_cd = (long long)L.nseq * L.stride;
+        scratch_off += L.smem_cd;
+
+        if (L.nnz > 0) {
+            const int M = L.npr;
+            auto it = fft_cache.find(M);
+            if (it == fft_cache.end()) {
+                FftCache fc;
+                if (!factorize(M, fc.fac)) {
+                    free_level(p);
+                    return chb_fail(CHB_ERR_UNSUPPORTED, "chb_plan_set_nint: FFT length " + std::to_string(2 * M) +
+                                                             " has a prime factor > " + std::to_string(CHB_MAX_PRIME));
+                }
+                const int N = 2 * M;
+                std::vector<cd> roots(N);
+                for (int j = 0; j < N; ++j) {
+                    double c, s;
+                    exact_root(j, N, &c, &s);
+                    roots[j] = mk(c, s);
+                }
+                std::vector<int> rev(M);
+                for (int k = 0; k < M; ++k) {
+                    int kk = k, pos = 0, Lcur = M;
+                    for (int r : fc.fac) {
+                        int t = kk % r;
+                        kk /= r;
+                        Lcur /= r;
+                        pos += t * Lcur;
+                    }
+                    rev[k] = pos;
+                }
+                int rc = level_upload(p, roots, &fc.roots);
+                if (!rc) rc = level_upload(p, rev, &fc.rev);
+                if (rc) { free_level(p); return rc; }
+                it = fft_cache.insert(std::make_pair(M, fc)).first;
+            }
+            L.fft.M = M;
+            L.fft.N = 2 * M;
+            L.fft.nfac = (int)it->second.fac.size();
+            for (int i = 0; i < L.fft.nfac; ++i) L.fft.fac[i] = it->second.fac[i];
+            L.fft.roots = it->second.roots;
+            L.fft.rev = it->second.rev;
+            if (L.shortcut == CHB_GENERAL_SYM) {
+                std::vector<cd> tw((size_t)(L.npr + 1) * L.nnz);
+                for (int m = 0; m <= L.npr; ++m)
+                    for (int ik = 0; ik < L.nnz; ++ik) {
+                        double c, s;
+                        exact_root((long long)m * L.nnz_k[ik], nint, &c, &s);
+                        tw[(size_t)m * L.nnz + ik] = mk(c, s);
+                    }
+                int rc = level_upload(p, tw, &L.gen_tw);
+                if (rc) { free_level(p); return rc; }
+            }
+        }
+        // segments of this loop + CSR over slice slots
+        std::vector<int> segs;
+        int max_slot = -1;
+        for (int s = 0; s < T.nsegm; ++s)
+            if (seg_loop[s] == il) {
+                segs.push_back(s);
+                max_slot = std::max(max_slot, (int)T.seg_iintrel[s]);
+                long long last_row = T.seg_iintrel[s] * (long long)segm_size + segm_store - 1;
+                if (last_row >= L.ninter) {
+                    free_level(p);
+                    return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_nint: segment reads past its loop slice");
+                }
+            }
+        L.seg_count = (int)segs.size();
+        L.n_iint = max_slot + 1;
+        std::vector<int> off(L.n_iint + 1, 0), lst;
+        for (int q = 0; q < L.n_iint; ++q) {
+            for (int s : segs)
+                if (T.seg_iintrel[s] == q) lst.push_back(s);
+            off[q + 1] = (int)lst.size();
+        }
+        int rc = level_upload(p, segs, &L.segs);
+        if (!rc) rc = level_upload(p, off, &L.iint_off);
+        if (!rc) rc = level_upload(p, lst, &L.iint_seg);
+        if (rc) { free_level(p); return rc; }
+    }
+
+    // segments / bins
+    std::vector<ChbSeg> segs(T.nsegm);
+    for (int s = 0; s < T.nsegm; ++s) {
+        memset(&segs[s], 0, sizeof(ChbSeg));
+        segs[s].loop = seg_loop[s];
+        segs[s].iintrel = (int)T.seg_iintrel[s];
+        segs[s].timerev = (int)T.seg_timerev[s];
+        segs[s].isid = T.seg_isid[s] ? 1 : 0;
+        for (int i = 0; i < G * G; ++i) segs[s].rot[i] = T.seg_rot[(size_t)s * G * G + i];
+    }
+    // greedy edge colouring of the interaction multigraph: a round never touches a segment twice
+    std::vector<int> colour(T.nbin, -1);
+    int nround = 0;
+    {
+        std::vector<std::vector<char>> used;  // used[round][segment]
+        for (int b = 0; b < T.nbin; ++b) {
+            int s = (int)T.bin_src[b], t = (int)T.bin_tgt[b];
+            int r = 0;
+            for (;; ++r) {
+                if (r == (int)used.size()) used.push_back(std::vector<char>(T.nsegm, 0));
+                if (!used[r][s] && !used[r][t]) break;
+            }
+            used[r][s] = used[r][t] = 1;
+            colour[b] = r;
+        }
+        nround = (int)used.size();
+    }
+    std::vector<ChbBin> bins;
+    std::vector<int> round_off(nround + 1, 0);
+    int max_round_bins = 1;
+    for (int r = 0; r < nround; ++r) {
+        for (int b = 0; b < T.nbin; ++b)
+            if (colour[b] == r) {
+                ChbBin B;
+                memset(&B, 0, sizeof(B));
+                B.src = (int)T.bin_src[b];
+                B.tgt = (int)T.bin_tgt[b];
+                B.isid = T.bin_isid[b] ? 1 : 0;
+                B.fac = T.bin_fac[b];
+                for (int i = 0; i < G * G; ++i) B.rot[i] = T.bin_rot[(size_t)b * G * G + i];
+                bins.push_back(B);
+            }
+        round_off[r + 1] = (int)bins.size();
+        max_round_bins = std::max(max_round_bins, round_off[r + 1] - round_off[r]);
+    }
+
+    ChbSys &S = p->sys;
+    memset(&S, 0, sizeof(S));
+    S.G = G;
+    S.nloop = nl;
+    S.nsegm = T.nsegm;
+    S.nbin = T.nbin;
+    S.segm_size = segm_size;
+    S.segm_store = segm_store;
+    S.nparams = mom_off;
+    S.segsz = (long long)T.nsegm * segm_store * G;
+    S.law_kind = T.law;
+    for (int i = 0; i < 4; ++i) S.law[i] = T.law_params[i];
+    S.nround = nround;
+    S.scratch_per_state = scratch_off;
+    int rc = level_upload(p, loops, &S.loops);
+    if (!rc) rc = level_upload(p, segs, &S.segs);
+    if (!rc) rc = level_upload(p, bins, &S.bins);
+    if (!rc) rc = level_upload(p, round_off, &S.round_off);
+    if (rc) { free_level(p); return rc; }
+    p->h_loops = loops;
+
+    // ---- launch geometry ----
+    // transform kernels: FFT buffer in shared memory when it fits, else in the per-state global scratch
+    p->fft_threads = 256;
+    const size_t red_bytes = sizeof(double) * 1024;
+    size_t budget = p->smem_limit > red_bytes + 1024 ? p->smem_limit - red_bytes - 1024 : 0;
+    p->loop_in_smem.assign(nl, 0);
+    size_t need = 0;
+    long long maxM = 1;
+    for (int il = 0; il < nl; ++il) {
+        size_t b = (size_t)loops[il].smem_cd * sizeof(cd);
+        if (b <= budget) {
+            p->loop_in_smem[il] = 1;
+            need = std::max(need, b);
+        }
+        maxM = std::max<long long>(maxM, (long long)loops[il].nseq * loops[il].npr);
+    }
+    if (maxM >= 4096) p->fft_threads = 512;
+    if (maxM >= 16384) p->fft_threads = 1024;
+    p->fft_smem = red_bytes + need;
+    // pair kernel tile: shared arrays spos (+sdpos) + sout, thread item = (bin in round, sample)
+    {
+        size_t per_sample = (size_t)T.nsegm * G * sizeof(double);
+        size_t target = 64 * 1024;  // for 3 arrays
+        int tile = 256;
+        while (tile > 1 && per_sample * tile * 3 > target) tile >>= 1;
+        while (tile > 1 && tile / 2 >= segm_store) tile >>= 1;
+        if (per_sample * tile * 3 + red_bytes > p->smem_limit) {
+            free_level(p);
+            return chb_fail(CHB_ERR_UNSUPPORTED, "chb_plan_set_nint: too many segments for the pair kernel tile");
+        }
+        S.pair_tile = tile;
+        S.pair_ntiles = (segm_store + tile - 1) / tile;
+        long long items = (long long)max_round_bins * tile;
+        int thr = 64;
+        while (thr < 1024 && thr < items) thr <<= 1;
+        p->pair_threads = thr;
+        size_t arr = per_sample * tile;
+        p->pair_smem[0] = red_bytes + arr;       // energy only: spos
+        p->pair_smem[1] = red_bytes + 2 * arr;   // + sout
+        p->pair_smem[2] = red_bytes + 3 * arr;   // + sdpos
+    }
+    p->nint = nint;
+    p->ready = true;
+    p->fused_active = 0;
+#ifndef CHB_HOSTSIM
+    {
+        int rcf = chb_fused_setup(p->fused, p->sys, loops, T.G, p->device, p->smem_limit, p->num_sms, p->level_allocs);
+        if (rcf < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: fused setup failed"); }
+        p->fused_active = rcf;
+    }
+#endif
+    return CHB_OK;
+}
+
+extern "C" int chb_plan_query(const chb_plan *p, int what, int64_t *v) {
+    CHB_REQUIRE(p && v, CHB_ERR_INVALID_ARGUMENT, "chb_plan_query: NULL argument");
+    if (what == CHB_Q_DEVICE) { *v = p->device; return CHB_OK; }
+    if (what == CHB_Q_LAUNCHES) { *v = p->launches; return CHB_OK; }
+    if (what == CHB_Q_NLOOP) { *v = p->T.nloop; return CHB_OK; }
+    if (what == CHB_Q_NBIN) { *v = p->T.nbin; return CHB_OK; }
+    if (what == CHB_Q_NSEGM) { *v = p->T.nsegm; return CHB_OK; }
+    if (what == CHB_Q_GEODIM) { *v = p->T.G; return CHB_OK; }
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_plan_query: call chb_plan_set_nint first");
+    switch (what) {
+        case CHB_Q_NINT: *v = p->nint; break;
+        case CHB_Q_NPARAMS: *v = p->sys.nparams; break;
+        case CHB_Q_SEGM_SIZE: *v = p->sys.segm_size; break;
+        case CHB_Q_SEGM_STORE: *v = p->sys.segm_store; break;
+        case CHB_Q_SEGMPOS_SIZE: *v = p->sys.segsz; break;
+        case CHB_Q_FUSED: *v = (p->fused_enabled && p->fused_active) ? 1 : 0; break;
+        case CHB_Q_CHUNK: {
+            int64_t c = p->chunk_user;
+            if (c <= 0) {
+                long long per_state = std::max<long long>(1, p->sys.segsz * 8 * 3);
+                c = std::max<long long>((48LL << 20) / per_state, (2LL * p->num_sms + p->T.nloop - 1) / p->T.nloop);
+                c = std::max<int64_t>(c, 1);
+            }
+            *v = c;
+            break;
+        }
+        default: return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_plan_query: unknown query");
+    }
+    return CHB_OK;
+}
+
+extern "C" int chb_plan_set_chunk(chb_plan *p, int64_t chunk) {
+    CHB_REQUIRE(p && chunk >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_chunk: bad argument");
+    p->chunk_user = chunk;
+    return CHB_OK;
+}
+extern "C" int chb_plan_set_fused(chb_plan *p, int enable) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_fused: NULL plan");
+    p->fused_enabled = enable ? 1 : 0;
+    return CHB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// workspace layout (per chunk of `nb` states)
+// ------------------------------------------------------------------------------------------------
+struct Workspace {
+    double *segA, *segB, *segC;  // [nb][segsz]
+    double *kin_part;            // [nb][nloop]
+    double *pot_part;            // [nb][ntiles]
+    cd *scratch;                 // [nb][scratch_per_state]
+};
+static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+static int64_t plan_chunk(const chb_plan *p, int64_t batch) {
+    int64_t c = 1;
+    chb_plan_query(p, CHB_Q_CHUNK, &c);
+    return std::max<int64_t>(1, std::min<int64_t>(c, std::max<int64_t>(batch, 1)));
+}
+static size_t ws_bytes_for(const chb_plan *p, int64_t nb) {
+    const ChbSys &S = p->sys;
+    size_t b = 0;
+    b += 3 * align_up((size_t)nb * S.segsz * sizeof(double));
+    b += align_up((size_t)nb * S.nloop * sizeof(double));
+    b += align_up((size_t)nb * S.pair_ntiles * sizeof(double));
+    bool any_scratch = false;
+    for (int il = 0; il < S.nloop; ++il)
+        if (!p->loop_in_smem[il]) any_scratch = true;
+    b += align_up(any_scratch ? (size_t)nb * S.scratch_per_state * sizeof(cd) : 16);
+    return b;
+}
+static Workspace ws_carve(const chb_plan *p, void *base, int64_t nb) {
+    const ChbSys &S = p->sys;
+    Workspace w;
+    char *q = (char *)base;
+    size_t seg = align_up((size_t)nb * S.segsz * sizeof(double));
+    w.segA = (double *)q; q += seg;
+    w.segB = (double *)q; q += seg;
+    w.segC = (double *)q; q += seg;
+    w.kin_part = (double *)q; q += align_up((size_t)nb * S.nloop * sizeof(double));
+    w.pot_part = (double *)q; q += align_up((size_t)nb * S.pair_ntiles * sizeof(double));
+    w.scratch = (cd *)q;
+    return w;
+}
+
+extern "C" int chb_workspace_bytes(const chb_plan *p, int64_t batch, size_t *out) {
+    CHB_REQUIRE(p && out && batch >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_workspace_bytes: bad argument");
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_workspace_bytes: call chb_plan_set_nint first");
+    *out = ws_bytes_for(p, plan_chunk(p, batch)) + 256;
+    return CHB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernels (GPU) / block loops (hostsim)
+// ------------------------------------------------------------------------------------------------
+#ifndef CHB_HOSTSIM
+struct DevCtx {
+    template <class F>
+    __device__ __forceinline__ void par(F f) {
+        f((int)threadIdx.x, (int)blockDim.x);
+        __syncthreads();
+    }
+};
+extern __shared__ __align__(16) unsigned char chb_smem_raw[];
+#define CHB_KERNEL __global__
+#define CHB_BLOCK_ID ((long long)blockIdx.x)
+#define CHB_NTHREADS ((int)blockDim.x)
+#define CHB_CTX_DECL DevCtx ctx
+#define CHB_SMEM chb_smem_raw
+#else
+struct HostCtx {
+    int nthr;
+    template <class F>
+    void par(F f) {
+        for (int t = 0; t < nthr; ++t) f(t, nthr);
+    }
+};
+static thread_local long long sim_block_id;
+static thread_local int sim_nthreads;
+static thread_local unsigned char *sim_smem;
+#define CHB_KERNEL static
+#define CHB_BLOCK_ID sim_block_id
+#define CHB_NTHREADS sim_nthreads
+#define CHB_CTX_DECL HostCtx ctx{sim_nthreads}
+#define CHB_SMEM sim_smem
+#endif
+
+// one CTA per (state, loop): params -> segmpos (+ kinetic partial)
+CHB_KERNEL void k_fwd(ChbSys S, const double *params, double *segmpos, cd *scratch, double *kin_part,
+                      unsigned long long smem_mask) {
+    CHB_CTX_DECL;
+    const long long blk = CHB_BLOCK_ID;
+    const int il = (int)(blk % S.nloop);
+    const long long b = blk / S.nloop;
+    const ChbLoop &L = S.loops[il];
+    double *red = (double *)CHB_SMEM;
+    cd *buf = ((smem_mask >> il) & 1ULL) ? (cd *)(CHB_SMEM + sizeof(double) * 1024)
+                                         : scratch + b * S.scratch_per_state + L.scratch_off;
+    cta_params_to_segmpos(ctx, S, L, params + b * S.nparams, segmpos ? segmpos + b * S.segsz : (double *)0, buf, red,
+                          kin_part ? kin_part + b * S.nloop + il : (double *)0);
+}
+
+// one CTA per (state, loop): segment array -> params (mode 0 transpose, 1 inverse)
+CHB_KERNEL void k_adj(ChbSys S, const double *seg, double *out, const double *kin_src, cd *scratch, int mode,
+                      unsigned long long smem_mask) {
+    CHB_CTX_DECL;
+    const long long blk = CHB_BLOCK_ID;
+    const int il = (int)(blk % S.nloop);
+    const long long b = blk / S.nloop;
+    const ChbLoop &L = S.loops[il];
+    cd *buf = ((smem_mask >> il) & 1ULL) ? (cd *)(CHB_SMEM + sizeof(double) * 1024)
+                                         : scratch + b * S.scratch_per_state + L.scratch_off;
+    cta_segm_to_params(ctx, S, L, seg + b * S.segsz, out + b * S.nparams, kin_src ? kin_src + b * S.nparams : (const double *)0,
+                       buf, mode);
+}
+
+template <int MODE>
+CHB_KERNEL void k_pair(ChbSys S, const double *seg, const double *dseg, double *out, double *pot_part, double globalmul) {
+    CHB_CTX_DECL;
+    const long long blk = CHB_BLOCK_ID;
+    const int tile = (int)(blk % S.pair_ntiles);
+    const long long b = blk / S.pair_ntiles;
+    double *red = (double *)CHB_SMEM;
+    const size_t arr = (size_t)S.nsegm * S.G * S.pair_tile;
+    double *spos = red + 1024;
+    double *sout = spos + arr;
+    double *sdpos = sout + arr;
+    cta_pair<MODE>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
+                   out ? out + b * S.segsz : (double *)0, pot_part ? pot_part + b * S.pair_ntiles + tile : (double *)0, tile,
+                   globalmul, spos, sdpos, sout, red);
+}
+
+CHB_KERNEL void k_kin(ChbSys S, const double *params, double *kin_out, int kin_stride) {
+    CHB_CTX_DECL;
+    const long long b = CHB_BLOCK_ID;
+    cta_kin(ctx, S, params + b * S.nparams, kin_out + b * kin_stride, (double *)CHB_SMEM);
+}
+
+// out[b] = sum kin_part[b][0..nk) + psign * sum pot_part[b][0..np)
+CHB_KERNEL void k_finish(double *out, const double *kin_part, int nk, const double *pot_part, int np, long long nstates,
+                         double psign) {
+#ifndef CHB_HOSTSIM
+    long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < nstates) out[b] = chb_finish_action(kin_part + b * nk, kin_part ? nk : 0, pot_part + b * np, pot_part ? np : 0, psign);
+#else
+    for (int t = 0; t < sim_nthreads; ++t) {
+        long long b = sim_block_id * sim_nthreads + t;
+        if (b < nstates) out[b] = chb_finish_action(kin_part + b * nk, kin_part ? nk : 0, pot_part + b * np, pot_part ? np : 0, psign);
+    }
+#endif
+}
+
+#ifndef CHB_HOSTSIM
+#define CHB_LAUNCH(p, kern, grid, block, smem, stream, ...)                                                  \
+    do {                                                                                                     \
+        if ((smem) > 48 * 1024) {                                                                            \
+            CHB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); \
+        }                                                                                                    \
+        kern<<<(unsigned)(grid), (unsigned)(block), (smem), (stream)>>>(__VA_ARGS__);                       \
+        CHB_CUDA(cudaGetLastError());                                                                        \
+        (p)->launches++;                                                                                     \
+    } while (0)
+#else
+#define CHB_LAUNCH(p, kern, grid, block, smem, stream, ...)             \
+    do {                                                                \
+        std::vector<unsigned char> smem_buf_((smem) + 64);              \
+        sim_smem = smem_buf_.data();                                    \
+        sim_smem += (16 - ((uintptr_t)sim_smem & 15)) & 15;             \
+        sim_nthreads = (int)(block);                                    \
+        for (long long blk_ = 0; blk_ < (long long)(grid); ++blk_) {    \
+            sim_block_id = blk_;                                        \
+            kern(__VA_ARGS__);                                          \
+        }                                                               \
+        (p)->launches++;                                                \
+    } while (0)
+#endif
+
+static unsigned long long smem_mask(const chb_plan *p) {
+    unsigned long long m = 0;
+    for (int il = 0; il < p->sys.nloop && il < 64; ++il)
+        if (p->loop_in_smem[il]) m |= 1ULL << il;
+    return m;
+}
+
+// ------------------------------------------------------------------------------------------------
+// operator drivers
+// ------------------------------------------------------------------------------------------------
+#define CHB_OP_PROLOGUE(name)                                                                                   \
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, name ": NULL plan");                                               \
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, name ": call chb_plan_set_nint first");                            \
+    CHB_REQUIRE(batch >= 0, CHB_ERR_INVALID_ARGUMENT, name ": negative batch");                                 \
+    if (batch == 0) return CHB_OK;                                                                              \
+    CHB_REQUIRE(p->sys.nloop <= 64, CHB_ERR_UNSUPPORTED, name ": more than 64 loops");                          \
+    const ChbSys &S = p->sys;                                                                                   \
+    const int64_t chunk = plan_chunk(p, batch);                                                                 \
+    CHB_REQUIRE(ws && ws_bytes >= ws_bytes_for(p, chunk), CHB_ERR_WORKSPACE, name ": workspace missing or too small"); \
+    chb_stream_t st = (chb_stream_t)stream;                                                                     \
+    void *ws_al = (void *)(((uintptr_t)ws + 255) & ~(uintptr_t)255);                                            \
+    Workspace W = ws_carve(p, ws_al, chunk);                                                                    \
+    const unsigned long long mask = smem_mask(p);                                                               \
+    (void)W; (void)mask; (void)st; (void)S;
+#ifndef CHB_HOSTSIM
+#define CHB_SET_DEVICE() CHB_CUDA(cudaSetDevice(p->device))
+#else
+#define CHB_SET_DEVICE() \
+    do {                 \
+    } while (0)
+#endif
+
+static int launch_fwd(chb_plan *p, int64_t nb, const double *params, double *segmpos, Workspace &W, bool want_kin,
+                      unsigned long long mask, chb_stream_t st) {
+    CHB_LAUNCH(p, k_fwd, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, p->sys, params, segmpos, W.scratch,
+               want_kin ? W.kin_part : (double *)0, mask);
+    return CHB_OK;
+}
+static int launch_adj(chb_plan *p, int64_t nb, const double *seg, double *out, const double *kin_src, Workspace &W,
+                      int mode, unsigned long long mask, chb_stream_t st) {
+    CHB_LAUNCH(p, k_adj, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, p->sys, seg, out, kin_src, W.scratch, mode,
+               mask);
+    return CHB_OK;
+}
+static int launch_pair(chb_plan *p, int mode, int64_t nb, const double *seg, const double *dseg, double *out,
+                       double *pot_part, double globalmul, chb_stream_t st) {
+    const long long grid = nb * p->sys.pair_ntiles;
+    if (mode == 0)
+        CHB_LAUNCH(p, k_pair<0>, grid, p->pair_threads, p->pair_smem[0], st, p->sys, seg, dseg, out, pot_part, globalmul);
+    else if (mode == 1)
+        CHB_LAUNCH(p, k_pair<1>, grid, p->pair_threads, p->pair_smem[1], st, p->sys, seg, dseg, out, pot_part, globalmul);
+    else
+        CHB_LAUNCH(p, k_pair<2>, grid, p->pair_threads, p->pair_smem[2], st, p->sys, seg, dseg, out, pot_part, globalmul);
+    return CHB_OK;
+}
+static int launch_finish(chb_plan *p, int64_t nb, double *out, const double *kin_part, int nk, const double *pot_part,
+                         int np, chb_stream_t st, double psign = -1.0) {
+    CHB_LAUNCH(p, k_finish, (nb + 127) / 128, 128, 0, st, out, kin_part, nk, pot_part, np, (long long)nb, psign);
+    return CHB_OK;
+}
+static int launch_kin(chb_plan *p, int64_t nb, const double *params, double *kin_out, int stride, chb_stream_t st) {
+    CHB_LAUNCH(p, k_kin, nb, 256, sizeof(double) * 256, st, p->sys, params, kin_out, stride);
+    return CHB_OK;
+}
+#define CHB_TRY(x)          \
+    do {                    \
+        int rc_ = (x);      \
+        if (rc_) return rc_; \
+    } while (0)
+
+extern "C" int chb_params_to_segmpos_dev(chb_plan *p, int64_t batch, const double *params, double *segmpos, void *ws,
+                                         size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_params_to_segmpos_dev");
+    CHB_REQUIRE(params && segmpos, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_segmpos_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_fwd(p, nb, params + c0 * S.nparams, segmpos + c0 * S.segsz, W, false, mask, st));
+    }
+    return CHB_OK;
+}
+
+static int segm_to_params_common(chb_plan *p, int64_t batch, const double *seg, double *params, void *ws,
+                                 size_t ws_bytes, void *stream, int mode, const char *name) {
+    CHB_OP_PROLOGUE("chb_segmpos_to_params(_T)_dev");
+    (void)name;
+    CHB_REQUIRE(seg && params, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_to_params(_T)_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_adj(p, nb, seg + c0 * S.segsz, params + c0 * S.nparams, nullptr, W, mode, mask, st));
+    }
+    return CHB_OK;
+}
+extern "C" int chb_segmpos_to_params_dev(chb_plan *p, int64_t batch, const double *segmpos, double *params, void *ws,
+                                         size_t ws_bytes, void *stream) {
+    return segm_to_params_common(p, batch, segmpos, params, ws, ws_bytes, stream, 1, "chb_segmpos_to_params_dev");
+}
+extern "C" int chb_segmpos_to_params_T_dev(chb_plan *p, int64_t batch, const double *segmpos, double *params, void *ws,
+                                           size_t ws_bytes, void *stream) {
+    return segm_to_params_common(p, batch, segmpos, params, ws, ws_bytes, stream, 0, "chb_segmpos_to_params_T_dev");
+}
+
+extern "C" int chb_params_to_kin_nrg_dev(chb_plan *p, int64_t batch, const double *params, double *kin, void *ws,
+                                         size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_params_to_kin_nrg_dev");
+    CHB_REQUIRE(params && kin, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_kin_nrg_dev: NULL array");
+    CHB_SET_DEVICE();
+    CHB_TRY(launch_kin(p, batch, params, kin, 1, st));
+    return CHB_OK;
+}
+
+extern "C" int chb_segmpos_to_pot_nrg_dev(chb_plan *p, int64_t batch, const double *segmpos, double *pot, void *ws,
+                                          size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_segmpos_to_pot_nrg_dev");
+    CHB_REQUIRE(segmpos && pot, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_to_pot_nrg_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_pair(p, 0, nb, segmpos + c0 * S.segsz, nullptr, nullptr, W.pot_part, 1.0, st));
+        CHB_TRY(launch_finish(p, nb, pot + c0, nullptr, 0, W.pot_part, S.pair_ntiles, st, +1.0));
+    }
+    return CHB_OK;
+}
+
+extern "C" int chb_segmpos_to_pot_nrg_grad_dev(chb_plan *p, int64_t batch, const double *segmpos, double globalmul,
+                                               double *grad, void *ws, size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_segmpos_to_pot_nrg_grad_dev");
+    CHB_REQUIRE(segmpos && grad, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_to_pot_nrg_grad_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_pair(p, 1, nb, segmpos + c0 * S.segsz, nullptr, grad + c0 * S.segsz, nullptr, globalmul, st));
+    }
+    return CHB_OK;
+}
+
+extern "C" int chb_segmpos_to_pot_nrg_hess_dev(chb_plan *p, int64_t batch, const double *segmpos, const double *dsegmpos,
+                                               double globalmul, double *hess, void *ws, size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_segmpos_to_pot_nrg_hess_dev");
+    CHB_REQUIRE(segmpos && dsegmpos && hess, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_to_pot_nrg_hess_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_pair(p, 2, nb, segmpos + c0 * S.segsz, dsegmpos + c0 * S.segsz, hess + c0 * S.segsz, nullptr,
+                            globalmul, st));
+    }
+    return CHB_OK;
+}
+
+extern "C" int chb_params_to_action_dev(chb_plan *p, int64_t batch, const double *params, double *action, void *ws,
+                                        size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_params_to_action_dev");
+    CHB_REQUIRE(params && action, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_action_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_fwd(p, nb, params + c0 * S.nparams, W.segA, W, true, mask, st));
+        CHB_TRY(launch_pair(p, 0, nb, W.segA, nullptr, nullptr, W.pot_part, 1.0, st));
+        CHB_TRY(launch_finish(p, nb, action + c0, W.kin_part, S.nloop, W.pot_part, S.pair_ntiles, st));
+    }
+    return CHB_OK;
+}
+
+extern "C" int chb_params_to_action_grad_dev(chb_plan *p, int64_t batch, const double *params, double *action,
+                                             double *grad, double *segmpos_out, void *ws, size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_params_to_action_grad_dev");
+    CHB_REQUIRE(params && grad, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_action_grad_dev: NULL array");
+    CHB_SET_DEVICE();
+#ifndef CHB_HOSTSIM
+    if (p->fused_enabled && p->fused_active && !segmpos_out) {
+        int rcf = chb_fused_action_grad(p->fused, p->sys, batch, params, action, grad, st);
+        if (rcf != 0) return chb_fail(CHB_ERR_CUDA, "chb_params_to_action_grad_dev: fused kernel launch failed");
+        p->launches += 1;
+        return CHB_OK;
+    }
+#endif
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        double *seg = segmpos_out ? segmpos_out + c0 * S.segsz : W.segA;
+        CHB_TRY(launch_fwd(p, nb, params + c0 * S.nparams, seg, W, action != nullptr, mask, st));
+        CHB_TRY(launch_pair(p, 1, nb, seg, nullptr, W.segB, action ? W.pot_part : nullptr, -1.0, st));
+        CHB_TRY(launch_adj(p, nb, W.segB, grad + c0 * S.nparams, params + c0 * S.nparams, W, 0, mask, st));
+        if (action) CHB_TRY(launch_finish(p, nb, action + c0, W.kin_part, S.nloop, W.pot_part, S.pair_ntiles, st));
+    }
+    return CHB_OK;
+}
+
+extern "C" int chb_params_to_action_hess_dev(chb_plan *p, int64_t batch, const double *params, const double *dparams,
+                                             double *hess, void *ws, size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_params_to_action_hess_dev");
+    CHB_REQUIRE(params && dparams && hess, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_action_hess_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_fwd(p, nb, params + c0 * S.nparams, W.segA, W, false, mask, st));
+        CHB_TRY(launch_fwd(p, nb, dparams + c0 * S.nparams, W.segB, W, false, mask, st));
+        CHB_TRY(launch_pair(p, 2, nb, W.segA, W.segB, W.segC, nullptr, -1.0, st));
+        CHB_TRY(launch_adj(p, nb, W.segC, hess + c0 * S.nparams, dparams + c0 * S.nparams, W, 0, mask, st));
+    }
+    return CHB_OK;
+}
+
+extern "C" int chb_segmpos_params_to_action_dev(chb_plan *p, int64_t batch, const double *segmpos, const double *params,
+                                                double *action, void *ws, size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_segmpos_params_to_action_dev");
+    CHB_REQUIRE(segmpos && params && action, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_params_to_action_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_kin(p, nb, params + c0 * S.nparams, W.kin_part, 1, st));
+        CHB_TRY(launch_pair(p, 0, nb, segmpos + c0 * S.segsz, nullptr, nullptr, W.pot_part, 1.0, st));
+        CHB_TRY(launch_finish(p, nb, action + c0, W.kin_part, 1, W.pot_part, S.pair_ntiles, st));
+    }
+    return CHB_OK;
+}
+
+extern "C" int chb_segmpos_params_to_action_grad_dev(chb_plan *p, int64_t batch, const double *segmpos,
+                                                     const double *params, double *action, double *grad, void *ws,
+                                                     size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_segmpos_params_to_action_grad_dev");
+    CHB_REQUIRE(segmpos && params && grad, CHB_ERR_INVALID_ARGUMENT,
+                "chb_segmpos_params_to_action_grad_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        if (action) CHB_TRY(launch_kin(p, nb, params + c0 * S.nparams, W.kin_part, 1, st));
+        CHB_TRY(launch_pair(p, 1, nb, segmpos + c0 * S.segsz, nullptr, W.segB, action ? W.pot_part : nullptr, -1.0, st));
+        CHB_TRY(launch_adj(p, nb, W.segB, grad + c0 * S.nparams, params + c0 * S.nparams, W, 0, mask, st));
+        if (action) CHB_TRY(launch_finish(p, nb, action + c0, W.kin_part, 1, W.pot_part, S.pair_ntiles, st));
+    }
+    return CHB_OK;
+}
+
+extern "C" int chb_segmpos_dparams_to_action_hess_dev(chb_plan *p, int64_t batch, const double *segmpos,
+                                                      const double *dparams, double *hess, void *ws, size_t ws_bytes,
+                                                      void *stream) {
+    CHB_OP_PROLOGUE("chb_segmpos_dparams_to_action_hess_dev");
+    CHB_REQUIRE(segmpos && dparams && hess, CHB_ERR_INVALID_ARGUMENT,
+                "chb_segmpos_dparams_to_action_hess_dev: NULL array");
+    CHB_SET_DEVICE();
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_fwd(p, nb, dparams + c0 * S.nparams, W.segB, W, false, mask, st));
+        CHB_TRY(launch_pair(p, 2, nb, segmpos + c0 * S.segsz, W.segB, W.segC, nullptr, -1.0, st));
+        CHB_TRY(launch_adj(p, nb, W.segC, hess + c0 * S.nparams, dparams + c0 * S.nparams, W, 0, mask, st));
+    }
+    return CHB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// memory helpers + host-pointer operators
+// ------------------------------------------------------------------------------------------------
+extern "C" int chb_malloc_device(chb_plan *p, size_t bytes, void **out) {
+    CHB_REQUIRE(p && out, CHB_ERR_INVALID_ARGUMENT, "chb_malloc_device: NULL argument");
+    return dev_alloc(p, bytes, out);
+}
+extern "C" int chb_free_device(chb_plan *p, void *ptr) {
+    (void)p;
+    if (ptr) dev_free(ptr);
+    return CHB_OK;
+}
+extern "C" int chb_malloc_pinned(size_t bytes, void **out) {
+    CHB_REQUIRE(out, CHB_ERR_INVALID_ARGUMENT, "chb_malloc_pinned: NULL argument");
+    if (bytes == 0) bytes = 16;
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaMallocHost(out, bytes));
+#else
+    *out = malloc(bytes);
+#endif
+    return CHB_OK;
+}
+extern "C" int chb_free_pinned(void *ptr) {
+#ifndef CHB_HOSTSIM
+    if (ptr) cudaFreeHost(ptr);
+#else
+    free(ptr);
+#endif
+    return CHB_OK;
+}
+extern "C" int chb_memcpy_h2d(chb_plan *p, void *dst, const void *src, size_t bytes, void *stream) {
+    CHB_REQUIRE(p && (bytes == 0 || (dst && src)), CHB_ERR_INVALID_ARGUMENT, "chb_memcpy_h2d: NULL argument");
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaSetDevice(p->device));
+    CHB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+#else
+    (void)stream;
+    memcpy(dst, src, bytes);
+#endif
+    return CHB_OK;
+}
+extern "C" int chb_memcpy_d2h(chb_plan *p, void *dst, const void *src, size_t bytes, void *stream) {
+    CHB_REQUIRE(p && (bytes == 0 || (dst && src)), CHB_ERR_INVALID_ARGUMENT, "chb_memcpy_d2h: NULL argument");
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaSetDevice(p->device));
+    CHB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+#else
+    (void)stream;
+    memcpy(dst, src, bytes);
+#endif
+    return CHB_OK;
+}
+extern "C" int chb_stream_synchronize(chb_plan *p, void *stream) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_stream_synchronize: NULL plan");
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaSetDevice(p->device));
+    CHB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+#else
+    (void)stream;
+#endif
+    return CHB_OK;
+}
+
+static int ensure_stage(chb_plan *p, size_t bytes) {
+    if (bytes <= p->stage_dev_bytes) return CHB_OK;
+    if (p->stage_dev) dev_free(p->stage_dev);
+    p->stage_dev = nullptr;
+    p->stage_dev_bytes = 0;
+    size_t want = bytes + bytes / 4;
+    int rc = dev_alloc(p, want, &p->stage_dev);
+    if (rc) return rc;
+    p->stage_dev_bytes = want;
+    return CHB_OK;
+}
+
+extern "C" int chb_run_host(chb_plan *p, int op, int64_t batch, const double *in0, const double *in1, double scalar,
+                            double *out0, double *out1) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_run_host: NULL plan");
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_run_host: call chb_plan_set_nint first");
+    CHB_REQUIRE(batch >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_run_host: negative batch");
+    if (batch == 0) return CHB_OK;
+    std::lock_guard<std::mutex> lock(p->host_mutex);
+    const ChbSys &S = p->sys;
+    const size_t np = (size_t)S.nparams, ns = (size_t)S.segsz;
+    size_t n_in0 = 0, n_in1 = 0, n_out0 = 0, n_out1 = 0;
+    switch (op) {
+        case CHB_OP_PARAMS_TO_SEGMPOS: n_in0 = np; n_out0 = ns; break;
+        case CHB_OP_SEGMPOS_TO_PARAMS:
+        case CHB_OP_SEGMPOS_TO_PARAMS_T: n_in0 = ns; n_out0 = np; break;
+        case CHB_OP_ACTION: n_in0 = np; n_out0 = 1; break;
+        case CHB_OP_ACTION_GRAD: n_in0 = np; n_out0 = out0 ? 1 : 0; n_out1 = np; break;
+        case CHB_OP_ACTION_HESS: n_in0 = np; n_in1 = np; n_out0 = np; break;
+        case CHB_OP_SEGMPOS_ACTION: n_in0 = ns; n_in1 = np; n_out0 = 1; break;
+        case CHB_OP_SEGMPOS_ACTION_GRAD: n_in0 = ns; n_in1 = np; n_out0 = out0 ? 1 : 0; n_out1 = np; break;
+        case CHB_OP_SEGMPOS_ACTION_HESS: n_in0 = ns; n_in1 = np; n_out0 = np; break;
+        case CHB_OP_KIN: n_in0 = np; n_out0 = 1; break;
+        case CHB_OP_POT: n_in0 = ns; n_out0 = 1; break;
+        case CHB_OP_POT_GRAD: n_in0 = ns; n_out0 = ns; break;
+        case CHB_OP_POT_HESS: n_in0 = ns; n_in1 = ns; n_out0 = ns; break;
+        default: return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_run_host: unknown op");
+    }
+    CHB_REQUIRE(in0 && (n_in1 == 0 || in1) && (n_out0 == 0 || out0) && (n_out1 == 0 || out1), CHB_ERR_INVALID_ARGUMENT,
+                "chb_run_host: NULL array for this op");
+    size_t wsb = 0;
+    CHB_TRY(chb_workspace_bytes(p, batch, &wsb));
+    const size_t B = (size_t)batch;
+    size_t b_in0 = align_up(B * n_in0 * 8), b_in1 = align_up(B * n_in1 * 8), b_out0 = align_up(B * std::max<size_t>(n_out0, 1) * 8),
+           b_out1 = align_up(B * n_out1 * 8);
+    CHB_TRY(ensure_stage(p, b_in0 + b_in1 + b_out0 + b_out1 + align_up(wsb) + 512));
+    char *q = (char *)(((uintptr_t)p->stage_dev + 255) & ~(uintptr_t)255);
+    double *d_in0 = (double *)q; q += b_in0;
+    double *d_in1 = (double *)q; q += b_in1;
+    double *d_out0 = (double *)q; q += b_out0;
+    double *d_out1 = (double *)q; q += b_out1;
+    void *d_ws = q;
+    void *st = nullptr;
+    CHB_TRY(chb_memcpy_h2d(p, d_in0, in0, B * n_in0 * 8, st));
+    if (n_in1) CHB_TRY(chb_memcpy_h2d(p, d_in1, in1, B * n_in1 * 8, st));
+    int rc = CHB_OK;
+    switch (op) {
+        case CHB_OP_PARAMS_TO_SEGMPOS: rc = chb_params_to_segmpos_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
+        case CHB_OP_SEGMPOS_TO_PARAMS: rc = chb_segmpos_to_params_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
+        case CHB_OP_SEGMPOS_TO_PARAMS_T: rc = chb_segmpos_to_params_T_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
+        case CHB_OP_ACTION: rc = chb_params_to_action_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
+        case CHB_OP_ACTION_GRAD:
+            rc = chb_params_to_action_grad_dev(p, batch, d_in0, n_out0 ? d_out0 : nullptr, d_out1, nullptr, d_ws, wsb, st);
+            break;
+        case CHB_OP_ACTION_HESS: rc = chb_params_to_action_hess_dev(p, batch, d_in0, d_in1, d_out0, d_ws, wsb, st); break;
+        case CHB_OP_SEGMPOS_ACTION: rc = chb_segmpos_params_to_action_dev(p, batch, d_in0, d_in1, d_out0, d_ws, wsb, st); break;
+        case CHB_OP_SEGMPOS_ACTION_GRAD:
+            rc = chb_segmpos_params_to_action_grad_dev(p, batch, d_in0, d_in1, n_out0 ? d_out0 : nullptr, d_out1, d_ws, wsb, st);
+            break;
+        case CHB_OP_SEGMPOS_ACTION_HESS:
+            rc = chb_segmpos_dparams_to_action_hess_dev(p, batch, d_in0, d_in1, d_out0, d_ws, wsb, st);
+            break;
+        case CHB_OP_KIN: rc = chb_params_to_kin_nrg_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
+        case CHB_OP_POT: rc = chb_segmpos_to_pot_nrg_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
+        case CHB_OP_POT_GRAD: rc = chb_segmpos_to_pot_nrg_grad_dev(p, batch, d_in0, scalar, d_out0, d_ws, wsb, st); break;
+        case CHB_OP_POT_HESS: rc = chb_segmpos_to_pot_nrg_hess_dev(p, batch, d_in0, d_in1, scalar, d_out0, d_ws, wsb, st); break;
+    }
+    if (rc) return rc;
+    if (n_out0) CHB_TRY(chb_memcpy_d2h(p, out0, d_out0, B * n_out0 * 8, st));
+    if (n_out1) CHB_TRY(chb_memcpy_d2h(p, out1, d_out1, B * n_out1 * 8, st));
+    CHB_TRY(chb_stream_synchronize(p, st));
+    return CHB_OK;
+}

@@ -1,0 +1,405 @@
+"""Host-side mirror of the reference ``NBodySyst`` API for the action hot path, backed by the B200 library.
+
+Same method names, argument meaning and error behaviour as the reference's Python-visible methods
+(choreo/cython/_NBodySyst.pyx:2519-3110, 3607-3727), so that
+``find.py`` / ``scipy_plus/nonlin.py`` can drive it unchanged for one state, plus ``*_batched`` variants that
+evaluate many independent states per call (leading batch dimension).
+
+Array carriers:
+  * NumPy arrays (host): staged through the library (``chb_run_host``: H2D, kernels, D2H, synchronous);
+  * torch CUDA tensors (optional): passed by ``data_ptr()`` to the ``*_dev`` entry points on torch's current
+    stream; results are torch tensors on the same device.  torch is only an array carrier here.
+
+There is no CPU fallback: constructing the object without the CUDA library / an sm_100 device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import types
+from typing import Any, Optional
+
+import numpy as np
+
+from . import _lib as L
+from .tables import PlanTables, extract_tables
+
+
+def _is_torch(x: Any) -> bool:
+    return type(x).__module__.startswith("torch")
+
+
+class NBodySystB200:
+    def __init__(self, tables: PlanTables, nint: Optional[int] = None, device: int = 0, _lib_handle=None):
+        self._lib = _lib_handle if _lib_handle is not None else L.load()
+        self.tables = tables
+        self.device = int(device)
+        self._plan = C.c_void_p()
+        struct, keep = L.tables_struct(tables)
+        L.check(self._lib, self._lib.chb_plan_create(C.byref(struct), self.device, C.byref(self._plan)))
+        del keep
+        self._ws = None  # torch workspace tensor (device path)
+        self._nint = 0
+        self.nint = int(nint) if nint is not None else 2 * tables.nint_min  # reference: nint_fac = 1 (:895)
+
+    # ------------------------------------------------------------------ construction helpers
+    @classmethod
+    def from_reference(cls, NBS, device: int = 0, _lib_handle=None) -> "NBodySystB200":
+        """Build from a live reference ``choreo.NBodySyst`` (tables are read from its public attributes)."""
+        return cls(extract_tables(NBS), nint=int(NBS.nint), device=device, _lib_handle=_lib_handle)
+
+    @classmethod
+    def from_file(cls, path: str, nint: Optional[int] = None, device: int = 0) -> "NBodySystB200":
+        return cls(PlanTables.load(path), nint=nint, device=device)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_plan", None) is not None and self._plan.value:
+                self._lib.chb_plan_destroy(self._plan)
+                self._plan = C.c_void_p()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ properties (reference names)
+    def _q(self, what: int) -> int:
+        v = C.c_int64()
+        L.check(self._lib, self._lib.chb_plan_query(self._plan, what, C.byref(v)))
+        return int(v.value)
+
+    geodim = property(lambda self: self.tables.geodim)
+    nbody = property(lambda self: self.tables.nbody)
+    nloop = property(lambda self: self.tables.nloop)
+    nsegm = property(lambda self: self.tables.nsegm)
+    nint_min = property(lambda self: self.tables.nint_min)
+    nbin_segm_unique = property(lambda self: self.tables.nbin)
+    GreaterNStore = property(lambda self: self.tables.greater_nstore)
+
+    @property
+    def nint(self) -> int:
+        return self._nint
+
+    @nint.setter
+    def nint(self, nint_in: int) -> None:
+        # reference setter: ValueError when nint % (2*nint_min) != 0 (:545-546); re-plans all buffers (:589-590)
+        L.check(self._lib, self._lib.chb_plan_set_nint(self._plan, int(nint_in)))
+        self._nint = int(nint_in)
+        self.nparams = self._q(L.Q_NPARAMS)
+        self.segm_size = self._q(L.Q_SEGM_SIZE)
+        self.segm_store = self._q(L.Q_SEGM_STORE)
+        self.ncoeffs = self._nint // 2 + 1
+        self._segsz = self._q(L.Q_SEGMPOS_SIZE)
+        self._ws = None
+
+    @property
+    def nint_fac(self) -> int:
+        return self._nint // (2 * self.nint_min)
+
+    @nint_fac.setter
+    def nint_fac(self, fac: int) -> None:
+        self.nint = 2 * self.nint_min * int(fac)
+
+    @property
+    def segmpos_shape(self):
+        return (self.nsegm, self.segm_store, self.geodim)
+
+    @property
+    def kernel_launches(self) -> int:
+        return self._q(L.Q_LAUNCHES)
+
+    @property
+    def fused(self) -> bool:
+        return bool(self._q(L.Q_FUSED))
+
+    def set_chunk(self, chunk: int) -> None:
+        L.check(self._lib, self._lib.chb_plan_set_chunk(self._plan, int(chunk)))
+        self._ws = None
+
+    def set_fused(self, enable: bool) -> None:
+        L.check(self._lib, self._lib.chb_plan_set_fused(self._plan, int(bool(enable))))
+
+    # ------------------------------------------------------------------ plumbing
+    def _check(self, arr, last_shape, what: str):
+        shp = tuple(arr.shape)
+        n = len(last_shape)
+        if shp[-n:] != tuple(last_shape):
+            raise ValueError(f"{what}: expected trailing shape {tuple(last_shape)}, got {shp}")
+        batch = int(np.prod(shp[:-n], dtype=np.int64)) if len(shp) > n else 1
+        return batch, shp[:-n]
+
+    def _host(self, op, in0, in0_shape, in1=None, in1_shape=None, out0_shape=None, out1_shape=None, scalar=0.0,
+              want_out0=True):
+        a0 = np.ascontiguousarray(in0, dtype=np.float64)
+        batch, lead = self._check(a0, in0_shape, "input")
+        a1 = None
+        if in1 is not None:
+            a1 = np.ascontiguousarray(in1, dtype=np.float64)
+            b1, _ = self._check(a1, in1_shape, "second input")
+            if b1 != batch:
+                raise ValueError("batch sizes of the two inputs differ")
+        o0 = np.empty(lead + tuple(out0_shape), dtype=np.float64) if (out0_shape is not None and want_out0) else None
+        o1 = np.empty(lead + tuple(out1_shape), dtype=np.float64) if out1_shape is not None else None
+        vp = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None  # noqa: E731
+        L.check(self._lib, self._lib.chb_run_host(self._plan, op, batch, vp(a0), vp(a1), float(scalar), vp(o0), vp(o1)))
+        return o0, o1
+
+    def _workspace(self, batch: int, like):
+        import torch
+        need = C.c_size_t()
+        L.check(self._lib, self._lib.chb_workspace_bytes(self._plan, batch, C.byref(need)))
+        if self._ws is None or self._ws.numel() < need.value or self._ws.device != like.device:
+            self._ws = torch.empty(int(need.value), dtype=torch.uint8, device=like.device)
+        return self._ws
+
+    def _dev(self, fname, batch, ptr_args, like):
+        """Call a *_dev entry point: ptr_args is the list between (plan, batch) and (ws, ws_bytes, stream)."""
+        import torch
+        ws = self._workspace(batch, like)
+        stream = torch.cuda.current_stream(like.device).cuda_stream
+        fn = getattr(self._lib, fname)
+        conv = [a if isinstance(a, float) else (C.c_void_p(a.data_ptr()) if a is not None else None) for a in ptr_args]
+        L.check(self._lib, fn(self._plan, batch, *conv, C.c_void_p(ws.data_ptr()), ws.numel(), C.c_void_p(stream)))
+
+    def _tprep(self, t, last_shape, what):
+        import torch
+        if t.dtype != torch.float64 or not t.is_cuda:
+            raise ValueError(f"{what}: torch tensors must be float64 CUDA tensors")
+        if t.device.index != self.device:
+            raise ValueError(f"{what}: tensor on {t.device}, plan on cuda:{self.device}")
+        t = t.contiguous()
+        batch, lead = self._check(t, last_shape, what)
+        return t, batch, lead
+
+    # ------------------------------------------------------------------ transforms
+    def params_to_segmpos(self, params_mom_buf):
+        """_NBodySyst.pyx:3607-3635."""
+        if _is_torch(params_mom_buf):
+            import torch
+            x, b, lead = self._tprep(params_mom_buf, (self.nparams,), "params")
+            out = torch.empty(lead + self.segmpos_shape, dtype=torch.float64, device=x.device)
+            self._dev("chb_params_to_segmpos_dev", b, [x, out], x)
+            return out
+        return self._host(L.OP_PARAMS_TO_SEGMPOS, params_mom_buf, (self.nparams,), out0_shape=self.segmpos_shape)[0]
+
+    def segmpos_to_params(self, segmpos):
+        """_NBodySyst.pyx:3669-3696."""
+        if _is_torch(segmpos):
+            import torch
+            x, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
+            out = torch.empty(lead + (self.nparams,), dtype=torch.float64, device=x.device)
+            self._dev("chb_segmpos_to_params_dev", b, [x, out], x)
+            return out
+        return self._host(L.OP_SEGMPOS_TO_PARAMS, segmpos, self.segmpos_shape, out0_shape=(self.nparams,))[0]
+
+    def segmpos_to_params_T(self, segmpos):
+        """_NBodySyst.pyx:3699-3727."""
+        if _is_torch(segmpos):
+            import torch
+            x, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
+            out = torch.empty(lead + (self.nparams,), dtype=torch.float64, device=x.device)
+            self._dev("chb_segmpos_to_params_T_dev", b, [x, out], x)
+            return out
+        return self._host(L.OP_SEGMPOS_TO_PARAMS_T, segmpos, self.segmpos_shape, out0_shape=(self.nparams,))[0]
+
+    # ------------------------------------------------------------------ energies
+    @staticmethod
+    def _scalar(arr, lead):
+        return float(arr.reshape(-1)[0]) if lead == () else arr.reshape(lead)
+
+    def params_to_kin_nrg(self, params_mom_buf):
+        """_NBodySyst.pyx:2519-2525."""
+        if _is_torch(params_mom_buf):
+            import torch
+            x, b, lead = self._tprep(params_mom_buf, (self.nparams,), "params")
+            out = torch.empty(lead, dtype=torch.float64, device=x.device)
+            self._dev("chb_params_to_kin_nrg_dev", b, [x, out], x)
+            return out
+        a = np.asarray(params_mom_buf)
+        o, _ = self._host(L.OP_KIN, a, (self.nparams,), out0_shape=())
+        return self._scalar(o, a.shape[:-1])
+
+    def params_to_kin_nrg_grad(self, params_mom_buf):
+        """_NBodySyst.pyx:2527-2540: the parameters themselves on every k>0 entry, 0 elsewhere."""
+        a = np.ascontiguousarray(params_mom_buf, dtype=np.float64)
+        lvl = self.tables.level(self._nint)
+        mask = np.ones(self.nparams, dtype=bool)
+        for il in range(self.nloop):
+            ncor, _ = self.tables.ncor_nco_in(il)
+            mask[lvl.mom_off[il]:lvl.mom_off[il] + ncor] = False
+        return a * mask
+
+    def segmpos_to_pot_nrg(self, segmpos):
+        """cdef segm_pos_to_pot_nrg, _NBodySyst.pyx:6372-6469."""
+        if _is_torch(segmpos):
+            import torch
+            x, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
+            out = torch.empty(lead, dtype=torch.float64, device=x.device)
+            self._dev("chb_segmpos_to_pot_nrg_dev", b, [x, out], x)
+            return out
+        a = np.asarray(segmpos)
+        o, _ = self._host(L.OP_POT, a, self.segmpos_shape, out0_shape=())
+        return self._scalar(o, a.shape[:-3])
+
+    def segmpos_to_pot_nrg_grad(self, segmpos, globalmul: float = 1.0):
+        """cdef segm_pos_to_pot_nrg_grad, _NBodySyst.pyx:6472-6533 (into a zeroed buffer)."""
+        if _is_torch(segmpos):
+            import torch
+            x, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
+            out = torch.empty_like(x)
+            self._dev("chb_segmpos_to_pot_nrg_grad_dev", b, [x, float(globalmul), out], x)
+            return out
+        return self._host(L.OP_POT_GRAD, segmpos, self.segmpos_shape, out0_shape=self.segmpos_shape,
+                          scalar=globalmul)[0]
+
+    def segmpos_to_pot_nrg_hess(self, segmpos, dsegmpos, globalmul: float = 1.0):
+        """cdef segm_pos_to_pot_nrg_hess, _NBodySyst.pyx:6899-6962."""
+        if _is_torch(segmpos):
+            import torch
+            x, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
+            dx, b2, _ = self._tprep(dsegmpos, self.segmpos_shape, "dsegmpos")
+            if b != b2:
+                raise ValueError("batch sizes differ")
+            out = torch.empty_like(x)
+            self._dev("chb_segmpos_to_pot_nrg_hess_dev", b, [x, dx, float(globalmul), out], x)
+            return out
+        return self._host(L.OP_POT_HESS, segmpos, self.segmpos_shape, dsegmpos, self.segmpos_shape,
+                          out0_shape=self.segmpos_shape, scalar=globalmul)[0]
+
+    def params_to_pot_nrg(self, params_mom_buf):
+        """_NBodySyst.pyx:2563-2600."""
+        return self.segmpos_to_pot_nrg(self.params_to_segmpos(params_mom_buf))
+
+    def params_to_pot_nrg_grad(self, params_mom_buf):
+        """_NBodySyst.pyx:2603-2661."""
+        return self.segmpos_to_params_T(self.segmpos_to_pot_nrg_grad(self.params_to_segmpos(params_mom_buf), 1.0))
+
+    def params_to_pot_nrg_hess(self, params_mom_buf, dparams_mom_buf):
+        """_NBodySyst.pyx:2664-2747."""
+        seg = self.params_to_segmpos(params_mom_buf)
+        dseg = self.params_to_segmpos(dparams_mom_buf)
+        return self.segmpos_to_params_T(self.segmpos_to_pot_nrg_hess(seg, dseg, 1.0))
+
+    # ------------------------------------------------------------------ action chain
+    def params_to_action(self, params_mom_buf):
+        """_NBodySyst.pyx:2750-2791."""
+        if _is_torch(params_mom_buf):
+            import torch
+            x, b, lead = self._tprep(params_mom_buf, (self.nparams,), "params")
+            out = torch.empty(lead, dtype=torch.float64, device=x.device)
+            self._dev("chb_params_to_action_dev", b, [x, out], x)
+            return out
+        a = np.asarray(params_mom_buf)
+        o, _ = self._host(L.OP_ACTION, a, (self.nparams,), out0_shape=())
+        return self._scalar(o, a.shape[:-1])
+
+    def params_to_action_grad(self, params_mom_buf):
+        """_NBodySyst.pyx:2794-2873."""
+        return self.params_to_action_and_grad(params_mom_buf, want_action=False)[1]
+
+    def params_to_action_and_grad(self, params_mom_buf, want_action: bool = True, want_segmpos: bool = False):
+        """One fused evaluation of ``params_to_action`` + ``params_to_action_grad`` (unit U1 of SURVEY.md 8(d)).
+        Returns (action or None, grad[, segmpos])."""
+        if _is_torch(params_mom_buf):
+            import torch
+            x, b, lead = self._tprep(params_mom_buf, (self.nparams,), "params")
+            act = torch.empty(lead, dtype=torch.float64, device=x.device) if want_action else None
+            grad = torch.empty_like(x)
+            seg = torch.empty(lead + self.segmpos_shape, dtype=torch.float64, device=x.device) if want_segmpos else None
+            self._dev("chb_params_to_action_grad_dev", b, [x, act, grad, seg], x)
+            return (act, grad, seg) if want_segmpos else (act, grad)
+        a = np.asarray(params_mom_buf)
+        if want_segmpos:
+            raise ValueError("want_segmpos is only available on the device (torch) path")
+        o0, o1 = self._host(L.OP_ACTION_GRAD, a, (self.nparams,), out0_shape=(), out1_shape=(self.nparams,),
+                            want_out0=want_action)
+        return (self._scalar(o0, a.shape[:-1]) if want_action else None), o1
+
+    def params_to_action_hess(self, params_mom_buf, dparams_mom_buf):
+        """_NBodySyst.pyx:2876-2965."""
+        if _is_torch(params_mom_buf):
+            import torch
+            x, b, lead = self._tprep(params_mom_buf, (self.nparams,), "params")
+            dx, b2, _ = self._tprep(dparams_mom_buf, (self.nparams,), "dparams")
+            if b != b2:
+                raise ValueError("batch sizes differ")
+            out = torch.empty_like(x)
+            self._dev("chb_params_to_action_hess_dev", b, [x, dx, out], x)
+            return out
+        return self._host(L.OP_ACTION_HESS, params_mom_buf, (self.nparams,), dparams_mom_buf, (self.nparams,),
+                          out0_shape=(self.nparams,))[0]
+
+    def segmpos_params_to_action(self, segmpos, params_mom_buf):
+        """_NBodySyst.pyx:2968-2991."""
+        if _is_torch(segmpos):
+            import torch
+            s, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
+            x, b2, _ = self._tprep(params_mom_buf, (self.nparams,), "params")
+            if b != b2:
+                raise ValueError("batch sizes differ")
+            out = torch.empty(lead, dtype=torch.float64, device=x.device)
+            self._dev("chb_segmpos_params_to_action_dev", b, [s, x, out], x)
+            return out
+        a = np.asarray(params_mom_buf)
+        o, _ = self._host(L.OP_SEGMPOS_ACTION, segmpos, self.segmpos_shape, a, (self.nparams,), out0_shape=())
+        return self._scalar(o, a.shape[:-1])
+
+    def segmpos_params_to_action_grad(self, segmpos, params_mom_buf):
+        """_NBodySyst.pyx:2994-3041."""
+        if _is_torch(segmpos):
+            import torch
+            s, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
+            x, b2, _ = self._tprep(params_mom_buf, (self.nparams,), "params")
+            if b != b2:
+                raise ValueError("batch sizes differ")
+            out = torch.empty_like(x)
+            self._dev("chb_segmpos_params_to_action_grad_dev", b, [s, x, None, out], x)
+            return out
+        return self._host(L.OP_SEGMPOS_ACTION_GRAD, segmpos, self.segmpos_shape, params_mom_buf, (self.nparams,),
+                          out0_shape=(), out1_shape=(self.nparams,), want_out0=False)[1]
+
+    def segmpos_dparams_to_action_hess(self, segmpos, dparams_mom_buf):
+        """_NBodySyst.pyx:3044-3110 (the Krylov matvec)."""
+        if _is_torch(segmpos):
+            import torch
+            s, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
+            x, b2, _ = self._tprep(dparams_mom_buf, (self.nparams,), "dparams")
+            if b != b2:
+                raise ValueError("batch sizes differ")
+            out = torch.empty_like(x)
+            self._dev("chb_segmpos_dparams_to_action_hess_dev", b, [s, x, out], x)
+            return out
+        return self._host(L.OP_SEGMPOS_ACTION_HESS, segmpos, self.segmpos_shape, dparams_mom_buf, (self.nparams,),
+                          out0_shape=(self.nparams,))[0]
+
+    # batched aliases: every method above already accepts leading batch dimensions
+    params_to_action_batched = params_to_action
+    params_to_action_grad_batched = params_to_action_grad
+    params_to_action_hess_batched = params_to_action_hess
+    params_to_segmpos_batched = params_to_segmpos
+    segmpos_dparams_to_action_hess_batched = segmpos_dparams_to_action_hess
+
+    # ------------------------------------------------------------------ solver glue
+    def GetKrylovJacobian(self, Use_exact_Jacobian: bool = True, jac_options_kw: Optional[dict] = None):
+        """_NBodySyst.pyx:2004-2032: scipy KrylovJacobian whose matvec is the exact Hessian-vector product with
+        cached segment positions."""
+        try:
+            from scipy.optimize._nonlin import KrylovJacobian
+        except Exception:  # scipy < 1.14
+            from scipy.optimize.nonlin import KrylovJacobian
+        jacobian = KrylovJacobian(**(jac_options_kw or {}))
+        if Use_exact_Jacobian:
+            def matvec(jself, v):
+                return jself.NBS.segmpos_dparams_to_action_hess(jself.segmpos, v)
+
+            def update(jself, x, f):
+                jself.segmpos = jself.NBS.params_to_segmpos(x)
+                KrylovJacobian.update(jself, x, f)
+
+            def setup(jself, x, f, func):
+                jself.segmpos = jself.NBS.params_to_segmpos(x)
+                KrylovJacobian.setup(jself, x, f, func)
+
+            jacobian.matvec = types.MethodType(matvec, jacobian)
+            jacobian.rmatvec = types.MethodType(matvec, jacobian)
+            jacobian.update = types.MethodType(update, jacobian)
+            jacobian.setup = types.MethodType(setup, jacobian)
+        jacobian.NBS = self
+        return jacobian

@@ -1,0 +1,234 @@
+/*
+ * choreo_b200.h -- C ABI of libchoreo_b200.so: the B200 (sm_100a, fp64) implementation of the
+ * action-evaluation hot path of gabrielfougeron/Choreographies2 ("choreo").
+ *
+ * The reference has no FFI for this path: the seam is the set of numeric methods of the Cython
+ * class NBodySyst (choreo/cython/_NBodySyst.pyx).  Every entry point below names the reference
+ * method / cdef function it replaces (file:line in choreo/cython/_NBodySyst.pyx @ 8c8dd3f2).
+ * INTEGRATION.md shows the ctypes binding a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - all entry points are extern "C", return an int status (CHB_OK == 0) and never abort;
+ *     chb_last_error_string() describes the last failure on the calling thread;
+ *   - arrays are C-contiguous IEEE fp64; batched arrays carry a leading batch dimension:
+ *         params   [batch][nparams]                     (reference: double[::1] params_mom_buf)
+ *         segmpos  [batch][nsegm][segm_store][geodim]   (reference: double[:,:,::1] segmpos)
+ *   - "_dev" operators take DEVICE pointers and are asynchronous on the given stream
+ *     (a cudaStream_t passed as void*, NULL = default stream); workspace is caller-provided
+ *     (chb_workspace_bytes) so one plan can serve several streams;
+ *   - "_host" operators take HOST pointers, stage through plan-owned pinned/device buffers and
+ *     return when the result is in the host buffer (one call at a time per plan);
+ *   - a plan is immutable between chb_plan_set_nint calls; tables are copied at creation.
+ */
+#ifndef CHOREO_B200_H
+#define CHOREO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CHB_ABI_VERSION 1
+
+enum chb_status {
+    CHB_OK = 0,
+    CHB_ERR_INVALID_ARGUMENT = 1, /* NULL pointer, negative size, inconsistent tables            */
+    CHB_ERR_INVALID_NINT = 2,     /* nint not divisible by 2*nint_min (reference: ValueError, :545) */
+    CHB_ERR_UNSUPPORTED = 3,      /* custom inter_law, geodim > 4, FFT length with a prime factor > 31 ... */
+    CHB_ERR_CUDA = 4,             /* a CUDA runtime call failed (message has the CUDA error string)   */
+    CHB_ERR_NO_DEVICE = 5,        /* no CUDA device / wrong architecture: there is NO CPU fallback    */
+    CHB_ERR_WORKSPACE = 6,        /* workspace too small / NULL                                       */
+    CHB_ERR_NOT_READY = 7         /* chb_plan_set_nint has not been called                            */
+};
+
+enum chb_inter_law {
+    CHB_LAW_GRAVITY = 0, /* gravity_pot,   _NBodySyst.pyx:111-123 */
+    CHB_LAW_POWER = 1    /* power_law_pot, _NBodySyst.pyx:125-133 */
+};
+
+enum chb_shortcut {
+    CHB_GENERAL_SYM = 0, /* _NBodySyst.pyx:94 */
+    CHB_RFFT = 1         /* _NBodySyst.pyx:95 */
+};
+
+/*
+ * Flat symmetry tables = the NBodySyst fields the hot path reads (_NBodySyst.pyx:293-494, 729-737);
+ * see choreographies2_b200/tables.py:extract_tables for how each is read from a live NBodySyst.
+ * All pointers are HOST pointers; integer tables are int64 (Py_ssize_t) or int32 (bint / intc).
+ */
+typedef struct chb_tables {
+    int32_t geodim;         /* NBodySyst.geodim                               */
+    int32_t nbody;          /* NBodySyst.nbody                                */
+    int32_t nloop;          /* NBodySyst.nloop                                */
+    int32_t nsegm;          /* NBodySyst.nsegm                                */
+    int32_t nbin;           /* NBodySyst.nbin_segm_unique                     */
+    int32_t nint_min;       /* NBodySyst.nint_min                             */
+    int32_t greater_nstore; /* NBodySyst.GreaterNStore (segm_store = segm_size + 1) */
+    int32_t inter_law;      /* enum chb_inter_law                             */
+    double inter_law_params[4]; /* (-nu, -nu(nu-1), nu-2, alpha), :1623-1629; gravity = (0.5,-0.75,-2.5,1) */
+    /* per loop [nloop] */
+    const int64_t *loopnb;     /* _loopnb        */
+    const double *loopmass;    /* _loopmass      */
+    const int64_t *ncoeff_min; /* _ncoeff_min_loop */
+    const int64_t *n_sub_fft;  /* _n_sub_fft     */
+    const int32_t *shortcut;   /* _ParamBasisShortcutPos */
+    const int64_t *nnz;        /* _nnz_k_shapes[il,0]   */
+    const int64_t *nppl;       /* _params_basis_shapes[il,2] */
+    const int64_t *nnz_k;        /* _nnz_k_buf (flat)            */
+    const int64_t *nnz_k_shifts; /* [nloop+1]                    */
+    const int32_t *co_in;        /* _co_in_buf (flat)            */
+    const int64_t *co_in_shifts; /* [nloop+1]                    */
+    const double *params_basis;         /* _params_basis_buf_pos as interleaved (re,im), per loop C-order (geodim,nnz,nppl) */
+    const int64_t *params_basis_shifts; /* [nloop+1], in complex elements */
+    const int64_t *alg_iint;    /* _ALG_Iint      */
+    const int64_t *alg_timerev; /* _ALG_TimeRev   */
+    const double *alg_spacerot; /* _ALG_SpaceRotPos [nloop][geodim][geodim] */
+    /* per body [nbody] */
+    const int64_t *bodyloop; /* _bodyloop */
+    /* per generating segment [nsegm] */
+    const int64_t *gensegm_to_body;      /* _gensegm_to_body    */
+    const int64_t *gensegm_to_iintrel;   /* _gensegm_to_iintrel */
+    const int64_t *inter_timerev;        /* _InterTimeRev       */
+    const double *inter_spacerot;        /* _InterSpaceRotPos [nsegm][geodim][geodim] */
+    const int32_t *inter_spacerot_isid;  /* _InterSpaceRotPosIsId */
+    /* per binary interaction [nbin] */
+    const int64_t *bin_source;          /* _BinSourceSegm     */
+    const int64_t *bin_target;          /* _BinTargetSegm     */
+    const double *bin_spacerot;         /* _BinSpaceRot [nbin][geodim][geodim] */
+    const int32_t *bin_spacerot_isid;   /* _BinSpaceRotIsId   */
+    const double *bin_prodchargesum;    /* _BinProdChargeSum (already divided by nint_min, :818) */
+} chb_tables;
+
+typedef struct chb_plan chb_plan;
+
+enum chb_query {
+    CHB_Q_NINT = 0,
+    CHB_Q_NPARAMS = 1,    /* NBodySyst.nparams    */
+    CHB_Q_SEGM_SIZE = 2,  /* NBodySyst.segm_size  */
+    CHB_Q_SEGM_STORE = 3, /* NBodySyst.segm_store */
+    CHB_Q_NSEGM = 4,
+    CHB_Q_GEODIM = 5,
+    CHB_Q_NLOOP = 6,
+    CHB_Q_NBIN = 7,
+    CHB_Q_DEVICE = 8,
+    CHB_Q_CHUNK = 9,          /* states processed per internal launch group             */
+    CHB_Q_LAUNCHES = 10,      /* kernels launched by this plan since creation (counter)  */
+    CHB_Q_FUSED = 11,         /* 1 if the fused single-kernel action+grad path is active */
+    CHB_Q_SEGMPOS_SIZE = 12   /* nsegm*segm_store*geodim                                 */
+};
+
+int chb_abi_version(void);
+const char *chb_last_error_string(void);
+/* number of visible CUDA devices with compute capability 10.x; 0 => every plan call fails (no CPU path) */
+int chb_device_count(void);
+
+/* NBodySyst.__init__ (tables) ; nint setter :540-590 (shapes, buffers, FFT plans) ; __dealloc__ */
+int chb_plan_create(const chb_tables *tables, int device, chb_plan **plan_out);
+int chb_plan_set_nint(chb_plan *plan, int64_t nint);
+int chb_plan_destroy(chb_plan *plan);
+int chb_plan_query(const chb_plan *plan, int what, int64_t *value_out);
+/* 0 = auto; otherwise number of states per internal launch group (L2 residency knob) */
+int chb_plan_set_chunk(chb_plan *plan, int64_t chunk);
+/* 0 = generic staged kernels only, 1 = allow the fused kernel when the layout supports it (default) */
+int chb_plan_set_fused(chb_plan *plan, int enable);
+
+/* bytes of device workspace any *_dev operator below needs for `batch` states */
+int chb_workspace_bytes(const chb_plan *plan, int64_t batch, size_t *bytes_out);
+
+/* ---- device-pointer operators (asynchronous on `stream`) -------------------------------------- */
+
+/* params_to_segmpos, :3607-3635 / cdef :5979-6047 */
+int chb_params_to_segmpos_dev(chb_plan *plan, int64_t batch, const double *params, double *segmpos,
+                              void *workspace, size_t workspace_bytes, void *stream);
+/* segmpos_to_params, :3669-3696 / cdef :6121-6176 */
+int chb_segmpos_to_params_dev(chb_plan *plan, int64_t batch, const double *segmpos, double *params,
+                              void *workspace, size_t workspace_bytes, void *stream);
+/* segmpos_to_params_T, :3699-3727 / cdef :6179-6251 */
+int chb_segmpos_to_params_T_dev(chb_plan *plan, int64_t batch, const double *segmpos, double *params,
+                                void *workspace, size_t workspace_bytes, void *stream);
+/* params_to_kin_nrg, :2519-2528 / cdef :4918-4944 ; kin[batch] */
+int chb_params_to_kin_nrg_dev(chb_plan *plan, int64_t batch, const double *params, double *kin,
+                              void *workspace, size_t workspace_bytes, void *stream);
+/* segm_pos_to_pot_nrg, cdef :6372-6469 ; pot[batch] */
+int chb_segmpos_to_pot_nrg_dev(chb_plan *plan, int64_t batch, const double *segmpos, double *pot,
+                               void *workspace, size_t workspace_bytes, void *stream);
+/* segm_pos_to_pot_nrg_grad, cdef :6472-6533 ; grad_segmpos is overwritten (reference accumulates into a zeroed buffer) */
+int chb_segmpos_to_pot_nrg_grad_dev(chb_plan *plan, int64_t batch, const double *segmpos, double globalmul,
+                                    double *grad_segmpos, void *workspace, size_t workspace_bytes, void *stream);
+/* segm_pos_to_pot_nrg_hess, cdef :6899-6962 */
+int chb_segmpos_to_pot_nrg_hess_dev(chb_plan *plan, int64_t batch, const double *segmpos, const double *dsegmpos,
+                                    double globalmul, double *hess_segmpos, void *workspace, size_t workspace_bytes,
+                                    void *stream);
+/* params_to_action, :2750-2791 ; action[batch] */
+int chb_params_to_action_dev(chb_plan *plan, int64_t batch, const double *params, double *action,
+                             void *workspace, size_t workspace_bytes, void *stream);
+/* params_to_action_grad, :2794-2873, fused with params_to_action: action (may be NULL) and grad in one pass.
+ * segmpos_out (may be NULL) receives params_to_segmpos(params) as a by-product (what
+ * GetKrylovJacobian.update caches, :2013-2015). */
+int chb_params_to_action_grad_dev(chb_plan *plan, int64_t batch, const double *params, double *action,
+                                  double *grad, double *segmpos_out, void *workspace, size_t workspace_bytes,
+                                  void *stream);
+/* params_to_action_hess, :2876-2965 */
+int chb_params_to_action_hess_dev(chb_plan *plan, int64_t batch, const double *params, const double *dparams,
+                                  double *hess, void *workspace, size_t workspace_bytes, void *stream);
+/* segmpos_params_to_action, :2968-2991 */
+int chb_segmpos_params_to_action_dev(chb_plan *plan, int64_t batch, const double *segmpos, const double *params,
+                                     double *action, void *workspace, size_t workspace_bytes, void *stream);
+/* segmpos_params_to_action_grad, :2994-3041 (action may be NULL) */
+int chb_segmpos_params_to_action_grad_dev(chb_plan *plan, int64_t batch, const double *segmpos,
+                                          const double *params, double *action, double *grad, void *workspace,
+                                          size_t workspace_bytes, void *stream);
+/* segmpos_dparams_to_action_hess, :3044-3110 (the Krylov matvec, :2010-2011) */
+int chb_segmpos_dparams_to_action_hess_dev(chb_plan *plan, int64_t batch, const double *segmpos,
+                                           const double *dparams, double *hess, void *workspace,
+                                           size_t workspace_bytes, void *stream);
+
+/* ---- host-pointer operators: H2D copy + operator + D2H copy, synchronous ------------------------ */
+/* which: one of the CHB_OP_* codes; unused pointers may be NULL.  in0/in1 -> out0/out1:
+ *   CHB_OP_PARAMS_TO_SEGMPOS       in0=params            out0=segmpos
+ *   CHB_OP_SEGMPOS_TO_PARAMS       in0=segmpos           out0=params
+ *   CHB_OP_SEGMPOS_TO_PARAMS_T     in0=segmpos           out0=params
+ *   CHB_OP_ACTION                  in0=params            out0=action
+ *   CHB_OP_ACTION_GRAD             in0=params            out0=action (or NULL) out1=grad
+ *   CHB_OP_ACTION_HESS             in0=params in1=dparams out0=hess
+ *   CHB_OP_SEGMPOS_ACTION          in0=segmpos in1=params out0=action
+ *   CHB_OP_SEGMPOS_ACTION_GRAD     in0=segmpos in1=params out0=action (or NULL) out1=grad
+ *   CHB_OP_SEGMPOS_ACTION_HESS     in0=segmpos in1=dparams out0=hess
+ *   CHB_OP_KIN                     in0=params            out0=kin
+ *   CHB_OP_POT                     in0=segmpos           out0=pot
+ *   CHB_OP_POT_GRAD                in0=segmpos           out0=grad_segmpos   (scalar = globalmul)
+ *   CHB_OP_POT_HESS                in0=segmpos in1=dsegmpos out0=hess_segmpos (scalar = globalmul)
+ */
+enum chb_op {
+    CHB_OP_PARAMS_TO_SEGMPOS = 0,
+    CHB_OP_SEGMPOS_TO_PARAMS = 1,
+    CHB_OP_SEGMPOS_TO_PARAMS_T = 2,
+    CHB_OP_ACTION = 3,
+    CHB_OP_ACTION_GRAD = 4,
+    CHB_OP_ACTION_HESS = 5,
+    CHB_OP_SEGMPOS_ACTION = 6,
+    CHB_OP_SEGMPOS_ACTION_GRAD = 7,
+    CHB_OP_SEGMPOS_ACTION_HESS = 8,
+    CHB_OP_KIN = 9,
+    CHB_OP_POT = 10,
+    CHB_OP_POT_GRAD = 11,
+    CHB_OP_POT_HESS = 12
+};
+int chb_run_host(chb_plan *plan, int op, int64_t batch, const double *in0, const double *in1, double scalar,
+                 double *out0, double *out1);
+
+/* ---- memory helpers so a NumPy-only caller needs no CUDA binding ---------------------------------- */
+int chb_malloc_device(chb_plan *plan, size_t bytes, void **ptr_out);
+int chb_free_device(chb_plan *plan, void *ptr);
+int chb_malloc_pinned(size_t bytes, void **ptr_out);
+int chb_free_pinned(void *ptr);
+int chb_memcpy_h2d(chb_plan *plan, void *dst_dev, const void *src_host, size_t bytes, void *stream);
+int chb_memcpy_d2h(chb_plan *plan, void *dst_host, const void *src_dev, size_t bytes, void *stream);
+int chb_stream_synchronize(chb_plan *plan, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CHOREO_B200_H */
