@@ -585,7 +585,6 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
         maxM = std::max<long long>(maxM, (long long)loops[il].nseq * loops[il].npr);
     }
     if (maxM >= 4096) p->fft_threads = 512;
-    if (maxM >= 16384) p->fft_threads = 1024;
     p->fft_smem = red_bytes + need;
     // pair kernel tile: shared arrays spos (+sdpos) + sout, thread item = (bin in round, sample)
     {
