@@ -336,7 +336,7 @@ def run_b200(args):
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "peak_source": peak_src,
-        "kernel": ("k_fused_action_grad: 1 launch per step covering the whole batch" if nbs.fused else
+        "kernel": ("k_fused<NSEG,1>: 1 launch per step, one CTA per state, whole evaluation in shared memory" if nbs.fused else
                    f"staged path: {launches_per_step} launches per step (k_fwd, k_pair<1>, k_adj, k_finish per chunk); "
                    "achieved = whole-step algorithmic bytes / whole-step time"),
         "alg_bytes_per_unit": alg_bytes_per_unit, "units_per_launch": B,

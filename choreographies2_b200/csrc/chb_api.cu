@@ -20,8 +20,8 @@
 
 #ifndef CHB_HOSTSIM
 #include <cuda_runtime.h>
-#include "chb_fused.cuh"
 #endif
+#include "chb_fused.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // errors
@@ -86,9 +86,9 @@ struct chb_plan {
     size_t stage_dev_bytes = 0;
     void *stage_pin = nullptr;
     size_t stage_pin_bytes = 0;
-#ifndef CHB_HOSTSIM
-    ChbFusedPlan fused;
-#endif
+    ChfSys fsys;            // fused path (valid when fused_active)
+    int fused_threads = 0;
+    size_t fused_smem = 0;
 };
 
 // ---- memory shims --------------------------------------------------------------------------------
@@ -352,6 +352,139 @@ struct FftCache {
     std::vector<int> fac;
 };
 
+
+// ---- fused path planning (chb_fused.cuh) ------------------------------------------------------------
+static bool chf_factorize(int N, std::vector<int> &fac) {
+    fac.clear();
+    int m = N, e2 = 0;
+    while (m % 2 == 0) { m /= 2; ++e2; }
+    while (e2 >= 4) { fac.push_back(16); e2 -= 4; }
+    if (e2 == 3) fac.push_back(8);
+    if (e2 == 2) fac.push_back(4);
+    if (e2 == 1) fac.push_back(2);
+    for (int q : {3, 5, 7})
+        while (m % q == 0) { fac.push_back(q); m /= q; }
+    return m == 1 && !fac.empty() && (int)fac.size() <= CHF_MAX_FAC;
+}
+
+// returns 1 when the fused path can serve this level (and fills p->fsys), 0 when not, <0 on error
+static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_size) {
+    const HostTables &T = p->T;
+    static_assert(sizeof(ChfSys) + sizeof(ChfArgs) <= 4000, "kernel parameter space");
+    if (T.G != 2 || T.gns || T.nloop > CHF_MAX_LOOPS || T.nsegm > CHF_MAX_SEGS || T.nsegm < 1) return 0;
+    ChfSys &F = p->fsys;
+    memset(&F, 0, sizeof(F));
+    F.nloop = T.nloop;
+    F.nseg = T.nsegm;
+    F.segm_size = segm_size;
+    F.law_kind = T.law;
+    for (int i = 0; i < 4; ++i) F.law[i] = T.law_params[i];
+    F.nparams = p->sys.nparams;
+    F.segsz = p->sys.segsz;
+    int aligned = (F.nparams % 2 == 0) ? 1 : 0;
+    int smem_cd = 0, maxN = 0;
+    std::map<int, int> first_loop_of_N;
+    for (int il = 0; il < T.nloop; ++il) {
+        const ChbLoop &L = loops[il];
+        if (L.shortcut != CHB_RFFT || L.nnz != 1 || L.nppl != 4 || L.n_sub_fft != 1 || !L.has_k0) return 0;
+        ChfLoop &FL = F.loops[il];
+        FL.N = 2 * L.npr;
+        FL.npr = L.npr;
+        if (FL.N % segm_size != 0) return 0;
+        std::vector<int> fac;
+        if (!chf_factorize(FL.N, fac)) return 0;
+        FL.nfac = (int)fac.size();
+        for (int i = 0; i < FL.nfac; ++i) FL.fac[i] = fac[i];
+        FL.swm = (FL.N % 16 == 0) ? 15 : 0;
+        FL.smem_off = smem_cd;
+        smem_cd += FL.N;
+        maxN = std::max(maxN, FL.N);
+        FL.mom_off = L.mom_off;
+        FL.nco_in = L.nco_in;
+        FL.ncm = L.ncm;
+        FL.co0 = L.co_in[0] ? L.co_prefix[0] : -1;
+        FL.co2 = L.co_in[2] ? L.co_prefix[2] : -1;
+        FL.loopmul = L.loopmul;
+        if ((L.mom_off - L.nco_in) % 2 != 0) aligned = 0;
+        // every slot of the loop must be covered by exactly one generating segment
+        std::vector<int> cover(FL.N / segm_size, 0);
+        for (int s = 0; s < T.nsegm; ++s)
+            if ((int)T.bodyloop[T.seg_body[s]] == il) {
+                if (T.seg_iintrel[s] >= (int64_t)cover.size()) return 0;
+                cover[T.seg_iintrel[s]]++;
+            }
+        for (int c : cover)
+            if (c != 1) return 0;
+    }
+    F.aligned16 = aligned;
+    for (int s = 0; s < T.nsegm; ++s) {
+        ChfSeg &sg = F.segs[s];
+        sg.loop = (int)T.bodyloop[T.seg_body[s]];
+        sg.row0 = (int)T.seg_iintrel[s] * segm_size;
+        sg.timerev = (int)T.seg_timerev[s];
+        sg.isid = T.seg_isid[s] ? 1 : 0;
+        for (int i = 0; i < 4; ++i) sg.rot[i] = T.seg_rot[(size_t)s * 4 + i];
+    }
+    for (int b = 0; b < T.nbin; ++b) {
+        ChfPair &P = F.pairs[T.bin_src[b] * CHF_MAX_SEGS + T.bin_tgt[b]];
+        if (P.on) return 0;  // two interactions on the same ordered segment pair: generic path
+        P.on = 1;
+        P.isid = T.bin_isid[b] ? 1 : 0;
+        P.fac = T.bin_fac[b];
+        for (int i = 0; i < 4; ++i) P.rot[i] = T.bin_rot[(size_t)b * 4 + i];
+    }
+    // threads: one group per loop, about one radix-16 butterfly pair per thread and pass
+    int Tg = ((maxN / 32 + 31) / 32) * 32;
+    int cap = (CHF_MAX_THREADS / T.nloop) / 32 * 32;
+    Tg = std::max(32, std::min(Tg, cap));
+    if (cap < 32) return 0;
+    F.T = Tg;
+    p->fused_threads = Tg * T.nloop;
+    p->fused_smem = CHF_RED_BYTES + (size_t)smem_cd * sizeof(cd);
+    if (p->fused_smem > p->smem_limit) return 0;
+    // tables, shared between loops of equal length
+    for (int il = 0; il < T.nloop; ++il) {
+        ChfLoop &FL = F.loops[il];
+        auto it = first_loop_of_N.find(FL.N);
+        if (it != first_loop_of_N.end()) {
+            FL.rev = F.loops[it->second].rev;
+            for (int i = 0; i < FL.nfac; ++i) FL.tw[i] = F.loops[it->second].tw[i];
+            continue;
+        }
+        first_loop_of_N[FL.N] = il;
+        const int N = FL.N;
+        std::vector<int> rev(N);
+        for (int k = 0; k < N; ++k) {
+            int kk = k, pos = 0, Lcur = N;
+            for (int i = 0; i < FL.nfac; ++i) {
+                int r = FL.fac[i];
+                int t = kk % r;
+                kk /= r;
+                Lcur /= r;
+                pos += t * Lcur;
+            }
+            rev[k] = pos;
+        }
+        int rc = level_upload(p, rev, &FL.rev);
+        if (rc) return -1;
+        int Lcur = N;
+        for (int i = 0; i < FL.nfac; ++i) {
+            const int r = FL.fac[i], Lp = Lcur / r, nb = chf_nbase(r);
+            std::vector<cd> tw((size_t)std::max(1, Lp * nb));
+            for (int j = 0; j < Lp; ++j)
+                for (int e = 0; e < nb; ++e) {
+                    double c, sn;
+                    exact_root((long long)j * (1LL << e), Lcur, &c, &sn);
+                    tw[(size_t)j * nb + e] = mk(c, sn);
+                }
+            rc = level_upload(p, tw, &FL.tw[i]);
+            if (rc) return -1;
+            Lcur = Lp;
+        }
+    }
+    return 1;
+}
+
 extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
     CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_nint: NULL plan");
     HostTables &T = p->T;
@@ -611,13 +744,12 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
     p->nint = nint;
     p->ready = true;
     p->fused_active = 0;
-#ifndef CHB_HOSTSIM
     {
-        int rcf = chb_fused_setup(p->fused, p->sys, loops, T.G, p->device, p->smem_limit, p->num_sms, p->level_allocs);
+        int rcf = fused_setup(p, loops, segm_size);
         if (rcf < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: fused setup failed"); }
         p->fused_active = rcf;
+        p->ready = true;
     }
-#endif
     return CHB_OK;
 }
 
@@ -715,10 +847,27 @@ extern "C" int chb_workspace_bytes(const chb_plan *p, int64_t batch, size_t *out
 // kernels (GPU) / block loops (hostsim)
 // ------------------------------------------------------------------------------------------------
 #ifndef CHB_HOSTSIM
+struct DevGrp {
+    int g, T;
+    // phase of one thread group: the group's own named barrier, so groups drift apart and overlap each other
+    template <class F>
+    __device__ __forceinline__ void par(F f) {
+        f((int)threadIdx.x - g * T, T);
+        asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(T) : "memory");
+    }
+};
 struct DevCtx {
     template <class F>
     __device__ __forceinline__ void par(F f) {
         f((int)threadIdx.x, (int)blockDim.x);
+        __syncthreads();
+    }
+    // blockDim.x == ngroups * T
+    template <class F>
+    __device__ __forceinline__ void groups(int ngroups, int T, F f) {
+        (void)ngroups;
+        DevGrp grp{(int)threadIdx.x / T, T};
+        f(grp);
         __syncthreads();
     }
 };
@@ -729,11 +878,25 @@ extern __shared__ __align__(16) unsigned char chb_smem_raw[];
 #define CHB_CTX_DECL DevCtx ctx
 #define CHB_SMEM chb_smem_raw
 #else
+struct HostGrp {
+    int g, T;
+    template <class F>
+    void par(F f) {
+        for (int t = 0; t < T; ++t) f(t, T);
+    }
+};
 struct HostCtx {
     int nthr;
     template <class F>
     void par(F f) {
         for (int t = 0; t < nthr; ++t) f(t, nthr);
+    }
+    template <class F>
+    void groups(int ngroups, int T, F f) {
+        for (int g = 0; g < ngroups; ++g) {
+            HostGrp grp{g, T};
+            f(grp);
+        }
     }
 };
 static thread_local long long sim_block_id;
@@ -809,6 +972,19 @@ CHB_KERNEL void k_finish(double *out, const double *kin_part, int nk, const doub
         if (b < nstates) out[b] = chb_finish_action(kin_part + b * nk, kin_part ? nk : 0, pot_part + b * np, pot_part ? np : 0, psign);
     }
 #endif
+}
+
+
+// one CTA per state: the whole evaluation in shared memory (chb_fused.cuh)
+#ifndef CHB_HOSTSIM
+#define CHF_BOUNDS __launch_bounds__(CHF_MAX_THREADS, 1)
+#else
+#define CHF_BOUNDS
+#endif
+template <int NSEG, int PMODE>
+CHB_KERNEL void CHF_BOUNDS k_fused(ChfSys F, ChfArgs A) {
+    CHB_CTX_DECL;
+    cta_fused<NSEG, PMODE>(ctx, F, A, CHB_BLOCK_ID, (double *)CHB_SMEM, (cd *)(CHB_SMEM + CHF_RED_BYTES));
 }
 
 #ifndef CHB_HOSTSIM
@@ -900,6 +1076,36 @@ static int launch_kin(chb_plan *p, int64_t nb, const double *params, double *kin
     CHB_LAUNCH(p, k_kin, nb, 256, sizeof(double) * 256, st, p->sys, params, kin_out, stride);
     return CHB_OK;
 }
+
+template <int NSEG>
+static int launch_fused_n(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A, chb_stream_t st) {
+    switch (pmode) {
+        case 0: CHB_LAUNCH(p, (k_fused<NSEG, 0>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A); break;
+        case 1: CHB_LAUNCH(p, (k_fused<NSEG, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A); break;
+        case 2: CHB_LAUNCH(p, (k_fused<NSEG, 2>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A); break;
+        default: CHB_LAUNCH(p, (k_fused<NSEG, 3>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A); break;
+    }
+    return CHB_OK;
+}
+// pmode: 0 energy, 1 energy + gradient, 2 Hessian-vector, 3 segment positions only
+static int launch_fused(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A, chb_stream_t st) {
+    switch (p->fsys.nseg) {
+        case 1: return launch_fused_n<1>(p, pmode, nb, A, st);
+        case 2: return launch_fused_n<2>(p, pmode, nb, A, st);
+        case 3: return launch_fused_n<3>(p, pmode, nb, A, st);
+        case 4: return launch_fused_n<4>(p, pmode, nb, A, st);
+        case 5: return launch_fused_n<5>(p, pmode, nb, A, st);
+        default: return launch_fused_n<6>(p, pmode, nb, A, st);
+    }
+}
+static bool use_fused(const chb_plan *p) { return p->fused_enabled && p->fused_active; }
+static ChfArgs chf_args(const double *vec_in, const double *kin_src, const double *seg_in, double *seg_out,
+                        double *vec_out, double *scalar_out, int kin_from) {
+    ChfArgs A;
+    A.vec_in = vec_in; A.kin_src = kin_src; A.seg_in = seg_in; A.seg_out = seg_out; A.vec_out = vec_out;
+    A.scalar_out = scalar_out; A.kin_from = kin_from;
+    return A;
+}
 #define CHB_TRY(x)          \
     do {                    \
         int rc_ = (x);      \
@@ -911,6 +1117,7 @@ extern "C" int chb_params_to_segmpos_dev(chb_plan *p, int64_t batch, const doubl
     CHB_OP_PROLOGUE("chb_params_to_segmpos_dev");
     CHB_REQUIRE(params && segmpos, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_segmpos_dev: NULL array");
     CHB_SET_DEVICE();
+    if (use_fused(p)) return launch_fused(p, 3, batch, chf_args(params, nullptr, nullptr, segmpos, nullptr, nullptr, 0), st);
     for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
         int64_t nb = std::min(chunk, batch - c0);
         CHB_TRY(launch_fwd(p, nb, params + c0 * S.nparams, segmpos + c0 * S.segsz, W, false, mask, st));
@@ -991,6 +1198,7 @@ extern "C" int chb_params_to_action_dev(chb_plan *p, int64_t batch, const double
     CHB_OP_PROLOGUE("chb_params_to_action_dev");
     CHB_REQUIRE(params && action, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_action_dev: NULL array");
     CHB_SET_DEVICE();
+    if (use_fused(p)) return launch_fused(p, 0, batch, chf_args(params, nullptr, nullptr, nullptr, nullptr, action, 1), st);
     for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
         int64_t nb = std::min(chunk, batch - c0);
         CHB_TRY(launch_fwd(p, nb, params + c0 * S.nparams, W.segA, W, true, mask, st));
@@ -1005,14 +1213,8 @@ extern "C" int chb_params_to_action_grad_dev(chb_plan *p, int64_t batch, const d
     CHB_OP_PROLOGUE("chb_params_to_action_grad_dev");
     CHB_REQUIRE(params && grad, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_action_grad_dev: NULL array");
     CHB_SET_DEVICE();
-#ifndef CHB_HOSTSIM
-    if (p->fused_enabled && p->fused_active && !segmpos_out) {
-        int rcf = chb_fused_action_grad(p->fused, p->sys, batch, params, action, grad, st);
-        if (rcf != 0) return chb_fail(CHB_ERR_CUDA, "chb_params_to_action_grad_dev: fused kernel launch failed");
-        p->launches += 1;
-        return CHB_OK;
-    }
-#endif
+    if (use_fused(p))
+        return launch_fused(p, 1, batch, chf_args(params, params, nullptr, segmpos_out, grad, action, action ? 1 : 0), st);
     for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
         int64_t nb = std::min(chunk, batch - c0);
         double *seg = segmpos_out ? segmpos_out + c0 * S.segsz : W.segA;
@@ -1029,6 +1231,15 @@ extern "C" int chb_params_to_action_hess_dev(chb_plan *p, int64_t batch, const d
     CHB_OP_PROLOGUE("chb_params_to_action_hess_dev");
     CHB_REQUIRE(params && dparams && hess, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_action_hess_dev: NULL array");
     CHB_SET_DEVICE();
+    if (use_fused(p)) {  // two forward transforms do not fit one CTA: segment positions go through the workspace
+        for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+            int64_t nb = std::min(chunk, batch - c0);
+            CHB_TRY(launch_fused(p, 3, nb, chf_args(params + c0 * S.nparams, nullptr, nullptr, W.segA, nullptr, nullptr, 0), st));
+            CHB_TRY(launch_fused(p, 2, nb, chf_args(dparams + c0 * S.nparams, dparams + c0 * S.nparams, W.segA, nullptr,
+                                                    hess + c0 * S.nparams, nullptr, 0), st));
+        }
+        return CHB_OK;
+    }
     for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
         int64_t nb = std::min(chunk, batch - c0);
         CHB_TRY(launch_fwd(p, nb, params + c0 * S.nparams, W.segA, W, false, mask, st));
@@ -1060,6 +1271,8 @@ extern "C" int chb_segmpos_params_to_action_grad_dev(chb_plan *p, int64_t batch,
     CHB_REQUIRE(segmpos && params && grad, CHB_ERR_INVALID_ARGUMENT,
                 "chb_segmpos_params_to_action_grad_dev: NULL array");
     CHB_SET_DEVICE();
+    if (use_fused(p))
+        return launch_fused(p, 1, batch, chf_args(nullptr, params, segmpos, nullptr, grad, action, action ? 2 : 0), st);
     for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
         int64_t nb = std::min(chunk, batch - c0);
         if (action) CHB_TRY(launch_kin(p, nb, params + c0 * S.nparams, W.kin_part, 1, st));
@@ -1077,6 +1290,8 @@ extern "C" int chb_segmpos_dparams_to_action_hess_dev(chb_plan *p, int64_t batch
     CHB_REQUIRE(segmpos && dparams && hess, CHB_ERR_INVALID_ARGUMENT,
                 "chb_segmpos_dparams_to_action_hess_dev: NULL array");
     CHB_SET_DEVICE();
+    if (use_fused(p))
+        return launch_fused(p, 2, batch, chf_args(dparams, dparams, segmpos, nullptr, hess, nullptr, 0), st);
     for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
         int64_t nb = std::min(chunk, batch - c0);
         CHB_TRY(launch_fwd(p, nb, dparams + c0 * S.nparams, W.segB, W, false, mask, st));

@@ -1,21 +1,511 @@
-// chb_fused.cuh -- placeholder interface of the fused action+gradient kernel (filled in later).
+// chb_fused.cuh -- the fused one-CTA-per-state path for planar systems whose loops all use the RFFT shortcut.
+//
+// One CTA owns one state.  Every loop's sampled path lives in shared memory as ONE complex sequence
+// z[n] = x[n] + i y[n] (geodim == 2, so a segment position IS a complex number), which turns the reference's
+// "c2r of length 2*npr, howmany geodim" (params_to_pos_slice, _NBodySyst.pyx:5463-5506) into a single in-place complex
+// FFT of length N = 2*npr whose spectrum is Z[k] = X0[k] + i X1[k], Z[N-k] = conj(X0[k]) + i conj(X1[k]).
+// The pair interactions (segm_pos_to_pot_nrg_grad / _hess, :6472-6533, :6899-6962) then run IN PLACE on the same
+// buffers (one thread per time sample reads every segment's position and overwrites it with the segment gradient),
+// and the adjoint transform (segmpos_to_params_T, :6179-6251) is the forward complex FFT of the same buffers followed
+// by a Hermitian split.  Parameters are read from HBM once, the result is written once; segment positions, segment
+// gradients and all FFT passes never leave the SM.
+//
+// Work split inside the CTA: one thread GROUP per loop (named barrier per group) for the load / FFT / store phases,
+// so the loops' memory phases and FFT passes overlap instead of draining the whole SM at every pass; the pair phase
+// uses all threads.  FFT passes are register butterflies of radix 16/8/4/2/3/5/7 on a XOR-swizzled buffer
+// (conflict-free for every power-of-two stride); per-pass twiddles come from a compact table of base powers
+// (w, w^2, w^4, w^8), the other powers are products.
+//
+// Like chb_core.cuh this header is written as CTA programs over a context (ctx.par / ctx.groups) so that the
+// GPU-less build container can run the very same index arithmetic under tests/hostsim; the product is the nvcc build.
 #pragma once
-#include <vector>
 #include "chb_core.cuh"
 
-struct ChbFusedPlan {
-    int active = 0;
+#define CHF_MAX_LOOPS 6
+#define CHF_MAX_SEGS 6
+#define CHF_MAX_FAC 8
+#define CHF_MAX_THREADS 384
+#define CHF_RED_BYTES 4096  // CHF_MAX_THREADS doubles, rounded up
+
+struct ChfLoop {
+    int N, npr, nfac, smem_off;  // smem_off in cd slots
+    int swm;                     // swizzle mask (15 when N % 16 == 0, else 0)
+    int nco_in;                  // zero-frequency parameters removed from the parameter vector
+    int ncm;                     // ncoeff_min: row k of the loop is harmonic k * ncm
+    int co0, co2;                // index (relative to mom_off) of the DC parameters of x and y, or -1 when removed
+    int fac[CHF_MAX_FAC];        // DIF radices, product N
+    const int *rev;              // [N] slot of spectral index k after the DIF passes
+    const cd *tw[CHF_MAX_FAC];   // DIF stage s: base twiddles exp(-2 pi i j 2^e / L_s), [Lp_s][nbase(r_s)]
+    long long mom_off;
+    double loopmul;  // 1/sqrt(loopnb*loopmass*4pi^2)
+};
+struct ChfSeg {
+    int loop, row0, timerev, isid;
+    double rot[4];
+};
+struct ChfPair {
+    int on, isid;
+    double fac;
+    double rot[4];
+};
+struct ChfSys {
+    int nloop, nseg, T, segm_size;
+    int aligned16, law_kind;
+    long long nparams, segsz;
+    double law[4];
+    ChfLoop loops[CHF_MAX_LOOPS];
+    ChfSeg segs[CHF_MAX_SEGS];
+    ChfPair pairs[CHF_MAX_SEGS * CHF_MAX_SEGS];  // [src * CHF_MAX_SEGS + tgt]
+};
+struct ChfArgs {
+    const double *vec_in;   // [B][nparams] vector sent through the forward transform (params / dparams), or NULL
+    const double *kin_src;  // [B][nparams] added to the adjoint result on k>0 entries (kinetic gradient / Hessian), or NULL
+    const double *seg_in;   // [B][segsz]  cached segment positions used as x in the pair phase, or NULL
+    double *seg_out;        // [B][segsz]  optional by-product: params_to_segmpos(vec_in)
+    double *vec_out;        // [B][nparams] adjoint result (gradient / Hessian-vector), or NULL
+    double *scalar_out;     // [B] kinetic - potential, or NULL
+    int kin_from;           // 0 none, 1 kinetic energy from vec_in (load phase), 2 from kin_src (store phase)
 };
 
-// returns 1 if the fused kernel can serve this level, 0 if not, <0 on CUDA error
-static inline int chb_fused_setup(ChbFusedPlan &F, const ChbSys &S, const std::vector<ChbLoop> &loops, int G, int device,
-                                  size_t smem_limit, int num_sms, std::vector<void *> &level_allocs) {
-    (void)S; (void)loops; (void)G; (void)device; (void)smem_limit; (void)num_sms; (void)level_allocs;
-    F.active = 0;
-    return 0;
+CHB_HD int chf_swz(int i, int m) { return i ^ ((i >> 4) & m); }
+CHB_HD int chf_nbase(int r) { return r == 2 ? 1 : (r <= 4 ? 2 : (r <= 8 ? 3 : 4)); }
+
+// ------------------------------------------------------------------------------------------------
+// register butterflies: y_t = sum_q a_q exp(SIGN 2 pi i q t / R), natural order in and out
+// ------------------------------------------------------------------------------------------------
+template <int SIGN>
+CHB_HD cd chf_muli(cd a) { return SIGN > 0 ? mk(-a.y, a.x) : mk(a.y, -a.x); }
+// a * (c + i SIGN s)
+template <int SIGN>
+CHB_HD cd chf_mulcs(cd a, double c, double s) {
+    return SIGN > 0 ? mk(a.x * c - a.y * s, a.x * s + a.y * c) : mk(a.x * c + a.y * s, a.y * c - a.x * s);
 }
-static inline int chb_fused_action_grad(ChbFusedPlan &F, const ChbSys &S, int64_t batch, const double *params,
-                                        double *action, double *grad, cudaStream_t st) {
-    (void)F; (void)S; (void)batch; (void)params; (void)action; (void)grad; (void)st;
-    return -1;
+template <int SIGN>
+CHB_HD void chf_dft2(cd &a0, cd &a1) {
+    cd t = a0;
+    a0 = cadd(t, a1);
+    a1 = csub(t, a1);
+}
+template <int SIGN>
+CHB_HD void chf_dft4(cd &a0, cd &a1, cd &a2, cd &a3) {
+    cd t0 = cadd(a0, a2), t1 = csub(a0, a2), t2 = cadd(a1, a3), t3 = chf_muli<SIGN>(csub(a1, a3));
+    a0 = cadd(t0, t2);
+    a1 = cadd(t1, t3);
+    a2 = csub(t0, t2);
+    a3 = csub(t1, t3);
+}
+#define CHF_H 0.70710678118654752440
+#define CHF_C1 0.92387953251128673848
+#define CHF_S1 0.38268343236508978178
+
+template <int R, int SIGN>
+struct ChfDft;
+template <int SIGN>
+struct ChfDft<2, SIGN> {
+    static CHB_HD void run(cd *a) { chf_dft2<SIGN>(a[0], a[1]); }
+};
+template <int SIGN>
+struct ChfDft<4, SIGN> {
+    static CHB_HD void run(cd *a) { chf_dft4<SIGN>(a[0], a[1], a[2], a[3]); }
+};
+template <int SIGN>
+struct ChfDft<8, SIGN> {
+    // q = q0 + 2 q1, t = t1 + 4 t0 : w8^(q t) = w8^(q0 t1) w2^(q0 t0) w4^(q1 t1)
+    static CHB_HD void run(cd *a) {
+        chf_dft4<SIGN>(a[0], a[2], a[4], a[6]);  // u[0][t1] in a[2 t1]
+        chf_dft4<SIGN>(a[1], a[3], a[5], a[7]);  // u[1][t1] in a[1 + 2 t1]
+        a[3] = chf_mulcs<SIGN>(a[3], CHF_H, CHF_H);
+        a[5] = chf_muli<SIGN>(a[5]);
+        a[7] = chf_mulcs<SIGN>(a[7], -CHF_H, CHF_H);
+        cd y[8];
+#pragma unroll
+        for (int t1 = 0; t1 < 4; ++t1) {
+            y[t1] = cadd(a[2 * t1], a[2 * t1 + 1]);
+            y[t1 + 4] = csub(a[2 * t1], a[2 * t1 + 1]);
+        }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) a[t] = y[t];
+    }
+};
+template <int SIGN>
+struct ChfDft<16, SIGN> {
+    // q = q0 + 4 q1, t = t1 + 4 t0 : w16^(q t) = w16^(q0 t1) w4^(q0 t0) w4^(q1 t1)
+    static CHB_HD void run(cd *a) {
+#pragma unroll
+        for (int q0 = 0; q0 < 4; ++q0) chf_dft4<SIGN>(a[q0], a[q0 + 4], a[q0 + 8], a[q0 + 12]);  // u[q0][t1] in a[q0 + 4 t1]
+        a[1 + 4] = chf_mulcs<SIGN>(a[1 + 4], CHF_C1, CHF_S1);    // w16^1
+        a[1 + 8] = chf_mulcs<SIGN>(a[1 + 8], CHF_H, CHF_H);      // w16^2
+        a[1 + 12] = chf_mulcs<SIGN>(a[1 + 12], CHF_S1, CHF_C1);  // w16^3
+        a[2 + 4] = chf_mulcs<SIGN>(a[2 + 4], CHF_H, CHF_H);      // w16^2
+        a[2 + 8] = chf_muli<SIGN>(a[2 + 8]);                     // w16^4
+        a[2 + 12] = chf_mulcs<SIGN>(a[2 + 12], -CHF_H, CHF_H);   // w16^6
+        a[3 + 4] = chf_mulcs<SIGN>(a[3 + 4], CHF_S1, CHF_C1);    // w16^3
+        a[3 + 8] = chf_mulcs<SIGN>(a[3 + 8], -CHF_H, CHF_H);     // w16^6
+        a[3 + 12] = chf_mulcs<SIGN>(a[3 + 12], -CHF_C1, -CHF_S1);  // w16^9
+#pragma unroll
+        for (int t1 = 0; t1 < 4; ++t1) chf_dft4<SIGN>(a[4 * t1], a[4 * t1 + 1], a[4 * t1 + 2], a[4 * t1 + 3]);  // y[t1+4 t0] in a[t0+4 t1]
+        cd y[16];
+#pragma unroll
+        for (int t1 = 0; t1 < 4; ++t1)
+#pragma unroll
+            for (int t0 = 0; t0 < 4; ++t0) y[t1 + 4 * t0] = a[t0 + 4 * t1];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) a[t] = y[t];
+    }
+};
+// cos / sin of 2 pi m / R for the odd radices
+CHB_HD constexpr double chf_cosR(int R, int m) {
+    return R == 3 ? (m == 0 ? 1.0 : -0.5)
+         : R == 5 ? (m == 0 ? 1.0 : ((m == 1 || m == 4) ? 0.30901699437494742410 : -0.80901699437494742410))
+                  : (m == 0 ? 1.0 : ((m == 1 || m == 6) ? 0.62348980185873353053
+                                   : ((m == 2 || m == 5) ? -0.22252093395631440429 : -0.90096886790241912624)));
+}
+CHB_HD constexpr double chf_sinR(int R, int m) {
+    return R == 3 ? (m == 0 ? 0.0 : (m == 1 ? 0.86602540378443864676 : -0.86602540378443864676))
+         : R == 5 ? (m == 0 ? 0.0 : (m == 1 ? 0.95105651629515357212 : (m == 2 ? 0.58778525229247312917
+                                   : (m == 3 ? -0.58778525229247312917 : -0.95105651629515357212))))
+                  : (m == 0 ? 0.0 : (m == 1 ? 0.78183148246802980871 : (m == 2 ? 0.97492791218182360702
+                                   : (m == 3 ? 0.43388373911755812048 : (m == 4 ? -0.43388373911755812048
+                                   : (m == 5 ? -0.97492791218182360702 : -0.78183148246802980871))))));
+}
+template <int R, int SIGN>
+struct ChfDftOdd {
+    static CHB_HD void run(cd *a) {
+        constexpr int H = (R - 1) / 2;
+        cd t[H + 1], d[H + 1], y[R];
+        y[0] = a[0];
+#pragma unroll
+        for (int p = 1; p <= H; ++p) {
+            t[p] = cadd(a[p], a[R - p]);
+            d[p] = csub(a[p], a[R - p]);
+            y[0] = cadd(y[0], t[p]);
+        }
+#pragma unroll
+        for (int k = 1; k <= H; ++k) {
+            cd m = a[0], n = mk(0.0, 0.0);
+#pragma unroll
+            for (int p = 1; p <= H; ++p) {
+                const double c = chf_cosR(R, (k * p) % R), s = chf_sinR(R, (k * p) % R);
+                m.x += c * t[p].x;
+                m.y += c * t[p].y;
+                n.x += s * d[p].x;
+                n.y += s * d[p].y;
+            }
+            n = chf_muli<SIGN>(n);
+            y[k] = cadd(m, n);
+            y[R - k] = csub(m, n);
+        }
+#pragma unroll
+        for (int k = 0; k < R; ++k) a[k] = y[k];
+    }
+};
+template <int SIGN>
+struct ChfDft<3, SIGN> : ChfDftOdd<3, SIGN> {};
+template <int SIGN>
+struct ChfDft<5, SIGN> : ChfDftOdd<5, SIGN> {};
+template <int SIGN>
+struct ChfDft<7, SIGN> : ChfDftOdd<7, SIGN> {};
+
+// a[t] *= w^t for t = 1..R-1, w^(2^e) read from the base table (conjugated for SIGN > 0)
+template <int R, int SIGN>
+CHB_HD void chf_twiddle(cd *a, const cd *base) {
+    cd w[R];
+#pragma unroll
+    for (int e = 0; (1 << e) < R; ++e) {
+        cd v = base[e];
+        if (SIGN > 0) v.y = -v.y;
+        w[1 << e] = v;
+    }
+#pragma unroll
+    for (int t = 1; t < R; ++t) {
+        if ((t & (t - 1)) != 0) {  // not a power of two: product of the top bit and the rest
+            int hb = 1;
+            while (hb * 2 <= t) hb *= 2;
+            w[t] = cmul(w[hb], w[t - hb]);
+        }
+        a[t] = cmul(a[t], w[t]);
+    }
+}
+
+// one pass over the N/R butterflies of a stage with current length L (DIF: twiddle the outputs, DIT: the inputs)
+template <int R, int SIGN, bool DIT, class Grp>
+CHB_D void chf_pass(Grp &grp, cd *buf, int swm, int N, int L, const cd *tw) {
+    const int Lp = L / R, nbf = N / R;
+    grp.par([&](int tid, int T) {
+        for (int b = tid; b < nbf; b += T) {
+            const int blk = b / Lp, j = b - blk * Lp;
+            const int base = blk * L + j;
+            cd a[R];
+#pragma unroll
+            for (int q = 0; q < R; ++q) a[q] = buf[chf_swz(base + q * Lp, swm)];
+            if (DIT && Lp > 1) chf_twiddle<R, SIGN>(a, tw + (long long)j * chf_nbase(R));
+            ChfDft<R, SIGN>::run(a);
+            if (!DIT && Lp > 1) chf_twiddle<R, SIGN>(a, tw + (long long)j * chf_nbase(R));
+#pragma unroll
+            for (int t = 0; t < R; ++t) buf[chf_swz(base + t * Lp, swm)] = a[t];
+        }
+    });
+}
+template <int SIGN, bool DIT, class Grp>
+CHB_D void chf_pass_r(Grp &grp, cd *buf, int swm, int N, int L, int r, const cd *tw) {
+    switch (r) {
+        case 16: chf_pass<16, SIGN, DIT>(grp, buf, swm, N, L, tw); break;
+        case 8: chf_pass<8, SIGN, DIT>(grp, buf, swm, N, L, tw); break;
+        case 4: chf_pass<4, SIGN, DIT>(grp, buf, swm, N, L, tw); break;
+        case 2: chf_pass<2, SIGN, DIT>(grp, buf, swm, N, L, tw); break;
+        case 3: chf_pass<3, SIGN, DIT>(grp, buf, swm, N, L, tw); break;
+        case 5: chf_pass<5, SIGN, DIT>(grp, buf, swm, N, L, tw); break;
+        default: chf_pass<7, SIGN, DIT>(grp, buf, swm, N, L, tw); break;
+    }
+}
+// backward (SIGN +1) transform, spectrum Z[k] in slot rev[k]  ->  z[n] in slot n  (decimation in time)
+template <class Grp>
+CHB_D void chf_fft_spec_to_time(Grp &grp, cd *buf, const ChfLoop &L) {
+    int len = 1;
+    for (int s = L.nfac - 1; s >= 0; --s) {
+        len *= L.fac[s];
+        chf_pass_r<+1, true>(grp, buf, L.swm, L.N, len, L.fac[s], L.tw[s]);
+    }
+}
+// forward (SIGN -1) transform, g[n] in slot n  ->  Y[k] in slot rev[k]  (decimation in frequency)
+template <class Grp>
+CHB_D void chf_fft_time_to_spec(Grp &grp, cd *buf, const ChfLoop &L) {
+    int len = L.N;
+    for (int s = 0; s < L.nfac; ++s) {
+        chf_pass_r<-1, false>(grp, buf, L.swm, L.N, len, L.fac[s], L.tw[s]);
+        len /= L.fac[s];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// load phase of one loop: parameters -> spectrum Z in digit-reversed slots (changevar_mom_pos, :4489-4573, fused)
+// ------------------------------------------------------------------------------------------------
+CHB_HD void chf_load4(const double *p, int aligned16, double *v) {
+#if defined(__CUDA_ARCH__)
+    if (aligned16) {
+        const double2 a = __ldg((const double2 *)p), b = __ldg((const double2 *)(p + 2));
+        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+        return;
+    }
+#endif
+    (void)aligned16;
+    v[0] = p[0]; v[1] = p[1]; v[2] = p[2]; v[3] = p[3];
+}
+CHB_HD void chf_store4(double *p, int aligned16, const double *v) {
+#if defined(__CUDA_ARCH__)
+    if (aligned16) {
+        *(double2 *)p = make_double2(v[0], v[1]);
+        *(double2 *)(p + 2) = make_double2(v[2], v[3]);
+        return;
+    }
+#endif
+    (void)aligned16;
+    p[0] = v[0]; p[1] = v[1]; p[2] = v[2]; p[3] = v[3];
+}
+
+template <class Grp>
+CHB_D void chf_load_loop(Grp &grp, const ChfSys &F, const ChfLoop &L, const double *vec_b, cd *buf, double *red,
+                          bool want_kin) {
+    grp.par([&](int tid, int T) {
+        double kin = 0.0;
+        const double *base = vec_b + L.mom_off - L.nco_in;
+        for (int k = tid; k < L.npr; k += T) {
+            if (k == 0) {
+                const double p0 = L.co0 >= 0 ? vec_b[L.mom_off + L.co0] : 0.0;
+                const double p2 = L.co2 >= 0 ? vec_b[L.mom_off + L.co2] : 0.0;
+                buf[chf_swz(L.rev[0], L.swm)] = mk(p0 * L.loopmul, p2 * L.loopmul);  // the c2r ignores Im of the DC term
+                buf[chf_swz(L.rev[L.npr], L.swm)] = mk(0.0, 0.0);                    // Nyquist row = zero padding
+            } else {
+                double p[4];
+                chf_load4(base + 4LL * k, F.aligned16, p);
+                kin += (p[0] * p[0] + p[1] * p[1]) + (p[2] * p[2] + p[3] * p[3]);
+                const double sc = L.loopmul / (double)((long long)k * L.ncm);
+                // X0 = (p0 + i p1) sc, X1 = (p2 + i p3) sc ; Z[k] = X0 + i X1 ; Z[N-k] = conj(X0) + i conj(X1)
+                buf[chf_swz(L.rev[k], L.swm)] = mk((p[0] - p[3]) * sc, (p[1] + p[2]) * sc);
+                buf[chf_swz(L.rev[L.N - k], L.swm)] = mk((p[0] + p[3]) * sc, (p[2] - p[1]) * sc);
+            }
+        }
+        if (want_kin) red[grp.g * T + tid] += 0.5 * kin;
+    });
+}
+
+// store phase of one loop: spectrum Y of the segment gradient -> parameter-space result (changevar_mom_pos_T,
+// :4746-4827, and params_to_kin_nrg_grad_daxpy, :4947-4973, fused)
+template <class Grp>
+CHB_D void chf_store_loop(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd *buf, const double *kin_b, double *out_b,
+                           double *red, bool want_kin) {
+    grp.par([&](int tid, int T) {
+        double kin = 0.0;
+        const long long off = L.mom_off - L.nco_in;
+        for (int k = tid; k < L.npr; k += T) {
+            const cd A = buf[chf_swz(L.rev[k], L.swm)];
+            if (k == 0) {
+                // f = 1, Y_0[0] = Re, imaginary parts of the DC term get no gradient
+                for (int c = 0; c < 4 - L.nco_in; ++c) out_b[L.mom_off + c] = 0.0;
+                if (L.co0 >= 0) out_b[L.mom_off + L.co0] = A.x * L.loopmul;
+                if (L.co2 >= 0) out_b[L.mom_off + L.co2] = A.y * L.loopmul;
+            } else {
+                const cd Bm = buf[chf_swz(L.rev[L.N - k], L.swm)];  // conj(Bm) = (Bm.x, -Bm.y)
+                const double sc = L.loopmul / (double)((long long)k * L.ncm);
+                // Y_0 = (A + conj(Bm))/2, Y_1 = (A - conj(Bm))/(2i); the adjoint carries a factor 2 for k > 0
+                double v[4] = {(A.x + Bm.x) * sc, (A.y - Bm.y) * sc, (A.y + Bm.y) * sc, (Bm.x - A.x) * sc};
+                if (kin_b) {
+                    double p[4];
+                    chf_load4(kin_b + off + 4LL * k, F.aligned16, p);
+                    kin += (p[0] * p[0] + p[1] * p[1]) + (p[2] * p[2] + p[3] * p[3]);
+                    v[0] += p[0]; v[1] += p[1]; v[2] += p[2]; v[3] += p[3];
+                }
+                chf_store4(out_b + off + 4LL * k, F.aligned16, v);
+            }
+        }
+        if (want_kin) red[grp.g * T + tid] += 0.5 * kin;
+    });
+}
+
+// ------------------------------------------------------------------------------------------------
+// pair phase, in place: PMODE 0 energy, 1 energy + gradient, 2 Hessian-vector, 3 none (segment positions only)
+// ------------------------------------------------------------------------------------------------
+CHB_HD void chf_inter_law(int kind, const double *law, double xsq, double *V, double *V1, double *V2) {
+    double a, b;
+    if (kind == 0) {
+#if defined(__CUDA_ARCH__)
+        double r = rsqrt(xsq);
+#else
+        double r = 1.0 / sqrt(xsq);
+#endif
+        double r2 = r * r;
+        a = r2 * r2 * r;  // xsq^-2.5 (inline_gravity_pot, :111-118)
+        b = xsq * a;
+        *V = -xsq * b;
+        *V1 = 0.5 * b;
+        *V2 = -0.75 * a;
+    } else {
+        a = law[3] * pow(xsq, law[2]);  // power_law_pot, :125-133
+        b = xsq * a;
+        *V = -xsq * b;
+        *V1 = law[0] * b;
+        *V2 = law[1] * a;
+    }
+}
+
+template <int NSEG, int PMODE, class Ctx>
+CHB_D void chf_pair(Ctx &ctx, const ChfSys &F, cd *sm, bool have_fwd, const double *seg_in_b, double *seg_out_b,
+                     double *red) {
+    ctx.par([&](int tid, int nthr) {
+        double e = 0.0;
+        const int size = F.segm_size;
+        const double inv_size = 1.0 / (double)size;
+        for (int i = tid; i < size; i += nthr) {
+            cd x[NSEG], dx[NSEG], g[NSEG];
+            int slot[NSEG];
+#pragma unroll
+            for (int s = 0; s < NSEG; ++s) {
+                const ChfSeg &sg = F.segs[s];
+                const ChfLoop &L = F.loops[sg.loop];
+                const int row = sg.row0 + (sg.timerev > 0 ? i : size - 1 - i);
+                slot[s] = L.smem_off + chf_swz(row, L.swm);
+                cd v = mk(0.0, 0.0);
+                if (have_fwd) {
+                    const cd u = sm[slot[s]];
+                    v = sg.isid ? u : mk(u.x * sg.rot[0] + u.y * sg.rot[2], u.x * sg.rot[1] + u.y * sg.rot[3]);  // x @ R
+                }
+                if (PMODE == 2) {
+                    dx[s] = v;
+                    x[s] = ((const cd *)seg_in_b)[(long long)s * size + i];
+                } else {
+                    x[s] = seg_in_b ? ((const cd *)seg_in_b)[(long long)s * size + i] : v;
+                    dx[s] = mk(0.0, 0.0);
+                }
+                if (seg_out_b) ((cd *)seg_out_b)[(long long)s * size + i] = v;
+                g[s] = mk(0.0, 0.0);
+            }
+            if (PMODE != 3) {
+#pragma unroll
+                for (int s = 0; s < NSEG; ++s) {
+#pragma unroll
+                    for (int t = 0; t < NSEG; ++t) {
+                        const ChfPair &P = F.pairs[s * CHF_MAX_SEGS + t];
+                        if (!P.on) continue;
+                        cd xs = x[s], ds = dx[s];
+                        if (!P.isid) {
+                            xs = mk(P.rot[0] * x[s].x + P.rot[1] * x[s].y, P.rot[2] * x[s].x + P.rot[3] * x[s].y);
+                            if (PMODE == 2)
+                                ds = mk(P.rot[0] * dx[s].x + P.rot[1] * dx[s].y, P.rot[2] * dx[s].x + P.rot[3] * dx[s].y);
+                        }
+                        const cd d = csub(xs, x[t]);
+                        const double xsq = d.x * d.x + d.y * d.y;
+                        double V, V1, V2;
+                        chf_inter_law(F.law_kind, F.law, xsq, &V, &V1, &V2);
+                        const double binfac = P.fac * inv_size;
+                        if (PMODE <= 1) e += V * binfac;
+                        if (PMODE >= 1) {
+                            const double f = -2.0 * binfac;  // globalmul = -1 (:2843)
+                            cd gv;
+                            if (PMODE == 1) {
+                                gv = mk(f * V1 * d.x, f * V1 * d.y);
+                            } else {
+                                const cd dd = csub(ds, dx[t]);
+                                const double bb = 2.0 * V2 * (d.x * dd.x + d.y * dd.y);
+                                gv = mk(f * (bb * d.x + V1 * dd.x), f * (bb * d.y + V1 * dd.y));
+                            }
+                            if (P.isid) {
+                                g[s] = cadd(g[s], gv);
+                            } else {  // R^T g
+                                g[s].x += P.rot[0] * gv.x + P.rot[2] * gv.y;
+                                g[s].y += P.rot[1] * gv.x + P.rot[3] * gv.y;
+                            }
+                            g[t] = csub(g[t], gv);
+                        }
+                    }
+                }
+            }
+            if (PMODE == 1 || PMODE == 2) {
+#pragma unroll
+                for (int s = 0; s < NSEG; ++s) {
+                    const ChfSeg &sg = F.segs[s];
+                    // segmpos_to_pos_slice_T (:5896-5976): pos_slice row += R . g
+                    sm[slot[s]] = sg.isid ? g[s]
+                                          : mk(sg.rot[0] * g[s].x + sg.rot[1] * g[s].y, sg.rot[2] * g[s].x + sg.rot[3] * g[s].y);
+                }
+            }
+        }
+        if (PMODE <= 1) red[tid] -= e;
+    });
+}
+
+// ------------------------------------------------------------------------------------------------
+// the CTA program
+// ------------------------------------------------------------------------------------------------
+template <int NSEG, int PMODE, class Ctx>
+CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, double *red, cd *sm) {
+    const double *vec_b = A.vec_in ? A.vec_in + b * F.nparams : (const double *)0;
+    const double *kin_b = A.kin_src ? A.kin_src + b * F.nparams : (const double *)0;
+    const double *seg_in_b = A.seg_in ? A.seg_in + b * F.segsz : (const double *)0;
+    double *seg_out_b = A.seg_out ? A.seg_out + b * F.segsz : (double *)0;
+    double *out_b = A.vec_out ? A.vec_out + b * F.nparams : (double *)0;
+    const bool have_fwd = vec_b != (const double *)0;
+    ctx.groups(F.nloop, F.T, [&](auto &grp) {
+        grp.par([&](int tid, int T) { red[grp.g * T + tid] = 0.0; });
+        if (have_fwd) {
+            const ChfLoop &L = F.loops[grp.g];
+            cd *buf = sm + L.smem_off;
+            chf_load_loop(grp, F, L, vec_b, buf, red, A.kin_from == 1);
+            chf_fft_spec_to_time(grp, buf, L);
+        }
+    });
+    chf_pair<NSEG, PMODE>(ctx, F, sm, have_fwd, seg_in_b, seg_out_b, red);
+    if (out_b) {
+        ctx.groups(F.nloop, F.T, [&](auto &grp) {
+            const ChfLoop &L = F.loops[grp.g];
+            cd *buf = sm + L.smem_off;
+            chf_fft_time_to_spec(grp, buf, L);
+            chf_store_loop(grp, F, L, buf, kin_b, out_b, red, A.kin_from == 2);
+        });
+    }
+    if (A.scalar_out) {
+        cta_reduce(ctx, red);
+        ctx.par([&](int tid, int nthr) {
+            if (tid == 0) A.scalar_out[b] = red[0];
+        });
+    }
 }

@@ -35,12 +35,40 @@ def test_hostsim_matches_reference_golden(name, sim, golden_cache):
         act, grad = nbs.params_to_action_and_grad(v("params"))
         assert relerr(act, v("action")) < TOL_ACTION, tag
         assert relerr(grad, v("grad")) < TOL_GRAD, tag
+        if nbs.fused:  # everything above and below ran on the fused CTA program: repeat the chain on the staged one
+            nbs.set_fused(False)
+            assert relerr(nbs.params_to_segmpos(v("params")), v("segmpos")) < TOL_TRANSFORM, tag
+            act, grad = nbs.params_to_action_and_grad(v("params"))
+            assert relerr(act, v("action")) < TOL_ACTION and relerr(grad, v("grad")) < TOL_GRAD, tag
+            assert relerr(nbs.params_to_action_hess(v("params"), v("dparams")), v("hess")) < TOL_HESS, tag
+            assert relerr(nbs.segmpos_dparams_to_action_hess(v("segmpos"), v("dparams")), v("hess_cached")) < TOL_HESS, tag
+            nbs.set_fused(True)
         assert relerr(nbs.params_to_action_hess(v("params"), v("dparams")), v("hess")) < TOL_HESS, tag
         assert relerr(nbs.segmpos_dparams_to_action_hess(v("segmpos"), v("dparams")), v("hess_cached")) < TOL_HESS, tag
         assert relerr(nbs.segmpos_params_to_action(v("segmpos"), v("params")), v("action")) < TOL_ACTION, tag
         assert relerr(nbs.segmpos_params_to_action_grad(v("segmpos"), v("params")), v("grad")) < TOL_GRAD, tag
         assert relerr(nbs.segmpos_to_params_T(v("segm")), v("params_T")) < TOL_TRANSFORM, tag
         assert relerr(nbs.segmpos_to_params(v("segmpos")), v("params_inv")) < TOL_TRANSFORM, tag
+
+
+@pytest.mark.parametrize("name,nint", [("3B", 4096), ("3C", 3072), ("3C", 3 * 2 * 600)])
+def test_hostsim_fused_radix16_sizes(name, nint, sim):
+    """The fused CTA program at the bench sizes (radix-16/8 passes, swizzled buffer) against the oracle."""
+    import os
+    from conftest import ROOT
+    from oracle.choreo_oracle import OracleSyst
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", f"{name}.npz"))
+    nbs = NBodySystB200(T, nint, _lib_handle=sim)
+    assert nbs.fused
+    O = OracleSyst(T, nint, backend="fft")
+    rng = np.random.default_rng(0)
+    x, dx = rng.random(nbs.nparams), rng.random(nbs.nparams)
+    act, grad = nbs.params_to_action_and_grad(x)
+    seg = nbs.params_to_segmpos(x)
+    assert relerr(act, O.params_to_action(x)) < TOL_ACTION
+    assert relerr(grad, O.params_to_action_grad(x)) < TOL_GRAD
+    assert relerr(seg, O.params_to_segmpos(x)) < TOL_TRANSFORM
+    assert relerr(nbs.segmpos_dparams_to_action_hess(seg, dx), O.segmpos_dparams_to_action_hess(seg, dx)) < TOL_HESS
 
 
 def test_host_layer_errors_and_batching(sim, golden_cache):

@@ -12,3 +12,8 @@ timeout 300 python bench.py --steps 2 --warmup 3 --batch 512 --no-e2e --no-cpu >
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches.csv \
     python bench.py --steps 2 --warmup 3 --batch 512 --no-e2e --no-cpu > $OUT/${TAG}_ncu.log 2>&1
 echo "ncu exit $?"
+if [ -n "$NCU_FULL" ]; then
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_fused -s 3 -c 1 -o $OUT/${TAG}_fused \
+    python bench.py --steps 1 --warmup 3 --batch 592 --no-e2e --no-cpu > $OUT/${TAG}_ncufull.log 2>&1
+echo "ncu full exit $?"
+fi
