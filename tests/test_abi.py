@@ -63,4 +63,6 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src, f
-                assert "hostsim" not in src or f in ("chb_api.cu", "chb_core.cuh"), f
+                # the CTA programs under csrc/ are also compiled by tests/hostsim (test-only emulation) and say so in
+                # comments; nothing on the Python side of the product may know about it
+                assert "hostsim" not in src or f.endswith((".cu", ".cuh")), f
