@@ -51,6 +51,7 @@ typedef void *chb_stream_t;
 // ------------------------------------------------------------------------------------------------
 // plan
 // ------------------------------------------------------------------------------------------------
+#define CHB_HOST_SLOTS 3  // stream slots of the host-pointer pipeline (chb_run_host)
 struct HostTables {
     int G = 0, nbody = 0, nloop = 0, nsegm = 0, nbin = 0, nint_min = 0, gns = 0, law = 0;
     double law_params[4] = {0, 0, 0, 0};
@@ -86,6 +87,9 @@ struct chb_plan {
     size_t stage_dev_bytes = 0;
     void *stage_pin = nullptr;
     size_t stage_pin_bytes = 0;
+#ifndef CHB_HOSTSIM
+    cudaStream_t host_streams[CHB_HOST_SLOTS] = {};
+#endif
     ChfSys fsys;            // fused path (valid when fused_active)
     int fused_threads = 0;
     size_t fused_smem = 0;
@@ -288,6 +292,8 @@ extern "C" int chb_plan_destroy(chb_plan *p) {
     free_level(p);
     if (p->stage_dev) dev_free(p->stage_dev);
 #ifndef CHB_HOSTSIM
+    for (int i = 0; i < CHB_HOST_SLOTS; ++i)
+        if (p->host_streams[i]) cudaStreamDestroy(p->host_streams[i]);
     if (p->stage_pin) cudaFreeHost(p->stage_pin);
 #else
     if (p->stage_pin) free(p->stage_pin);
@@ -1376,6 +1382,55 @@ static int ensure_stage(chb_plan *p, size_t bytes) {
     return CHB_OK;
 }
 
+// element counts per state of the arrays of a host operator
+static int host_op_shapes(const chb_plan *p, int op, bool have_out0, size_t *n_in0, size_t *n_in1, size_t *n_out0,
+                          size_t *n_out1) {
+    const size_t np = (size_t)p->sys.nparams, ns = (size_t)p->sys.segsz;
+    *n_in0 = *n_in1 = *n_out0 = *n_out1 = 0;
+    switch (op) {
+        case CHB_OP_PARAMS_TO_SEGMPOS: *n_in0 = np; *n_out0 = ns; break;
+        case CHB_OP_SEGMPOS_TO_PARAMS:
+        case CHB_OP_SEGMPOS_TO_PARAMS_T: *n_in0 = ns; *n_out0 = np; break;
+        case CHB_OP_ACTION: *n_in0 = np; *n_out0 = 1; break;
+        case CHB_OP_ACTION_GRAD: *n_in0 = np; *n_out0 = have_out0 ? 1 : 0; *n_out1 = np; break;
+        case CHB_OP_ACTION_HESS: *n_in0 = np; *n_in1 = np; *n_out0 = np; break;
+        case CHB_OP_SEGMPOS_ACTION: *n_in0 = ns; *n_in1 = np; *n_out0 = 1; break;
+        case CHB_OP_SEGMPOS_ACTION_GRAD: *n_in0 = ns; *n_in1 = np; *n_out0 = have_out0 ? 1 : 0; *n_out1 = np; break;
+        case CHB_OP_SEGMPOS_ACTION_HESS: *n_in0 = ns; *n_in1 = np; *n_out0 = np; break;
+        case CHB_OP_KIN: *n_in0 = np; *n_out0 = 1; break;
+        case CHB_OP_POT: *n_in0 = ns; *n_out0 = 1; break;
+        case CHB_OP_POT_GRAD: *n_in0 = ns; *n_out0 = ns; break;
+        case CHB_OP_POT_HESS: *n_in0 = ns; *n_in1 = ns; *n_out0 = ns; break;
+        default: return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_run_host: unknown op");
+    }
+    return CHB_OK;
+}
+
+static int host_op_dispatch(chb_plan *p, int op, int64_t nb, const double *d_in0, const double *d_in1, double scalar,
+                            double *d_out0, double *d_out1, bool have_out0, void *d_ws, size_t wsb, void *st) {
+    switch (op) {
+        case CHB_OP_PARAMS_TO_SEGMPOS: return chb_params_to_segmpos_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
+        case CHB_OP_SEGMPOS_TO_PARAMS: return chb_segmpos_to_params_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
+        case CHB_OP_SEGMPOS_TO_PARAMS_T: return chb_segmpos_to_params_T_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
+        case CHB_OP_ACTION: return chb_params_to_action_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
+        case CHB_OP_ACTION_GRAD:
+            return chb_params_to_action_grad_dev(p, nb, d_in0, have_out0 ? d_out0 : nullptr, d_out1, nullptr, d_ws, wsb, st);
+        case CHB_OP_ACTION_HESS: return chb_params_to_action_hess_dev(p, nb, d_in0, d_in1, d_out0, d_ws, wsb, st);
+        case CHB_OP_SEGMPOS_ACTION: return chb_segmpos_params_to_action_dev(p, nb, d_in0, d_in1, d_out0, d_ws, wsb, st);
+        case CHB_OP_SEGMPOS_ACTION_GRAD:
+            return chb_segmpos_params_to_action_grad_dev(p, nb, d_in0, d_in1, have_out0 ? d_out0 : nullptr, d_out1, d_ws, wsb, st);
+        case CHB_OP_SEGMPOS_ACTION_HESS: return chb_segmpos_dparams_to_action_hess_dev(p, nb, d_in0, d_in1, d_out0, d_ws, wsb, st);
+        case CHB_OP_KIN: return chb_params_to_kin_nrg_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
+        case CHB_OP_POT: return chb_segmpos_to_pot_nrg_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
+        case CHB_OP_POT_GRAD: return chb_segmpos_to_pot_nrg_grad_dev(p, nb, d_in0, scalar, d_out0, d_ws, wsb, st);
+        case CHB_OP_POT_HESS: return chb_segmpos_to_pot_nrg_hess_dev(p, nb, d_in0, d_in1, scalar, d_out0, d_ws, wsb, st);
+    }
+    return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_run_host: unknown op");
+}
+
+// Host-pointer operator: the batch is cut into slices that travel through CHB_HOST_SLOTS stream slots
+// (H2D, kernels, D2H of a slice are ordered on its stream; slices on different streams overlap), so that with
+// pinned host buffers (chb_malloc_pinned) the PCIe link runs in both directions while the SMs compute.
 extern "C" int chb_run_host(chb_plan *p, int op, int64_t batch, const double *in0, const double *in1, double scalar,
                             double *out0, double *out1) {
     CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_run_host: NULL plan");
@@ -1383,67 +1438,58 @@ extern "C" int chb_run_host(chb_plan *p, int op, int64_t batch, const double *in
     CHB_REQUIRE(batch >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_run_host: negative batch");
     if (batch == 0) return CHB_OK;
     std::lock_guard<std::mutex> lock(p->host_mutex);
-    const ChbSys &S = p->sys;
-    const size_t np = (size_t)S.nparams, ns = (size_t)S.segsz;
-    size_t n_in0 = 0, n_in1 = 0, n_out0 = 0, n_out1 = 0;
-    switch (op) {
-        case CHB_OP_PARAMS_TO_SEGMPOS: n_in0 = np; n_out0 = ns; break;
-        case CHB_OP_SEGMPOS_TO_PARAMS:
-        case CHB_OP_SEGMPOS_TO_PARAMS_T: n_in0 = ns; n_out0 = np; break;
-        case CHB_OP_ACTION: n_in0 = np; n_out0 = 1; break;
-        case CHB_OP_ACTION_GRAD: n_in0 = np; n_out0 = out0 ? 1 : 0; n_out1 = np; break;
-        case CHB_OP_ACTION_HESS: n_in0 = np; n_in1 = np; n_out0 = np; break;
-        case CHB_OP_SEGMPOS_ACTION: n_in0 = ns; n_in1 = np; n_out0 = 1; break;
-        case CHB_OP_SEGMPOS_ACTION_GRAD: n_in0 = ns; n_in1 = np; n_out0 = out0 ? 1 : 0; n_out1 = np; break;
-        case CHB_OP_SEGMPOS_ACTION_HESS: n_in0 = ns; n_in1 = np; n_out0 = np; break;
-        case CHB_OP_KIN: n_in0 = np; n_out0 = 1; break;
-        case CHB_OP_POT: n_in0 = ns; n_out0 = 1; break;
-        case CHB_OP_POT_GRAD: n_in0 = ns; n_out0 = ns; break;
-        case CHB_OP_POT_HESS: n_in0 = ns; n_in1 = ns; n_out0 = ns; break;
-        default: return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_run_host: unknown op");
-    }
+    size_t n_in0, n_in1, n_out0, n_out1;
+    const bool have_out0 = out0 != nullptr;
+    CHB_TRY(host_op_shapes(p, op, have_out0, &n_in0, &n_in1, &n_out0, &n_out1));
     CHB_REQUIRE(in0 && (n_in1 == 0 || in1) && (n_out0 == 0 || out0) && (n_out1 == 0 || out1), CHB_ERR_INVALID_ARGUMENT,
                 "chb_run_host: NULL array for this op");
+    // slice size: ~48 MB of the widest array, a multiple of the SM count when the batch allows it
+    const size_t widest = std::max(std::max(n_in0, n_in1), std::max(n_out0, n_out1)) * 8;
+    int64_t slice = (int64_t)std::max<size_t>(1, ((size_t)48 << 20) / std::max<size_t>(widest, 1));
+    if (slice >= p->num_sms) slice -= slice % p->num_sms;
+    slice = std::min<int64_t>(slice, batch);
+    const int nslots = (int)std::min<int64_t>(CHB_HOST_SLOTS, (batch + slice - 1) / slice);
     size_t wsb = 0;
-    CHB_TRY(chb_workspace_bytes(p, batch, &wsb));
-    const size_t B = (size_t)batch;
-    size_t b_in0 = align_up(B * n_in0 * 8), b_in1 = align_up(B * n_in1 * 8), b_out0 = align_up(B * std::max<size_t>(n_out0, 1) * 8),
-           b_out1 = align_up(B * n_out1 * 8);
-    CHB_TRY(ensure_stage(p, b_in0 + b_in1 + b_out0 + b_out1 + align_up(wsb) + 512));
-    char *q = (char *)(((uintptr_t)p->stage_dev + 255) & ~(uintptr_t)255);
-    double *d_in0 = (double *)q; q += b_in0;
-    double *d_in1 = (double *)q; q += b_in1;
-    double *d_out0 = (double *)q; q += b_out0;
-    double *d_out1 = (double *)q; q += b_out1;
-    void *d_ws = q;
-    void *st = nullptr;
-    CHB_TRY(chb_memcpy_h2d(p, d_in0, in0, B * n_in0 * 8, st));
-    if (n_in1) CHB_TRY(chb_memcpy_h2d(p, d_in1, in1, B * n_in1 * 8, st));
+    CHB_TRY(chb_workspace_bytes(p, slice, &wsb));
+    const size_t S = (size_t)slice;
+    const size_t b_in0 = align_up(S * n_in0 * 8), b_in1 = align_up(S * n_in1 * 8),
+                 b_out0 = align_up(S * std::max<size_t>(n_out0, 1) * 8), b_out1 = align_up(S * n_out1 * 8);
+    const size_t per_slot = b_in0 + b_in1 + b_out0 + b_out1 + align_up(wsb);
+    CHB_TRY(ensure_stage(p, per_slot * nslots + 512));
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaSetDevice(p->device));
+    for (int i = 0; i < nslots; ++i)
+        if (!p->host_streams[i]) CHB_CUDA(cudaStreamCreateWithFlags(&p->host_streams[i], cudaStreamNonBlocking));
+#endif
+    char *base = (char *)(((uintptr_t)p->stage_dev + 255) & ~(uintptr_t)255);
     int rc = CHB_OK;
-    switch (op) {
-        case CHB_OP_PARAMS_TO_SEGMPOS: rc = chb_params_to_segmpos_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
-        case CHB_OP_SEGMPOS_TO_PARAMS: rc = chb_segmpos_to_params_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
-        case CHB_OP_SEGMPOS_TO_PARAMS_T: rc = chb_segmpos_to_params_T_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
-        case CHB_OP_ACTION: rc = chb_params_to_action_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
-        case CHB_OP_ACTION_GRAD:
-            rc = chb_params_to_action_grad_dev(p, batch, d_in0, n_out0 ? d_out0 : nullptr, d_out1, nullptr, d_ws, wsb, st);
-            break;
-        case CHB_OP_ACTION_HESS: rc = chb_params_to_action_hess_dev(p, batch, d_in0, d_in1, d_out0, d_ws, wsb, st); break;
-        case CHB_OP_SEGMPOS_ACTION: rc = chb_segmpos_params_to_action_dev(p, batch, d_in0, d_in1, d_out0, d_ws, wsb, st); break;
-        case CHB_OP_SEGMPOS_ACTION_GRAD:
-            rc = chb_segmpos_params_to_action_grad_dev(p, batch, d_in0, d_in1, n_out0 ? d_out0 : nullptr, d_out1, d_ws, wsb, st);
-            break;
-        case CHB_OP_SEGMPOS_ACTION_HESS:
-            rc = chb_segmpos_dparams_to_action_hess_dev(p, batch, d_in0, d_in1, d_out0, d_ws, wsb, st);
-            break;
-        case CHB_OP_KIN: rc = chb_params_to_kin_nrg_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
-        case CHB_OP_POT: rc = chb_segmpos_to_pot_nrg_dev(p, batch, d_in0, d_out0, d_ws, wsb, st); break;
-        case CHB_OP_POT_GRAD: rc = chb_segmpos_to_pot_nrg_grad_dev(p, batch, d_in0, scalar, d_out0, d_ws, wsb, st); break;
-        case CHB_OP_POT_HESS: rc = chb_segmpos_to_pot_nrg_hess_dev(p, batch, d_in0, d_in1, scalar, d_out0, d_ws, wsb, st); break;
+    int64_t c0 = 0;
+    for (int it = 0; c0 < batch && rc == CHB_OK; ++it, c0 += slice) {
+        const int64_t nb = std::min<int64_t>(slice, batch - c0);
+        const int slot = it % nslots;
+        char *q = base + per_slot * slot;
+        double *d_in0 = (double *)q; q += b_in0;
+        double *d_in1 = (double *)q; q += b_in1;
+        double *d_out0 = (double *)q; q += b_out0;
+        double *d_out1 = (double *)q; q += b_out1;
+        void *d_ws = q;
+#ifndef CHB_HOSTSIM
+        void *st = (void *)p->host_streams[slot];
+#else
+        void *st = nullptr;
+#endif
+        const size_t B = (size_t)nb;
+        rc = chb_memcpy_h2d(p, d_in0, in0 + (size_t)c0 * n_in0, B * n_in0 * 8, st);
+        if (!rc && n_in1) rc = chb_memcpy_h2d(p, d_in1, in1 + (size_t)c0 * n_in1, B * n_in1 * 8, st);
+        if (!rc) rc = host_op_dispatch(p, op, nb, d_in0, d_in1, scalar, d_out0, d_out1, have_out0, d_ws, wsb, st);
+        if (!rc && n_out0) rc = chb_memcpy_d2h(p, out0 + (size_t)c0 * n_out0, d_out0, B * n_out0 * 8, st);
+        if (!rc && n_out1) rc = chb_memcpy_d2h(p, out1 + (size_t)c0 * n_out1, d_out1, B * n_out1 * 8, st);
     }
-    if (rc) return rc;
-    if (n_out0) CHB_TRY(chb_memcpy_d2h(p, out0, d_out0, B * n_out0 * 8, st));
-    if (n_out1) CHB_TRY(chb_memcpy_d2h(p, out1, d_out1, B * n_out1 * 8, st));
-    CHB_TRY(chb_stream_synchronize(p, st));
-    return CHB_OK;
+#ifndef CHB_HOSTSIM
+    for (int i = 0; i < nslots; ++i) {
+        cudaError_t e = cudaStreamSynchronize(p->host_streams[i]);
+        if (e != cudaSuccess && rc == CHB_OK) rc = chb_fail(CHB_ERR_CUDA, std::string("chb_run_host: ") + cudaGetErrorString(e));
+    }
+#endif
+    return rc;
 }

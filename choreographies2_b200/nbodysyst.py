@@ -125,8 +125,29 @@ class NBodySystB200:
         batch = int(np.prod(shp[:-n], dtype=np.int64)) if len(shp) > n else 1
         return batch, shp[:-n]
 
+    def _out(self, given, shape, what):
+        if given is None:
+            return np.empty(shape, dtype=np.float64)
+        if (not isinstance(given, np.ndarray) or given.dtype != np.float64 or not given.flags.c_contiguous
+                or tuple(given.shape) != tuple(shape)):
+            raise ValueError(f"{what}: expected a C-contiguous float64 array of shape {tuple(shape)}")
+        return given
+
+    def pinned_empty(self, shape) -> np.ndarray:
+        """Page-locked float64 NumPy array (``chb_malloc_pinned``): host buffers of this kind let the host-pointer
+        operators overlap H2D, kernels and D2H.  Freed when the array (and every view of it) is collected."""
+        import weakref
+        shape = tuple(int(v) for v in (shape if hasattr(shape, "__len__") else (shape,)))
+        n = int(np.prod(shape, dtype=np.int64))
+        ptr = C.c_void_p()
+        L.check(self._lib, self._lib.chb_malloc_pinned(max(n, 1) * 8, C.byref(ptr)))
+        buf = (C.c_double * max(n, 1)).from_address(ptr.value)
+        arr = np.frombuffer(buf, dtype=np.float64, count=n).reshape(shape)
+        weakref.finalize(buf, self._lib.chb_free_pinned, C.c_void_p(ptr.value))
+        return arr
+
     def _host(self, op, in0, in0_shape, in1=None, in1_shape=None, out0_shape=None, out1_shape=None, scalar=0.0,
-              want_out0=True):
+              want_out0=True, out0=None, out1=None):
         a0 = np.ascontiguousarray(in0, dtype=np.float64)
         batch, lead = self._check(a0, in0_shape, "input")
         a1 = None
@@ -135,8 +156,8 @@ class NBodySystB200:
             b1, _ = self._check(a1, in1_shape, "second input")
             if b1 != batch:
                 raise ValueError("batch sizes of the two inputs differ")
-        o0 = np.empty(lead + tuple(out0_shape), dtype=np.float64) if (out0_shape is not None and want_out0) else None
-        o1 = np.empty(lead + tuple(out1_shape), dtype=np.float64) if out1_shape is not None else None
+        o0 = self._out(out0, lead + tuple(out0_shape), "out0") if (out0_shape is not None and want_out0) else None
+        o1 = self._out(out1, lead + tuple(out1_shape), "out1") if out1_shape is not None else None
         vp = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None  # noqa: E731
         L.check(self._lib, self._lib.chb_run_host(self._plan, op, batch, vp(a0), vp(a1), float(scalar), vp(o0), vp(o1)))
         return o0, o1
@@ -294,9 +315,11 @@ class NBodySystB200:
         """_NBodySyst.pyx:2794-2873."""
         return self.params_to_action_and_grad(params_mom_buf, want_action=False)[1]
 
-    def params_to_action_and_grad(self, params_mom_buf, want_action: bool = True, want_segmpos: bool = False):
+    def params_to_action_and_grad(self, params_mom_buf, want_action: bool = True, want_segmpos: bool = False,
+                                  out_action=None, out_grad=None):
         """One fused evaluation of ``params_to_action`` + ``params_to_action_grad`` (unit U1 of SURVEY.md 8(d)).
-        Returns (action or None, grad[, segmpos])."""
+        Returns (action or None, grad[, segmpos]).  Host path: ``out_action`` / ``out_grad`` may be preallocated
+        (e.g. ``pinned_empty``) arrays that receive the results."""
         if _is_torch(params_mom_buf):
             import torch
             x, b, lead = self._tprep(params_mom_buf, (self.nparams,), "params")
@@ -309,7 +332,7 @@ class NBodySystB200:
         if want_segmpos:
             raise ValueError("want_segmpos is only available on the device (torch) path")
         o0, o1 = self._host(L.OP_ACTION_GRAD, a, (self.nparams,), out0_shape=(), out1_shape=(self.nparams,),
-                            want_out0=want_action)
+                            want_out0=want_action, out0=out_action, out1=out_grad)
         return (self._scalar(o0, a.shape[:-1]) if want_action else None), o1
 
     def params_to_action_hess(self, params_mom_buf, dparams_mom_buf):
