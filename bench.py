@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=4096, help="states per GPU")
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--no-fused", action="store_true")
+    ap.add_argument("--fused-ver", type=int, default=2, help="2 = load/store fused into the FFT passes (default), 1 = separate phases")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample", type=int, default=0, help="states in the cpu_baseline sample (0 = auto)")
@@ -252,7 +253,7 @@ def run_b200(args):
     nbs = NBodySystB200(T, args.nint, device=local)
     if args.chunk:
         nbs.set_chunk(args.chunk)
-    nbs.set_fused(not args.no_fused)
+    nbs.set_fused(0 if args.no_fused else args.fused_ver)
     B, npar = args.batch, nbs.nparams
     rng = np.random.default_rng(1234 + rank)
     x_host = torch.from_numpy(rng.random((B, npar))).pin_memory()

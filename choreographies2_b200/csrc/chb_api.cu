@@ -70,7 +70,7 @@ struct chb_plan {
     std::vector<ChbLoop> h_loops;      // host mirror (device pointers inside)
     ChbSys sys;                        // passed by value to kernels
     int64_t chunk_user = 0;
-    int fused_enabled = 1;
+    int fused_enabled = 2;  // 0 staged kernels only, 1 fused v1 (separate load/store phases), 2 fused v2
     int fused_active = 0;
     int64_t launches = 0;
     size_t smem_limit = 0;  // max dynamic shared memory per block (opt-in)
@@ -362,14 +362,17 @@ struct FftCache {
 // ---- fused path planning (chb_fused.cuh) ------------------------------------------------------------
 static bool chf_factorize(int N, std::vector<int> &fac) {
     fac.clear();
+    // odd radices first (outermost), the largest power of two last: the last factor is the pass that the v2 kernel
+    // fuses with the parameter load / result store (chf_load_pass / chf_store_pass), which needs it even
     int m = N, e2 = 0;
     while (m % 2 == 0) { m /= 2; ++e2; }
-    while (e2 >= 4) { fac.push_back(16); e2 -= 4; }
-    if (e2 == 3) fac.push_back(8);
-    if (e2 == 2) fac.push_back(4);
-    if (e2 == 1) fac.push_back(2);
-    for (int q : {3, 5, 7})
+    for (int q : {7, 5, 3})
         while (m % q == 0) { fac.push_back(q); m /= q; }
+    const int rem = e2 % 4;
+    if (rem == 1) fac.push_back(2);
+    if (rem == 2) fac.push_back(4);
+    if (rem == 3) fac.push_back(8);
+    for (; e2 >= 4; e2 -= 4) fac.push_back(16);
     return m == 1 && !fac.empty() && (int)fac.size() <= CHF_MAX_FAC;
 }
 
@@ -448,6 +451,11 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
     p->fused_threads = Tg * T.nloop;
     p->fused_smem = CHF_RED_BYTES + (size_t)smem_cd * sizeof(cd);
     if (p->fused_smem > p->smem_limit) return 0;
+    {   // co-resident CTAs = distance (in states) of the L2 prefetch
+        const size_t per_cta = p->fused_smem + 1024;
+        int occ = (int)std::min<size_t>((size_t)(228 * 1024) / per_cta, (size_t)(2048 / p->fused_threads));
+        F.pf_stride = std::max(1, occ) * p->num_sms;
+    }
     // tables, shared between loops of equal length
     for (int il = 0; il < T.nloop; ++il) {
         ChfLoop &FL = F.loops[il];
@@ -797,7 +805,7 @@ extern "C" int chb_plan_set_chunk(chb_plan *p, int64_t chunk) {
 }
 extern "C" int chb_plan_set_fused(chb_plan *p, int enable) {
     CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_fused: NULL plan");
-    p->fused_enabled = enable ? 1 : 0;
+    p->fused_enabled = enable < 0 ? 0 : (enable > 2 ? 2 : enable);
     return CHB_OK;
 }
 
@@ -861,6 +869,25 @@ struct DevGrp {
         f((int)threadIdx.x - g * T, T);
         asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(T) : "memory");
     }
+    __device__ __forceinline__ void sync() { asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(T) : "memory"); }
+    // f1, exchange of s.x[0..NX) with lane ^ s.xm (0 keeps the own values), f2; no barrier.  T is a multiple of 32
+    // and every thread of the group makes the call, so all lanes of a warp take part in the shuffles.
+    template <class S, int NX, class F1, class F2>
+    __device__ __forceinline__ void par_xchg(F1 f1, F2 f2) {
+        S s;
+        const int tid = (int)threadIdx.x - g * T;
+        f1(tid, T, s);
+#pragma unroll
+        for (int i = 0; i < NX; ++i) {
+            s.x[i].x = __shfl_xor_sync(0xffffffffu, s.x[i].x, s.xm);
+            s.x[i].y = __shfl_xor_sync(0xffffffffu, s.x[i].y, s.xm);
+        }
+        f2(tid, T, s);
+    }
+    template <class F>
+    __device__ __forceinline__ void one(F f) {
+        if ((int)threadIdx.x == g * T) f();
+    }
 };
 struct DevCtx {
     template <class F>
@@ -890,6 +917,20 @@ struct HostGrp {
     void par(F f) {
         for (int t = 0; t < T; ++t) f(t, T);
     }
+    void sync() {}
+    template <class S, int NX, class F1, class F2>
+    void par_xchg(F1 f1, F2 f2) {
+        std::vector<S> st((size_t)T);
+        for (int t = 0; t < T; ++t) f1(t, T, st[t]);
+        for (int t = 0; t < T; ++t) {
+            const int u = t ^ st[t].xm;
+            if (u > t)
+                for (int i = 0; i < NX; ++i) std::swap(st[t].x[i], st[u].x[i]);
+        }
+        for (int t = 0; t < T; ++t) f2(t, T, st[t]);
+    }
+    template <class F>
+    void one(F f) { f(); }
 };
 struct HostCtx {
     int nthr;
@@ -1094,7 +1135,10 @@ static int launch_fused_n(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A, 
     return CHB_OK;
 }
 // pmode: 0 energy, 1 energy + gradient, 2 Hessian-vector, 3 segment positions only
-static int launch_fused(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A, chb_stream_t st) {
+static int launch_fused(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A0, chb_stream_t st) {
+    ChfArgs A = A0;
+    A.nstates = nb;
+    p->fsys.ver = p->fused_enabled;
     switch (p->fsys.nseg) {
         case 1: return launch_fused_n<1>(p, pmode, nb, A, st);
         case 2: return launch_fused_n<2>(p, pmode, nb, A, st);
@@ -1108,6 +1152,7 @@ static bool use_fused(const chb_plan *p) { return p->fused_enabled && p->fused_a
 static ChfArgs chf_args(const double *vec_in, const double *kin_src, const double *seg_in, double *seg_out,
                         double *vec_out, double *scalar_out, int kin_from) {
     ChfArgs A;
+    A.nstates = 0;  // set by launch_fused
     A.vec_in = vec_in; A.kin_src = kin_src; A.seg_in = seg_in; A.seg_out = seg_out; A.vec_out = vec_out;
     A.scalar_out = scalar_out; A.kin_from = kin_from;
     return A;

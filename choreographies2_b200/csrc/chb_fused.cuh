@@ -51,6 +51,8 @@ struct ChfPair {
 struct ChfSys {
     int nloop, nseg, T, segm_size;
     int aligned16, law_kind;
+    int ver;        // 2: parameter load / result store fused into the first / last FFT pass (lane-pair exchange), 1: separate phases
+    int pf_stride;  // > 0: CTA b asks L2 for the parameters of state b + pf_stride while it computes (co-resident CTA count)
     long long nparams, segsz;
     double law[4];
     ChfLoop loops[CHF_MAX_LOOPS];
@@ -65,6 +67,7 @@ struct ChfArgs {
     double *vec_out;        // [B][nparams] adjoint result (gradient / Hessian-vector), or NULL
     double *scalar_out;     // [B] kinetic - potential, or NULL
     int kin_from;           // 0 none, 1 kinetic energy from vec_in (load phase), 2 from kin_src (store phase)
+    long long nstates;      // batch size (bound of the L2 prefetch)
 };
 
 CHB_HD int chf_swz(int i, int m) { return i ^ ((i >> 4) & m); }
@@ -260,18 +263,19 @@ CHB_D void chf_pass_r(Grp &grp, cd *buf, int swm, int N, int L, int r, const cd 
 }
 // backward (SIGN +1) transform, spectrum Z[k] in slot rev[k]  ->  z[n] in slot n  (decimation in time)
 template <class Grp>
-CHB_D void chf_fft_spec_to_time(Grp &grp, cd *buf, const ChfLoop &L) {
+CHB_D void chf_fft_spec_to_time(Grp &grp, cd *buf, const ChfLoop &L, bool skip_first = false) {
     int len = 1;
     for (int s = L.nfac - 1; s >= 0; --s) {
         len *= L.fac[s];
+        if (skip_first && s == L.nfac - 1) continue;  // done by chf_load_pass
         chf_pass_r<+1, true>(grp, buf, L.swm, L.N, len, L.fac[s], L.tw[s]);
     }
 }
 // forward (SIGN -1) transform, g[n] in slot n  ->  Y[k] in slot rev[k]  (decimation in frequency)
 template <class Grp>
-CHB_D void chf_fft_time_to_spec(Grp &grp, cd *buf, const ChfLoop &L) {
+CHB_D void chf_fft_time_to_spec(Grp &grp, cd *buf, const ChfLoop &L, bool skip_last = false) {
     int len = L.N;
-    for (int s = 0; s < L.nfac; ++s) {
+    for (int s = 0; s < L.nfac - (skip_last ? 1 : 0); ++s) {  // the last pass is chf_store_pass when skipped
         chf_pass_r<-1, false>(grp, buf, L.swm, L.N, len, L.fac[s], L.tw[s]);
         len /= L.fac[s];
     }
@@ -360,6 +364,213 @@ CHB_D void chf_store_loop(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd 
         }
         if (want_kin) red[grp.g * T + tid] += 0.5 * kin;
     });
+}
+
+// ------------------------------------------------------------------------------------------------
+// v2: load / store fused into the Lp = 1 pass (the last factor R of the plan, a power of two).
+//
+// That pass works on butterflies "klo": spectral indices k = klo + q M, q = 0..R-1, M = N/R, which live in the R
+// consecutive slots rev[klo] .. rev[klo] + R - 1.  Rows k < npr = (R/2) M of the parameter vector are q < R/2; the upper
+// half q >= R/2 is the Hermitian mirror Z[N-k] of the rows (M - klo) + (R-1-q) M, i.e. of the direct rows of butterfly
+// M - klo.  Two adjacent lanes own the butterflies klo and M - klo, each reads its R/2 direct rows ONCE from global
+// memory (R/2 independent 32-byte loads in flight per thread), computes Z[k] for itself and Z[N-k] for its partner,
+// and the mirrors change lanes by warp shuffle.  klo = 0 (DC and Nyquist rows) and klo = M/2 are their own partners.
+// The store pass is the transpose: every lane sends the upper half of its butterfly output to its partner and stores
+// its R/2 direct rows with the Hermitian split, changevar_mom_pos_T and the kinetic term applied on the way out.
+// ------------------------------------------------------------------------------------------------
+template <int R>
+struct ChfXS {
+    cd a[R];
+    cd x[(R / 2) > 0 ? (R / 2) : 1];  // exchanged with lane ^ xm
+    int xm;
+    int klo;  // -1: idle lane
+    int base;
+};
+
+// 1 / k for a positive integer k: fp32 seed + two Newton steps (full fp64 accuracy, no special cases to branch on)
+CHB_HD double chf_rcp(int k) {
+#if defined(__CUDA_ARCH__)
+    const double d = (double)k;
+    const double x0 = (double)__frcp_rn((float)k);
+    double e = fma(-d, x0, 1.0);
+    const double x1 = fma(x0, e, x0);
+    e = fma(-d, x1, 1.0);
+    return fma(x1, e, x1);
+#else
+    return 1.0 / (double)k;
+#endif
+}
+
+CHB_HD int chf_pair_klo(int pr, int h, int M, int npairs) {
+    if (pr >= npairs) return -1;
+    if (pr == 0) return h == 0 ? 0 : ((M & 1) ? -1 : M / 2);
+    return h == 0 ? pr : M - pr;
+}
+
+template <int R, class Grp>
+CHB_D void chf_load_pass(Grp &grp, const ChfSys &F, const ChfLoop &L, const double *vec_b, cd *buf, double *red,
+                          bool want_kin) {
+    constexpr int H = R / 2;
+    const int M = L.N / R, npairs = (M + 1) / 2, half = grp.T / 2;
+    const double *rows = vec_b + L.mom_off - L.nco_in;
+    const double lm = L.loopmul / (double)L.ncm;
+    for (int p0 = 0; p0 < npairs; p0 += half) {
+        grp.template par_xchg<ChfXS<R>, H>(
+            [&](int tid, int T, ChfXS<R> &s) {
+                (void)T;
+                const int pr = p0 + (tid >> 1);
+                const int klo = chf_pair_klo(pr, tid & 1, M, npairs);
+                s.klo = klo;
+                s.xm = pr == 0 ? 0 : 1;
+                double p[H][4];
+#pragma unroll
+                for (int q = 0; q < H; ++q) {
+                    p[q][0] = p[q][1] = p[q][2] = p[q][3] = 0.0;
+                    if (klo > 0 || (klo == 0 && q > 0)) chf_load4(rows + 4LL * (klo + q * M), F.aligned16, p[q]);
+                }
+                s.base = klo >= 0 ? L.rev[klo] : 0;
+                double kin = 0.0;
+#pragma unroll
+                for (int q = 0; q < H; ++q) {
+                    const int k = klo + q * M;
+                    if (klo == 0 && q == 0) {
+                        // DC row: the c2r ignores Im of the zero-frequency term; removed parameters are zero
+                        const double c0 = L.co0 >= 0 ? vec_b[L.mom_off + L.co0] : 0.0;
+                        const double c2 = L.co2 >= 0 ? vec_b[L.mom_off + L.co2] : 0.0;
+                        s.a[q] = mk(c0 * L.loopmul, c2 * L.loopmul);
+                        s.x[q] = mk(0.0, 0.0);
+                    } else {
+                        const double sc = klo >= 0 ? lm * chf_rcp(k) : 0.0;
+                        kin += (p[q][0] * p[q][0] + p[q][1] * p[q][1]) + (p[q][2] * p[q][2] + p[q][3] * p[q][3]);
+                        // X0 = (p0 + i p1) sc, X1 = (p2 + i p3) sc ; Z[k] = X0 + i X1 ; Z[N-k] = conj(X0) + i conj(X1)
+                        s.a[q] = mk((p[q][0] - p[q][3]) * sc, (p[q][1] + p[q][2]) * sc);
+                        s.x[q] = mk((p[q][0] + p[q][3]) * sc, (p[q][2] - p[q][1]) * sc);
+                    }
+                }
+                if (want_kin) red[grp.g * grp.T + tid] += 0.5 * kin;
+            },
+            [&](int tid, int T, ChfXS<R> &s) {
+                (void)tid; (void)T;
+                if (s.klo < 0) return;
+                const bool dc = s.klo == 0;
+#pragma unroll
+                for (int q = H; q < R; ++q) {
+                    // mirror of row (R-1-q) of the partner butterfly; butterfly 0 pairs q with R - q and holds the Nyquist zero
+                    const cd gen = s.x[R - 1 - q];
+                    const cd spc = q == H ? mk(0.0, 0.0) : s.x[(R - q) < H ? (R - q) : 0];
+                    s.a[q] = dc ? spc : gen;
+                }
+                ChfDft<R, +1>::run(s.a);
+#pragma unroll
+                for (int t = 0; t < R; ++t) buf[chf_swz(s.base + t, L.swm)] = s.a[t];
+            });
+    }
+    grp.sync();
+}
+
+template <int R, class Grp>
+CHB_D void chf_store_pass(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd *buf, const double *kin_b, double *out_b,
+                           double *red, bool want_kin) {
+    constexpr int H = R / 2;
+    const int M = L.N / R, npairs = (M + 1) / 2, half = grp.T / 2;
+    const long long off = L.mom_off - L.nco_in;
+    const double lm = L.loopmul / (double)L.ncm;
+    for (int p0 = 0; p0 < npairs; p0 += half) {
+        grp.template par_xchg<ChfXS<R>, H>(
+            [&](int tid, int T, ChfXS<R> &s) {
+                (void)T;
+                const int pr = p0 + (tid >> 1);
+                const int klo = chf_pair_klo(pr, tid & 1, M, npairs);
+                s.klo = klo;
+                s.xm = pr == 0 ? 0 : 1;
+                s.base = klo >= 0 ? L.rev[klo] : 0;
+#pragma unroll
+                for (int q = 0; q < R; ++q) s.a[q] = klo >= 0 ? buf[chf_swz(s.base + q, L.swm)] : mk(0.0, 0.0);
+                ChfDft<R, -1>::run(s.a);  // a[t] = Y[klo + t M]
+                const bool dc = klo == 0;
+#pragma unroll
+                for (int t = 0; t < H; ++t) {
+                    // Y[N - (klo + t M)] is output R-1-t of butterfly M - klo (output R - t of butterfly 0)
+                    const cd gen = s.a[R - 1 - t];
+                    const cd spc = t == 0 ? mk(0.0, 0.0) : s.a[R - t];
+                    s.x[t] = dc ? spc : gen;
+                }
+            },
+            [&](int tid, int T, ChfXS<R> &s) {
+                (void)T;
+                const int klo = s.klo;
+                if (klo < 0) return;
+                double p[H][4];
+                if (kin_b) {
+#pragma unroll
+                    for (int t = 0; t < H; ++t) {
+                        p[t][0] = p[t][1] = p[t][2] = p[t][3] = 0.0;
+                        if (klo > 0 || t > 0) chf_load4(kin_b + off + 4LL * (klo + t * M), F.aligned16, p[t]);
+                    }
+                }
+                double kin = 0.0;
+#pragma unroll
+                for (int t = 0; t < H; ++t) {
+                    const int k = klo + t * M;
+                    const cd A = s.a[t], Bm = s.x[t];
+                    if (klo == 0 && t == 0) {
+                        // f = 1, Y_0[0] = Re, imaginary parts of the DC term get no gradient
+                        for (int c = 0; c < 4 - L.nco_in; ++c) out_b[L.mom_off + c] = 0.0;
+                        if (L.co0 >= 0) out_b[L.mom_off + L.co0] = A.x * L.loopmul;
+                        if (L.co2 >= 0) out_b[L.mom_off + L.co2] = A.y * L.loopmul;
+                    } else {
+                        const double sc = lm * chf_rcp(k);
+                        // Y_0 = (A + conj(Bm))/2, Y_1 = (A - conj(Bm))/(2i); the adjoint carries a factor 2 for k > 0
+                        double v[4] = {(A.x + Bm.x) * sc, (A.y - Bm.y) * sc, (A.y + Bm.y) * sc, (Bm.x - A.x) * sc};
+                        if (kin_b) {
+                            kin += (p[t][0] * p[t][0] + p[t][1] * p[t][1]) + (p[t][2] * p[t][2] + p[t][3] * p[t][3]);
+                            v[0] += p[t][0]; v[1] += p[t][1]; v[2] += p[t][2]; v[3] += p[t][3];
+                        }
+                        chf_store4(out_b + off + 4LL * k, F.aligned16, v);
+                    }
+                }
+                if (want_kin) red[grp.g * grp.T + tid] += 0.5 * kin;
+            });
+    }
+    grp.sync();
+}
+
+template <class Grp>
+CHB_D void chf_load_pass_r(Grp &grp, const ChfSys &F, const ChfLoop &L, const double *vec_b, cd *buf, double *red,
+                            bool want_kin) {
+    switch (L.fac[L.nfac - 1]) {
+        case 16: chf_load_pass<16>(grp, F, L, vec_b, buf, red, want_kin); break;
+        case 8: chf_load_pass<8>(grp, F, L, vec_b, buf, red, want_kin); break;
+        case 4: chf_load_pass<4>(grp, F, L, vec_b, buf, red, want_kin); break;
+        default: chf_load_pass<2>(grp, F, L, vec_b, buf, red, want_kin); break;
+    }
+}
+template <class Grp>
+CHB_D void chf_store_pass_r(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd *buf, const double *kin_b,
+                             double *out_b, double *red, bool want_kin) {
+    switch (L.fac[L.nfac - 1]) {
+        case 16: chf_store_pass<16>(grp, F, L, buf, kin_b, out_b, red, want_kin); break;
+        case 8: chf_store_pass<8>(grp, F, L, buf, kin_b, out_b, red, want_kin); break;
+        case 4: chf_store_pass<4>(grp, F, L, buf, kin_b, out_b, red, want_kin); break;
+        default: chf_store_pass<2>(grp, F, L, buf, kin_b, out_b, red, want_kin); break;
+    }
+}
+
+// ask L2 for the parameter rows of a later state (the CTA that will own it is not resident yet)
+CHB_D void chf_prefetch_l2(const double *base, long long first, long long count, const double *arr_end) {
+#if defined(__CUDA_ARCH__)
+    unsigned long long a0 = ((unsigned long long)(base + first)) & ~15ULL;
+    unsigned long long a1 = ((unsigned long long)(base + first + count)) & ~15ULL;
+    const unsigned long long lim = ((unsigned long long)arr_end) & ~15ULL;
+    if (a1 > lim) a1 = lim;
+    while (a0 < a1) {
+        const unsigned n = (unsigned)((a1 - a0) < 16384ULL ? (a1 - a0) : 16384ULL);
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(n) : "memory");
+        a0 += n;
+    }
+#else
+    (void)base; (void)first; (void)count; (void)arr_end;
+#endif
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -489,8 +700,18 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
         if (have_fwd) {
             const ChfLoop &L = F.loops[grp.g];
             cd *buf = sm + L.smem_off;
-            chf_load_loop(grp, F, L, vec_b, buf, red, A.kin_from == 1);
-            chf_fft_spec_to_time(grp, buf, L);
+            if (F.ver >= 2) {
+                chf_load_pass_r(grp, F, L, vec_b, buf, red, A.kin_from == 1);
+                if (F.pf_stride > 0 && b + F.pf_stride < A.nstates)
+                    grp.one([&]() {
+                        chf_prefetch_l2(A.vec_in + (b + F.pf_stride) * F.nparams, L.mom_off - L.nco_in, 4LL * L.npr,
+                                        A.vec_in + A.nstates * F.nparams);
+                    });
+                chf_fft_spec_to_time(grp, buf, L, true);
+            } else {
+                chf_load_loop(grp, F, L, vec_b, buf, red, A.kin_from == 1);
+                chf_fft_spec_to_time(grp, buf, L);
+            }
         }
     });
     chf_pair<NSEG, PMODE>(ctx, F, sm, have_fwd, seg_in_b, seg_out_b, red);
@@ -498,8 +719,13 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
         ctx.groups(F.nloop, F.T, [&](auto &grp) {
             const ChfLoop &L = F.loops[grp.g];
             cd *buf = sm + L.smem_off;
-            chf_fft_time_to_spec(grp, buf, L);
-            chf_store_loop(grp, F, L, buf, kin_b, out_b, red, A.kin_from == 2);
+            if (F.ver >= 2) {
+                chf_fft_time_to_spec(grp, buf, L, true);
+                chf_store_pass_r(grp, F, L, buf, kin_b, out_b, red, A.kin_from == 2);
+            } else {
+                chf_fft_time_to_spec(grp, buf, L);
+                chf_store_loop(grp, F, L, buf, kin_b, out_b, red, A.kin_from == 2);
+            }
         });
     }
     if (A.scalar_out) {

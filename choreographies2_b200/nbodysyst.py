@@ -113,8 +113,11 @@ class NBodySystB200:
         L.check(self._lib, self._lib.chb_plan_set_chunk(self._plan, int(chunk)))
         self._ws = None
 
-    def set_fused(self, enable: bool) -> None:
-        L.check(self._lib, self._lib.chb_plan_set_fused(self._plan, int(bool(enable))))
+    def set_fused(self, enable) -> None:
+        """False/0: generic staged kernels only; True/2: fused kernel (default); 1: fused kernel with separate
+        load/store phases (kept for A/B measurements)."""
+        level = 2 if enable is True else int(enable)
+        L.check(self._lib, self._lib.chb_plan_set_fused(self._plan, level))
 
     # ------------------------------------------------------------------ plumbing
     def _check(self, arr, last_shape, what: str):

@@ -131,7 +131,8 @@ int chb_plan_destroy(chb_plan *plan);
 int chb_plan_query(const chb_plan *plan, int what, int64_t *value_out);
 /* 0 = auto; otherwise number of states per internal launch group (L2 residency knob) */
 int chb_plan_set_chunk(chb_plan *plan, int64_t chunk);
-/* 0 = generic staged kernels only, 1 = allow the fused kernel when the layout supports it (default) */
+/* 0 = generic staged kernels only; 2 = fused kernel when the layout supports it (default): parameter load and result
+ * store are part of the first / last FFT pass; 1 = same kernel with separate load / store phases (A/B measurements) */
 int chb_plan_set_fused(chb_plan *plan, int enable);
 
 /* bytes of device workspace any *_dev operator below needs for `batch` states */
