@@ -17,7 +17,7 @@ HEADERS = ["chb_core.cuh", "chb_fused.cuh", os.path.join("..", "..", "include", 
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared", "-Xptxas=-v",
+    "-Xcompiler", "-fPIC", "-shared", "-Xptxas=-v", "-split-compile=0",
 ]
 
 

@@ -442,6 +442,19 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
         P.fac = T.bin_fac[b];
         for (int i = 0; i < 4; ++i) P.rot[i] = T.bin_rot[(size_t)b * 4 + i];
     }
+    {   // common layout served by chf_pair_fast
+        bool fast = T.law == 0;
+        for (int s = 0; s < T.nsegm && fast; ++s) {
+            const ChfSeg &sg = F.segs[s];
+            const ChfLoop &FL = F.loops[sg.loop];
+            fast = sg.isid && sg.timerev > 0 && (FL.swm == 0 || segm_size % 256 == 0);
+            for (int t = 0; t < T.nsegm && fast; ++t) {
+                const ChfPair &P = F.pairs[s * CHF_MAX_SEGS + t];
+                fast = t > s ? (P.on && P.isid) : !P.on;
+            }
+        }
+        F.pair_fast = fast ? 1 : 0;
+    }
     // threads: one group per loop, about one radix-16 butterfly pair per thread and pass
     int Tg = ((maxN / 32 + 31) / 32) * 32;
     int cap = (CHF_MAX_THREADS / T.nloop) / 32 * 32;

@@ -52,6 +52,7 @@ struct ChfSys {
     int nloop, nseg, T, segm_size;
     int aligned16, law_kind;
     int ver;        // 2: parameter load / result store fused into the first / last FFT pass (lane-pair exchange), 1: separate phases
+    int pair_fast;  // gravity, every pair s < t interacts once with identity rotation, segments are plain slices
     int pf_stride;  // > 0: CTA b asks L2 for the parameters of state b + pf_stride while it computes (co-resident CTA count)
     long long nparams, segsz;
     double law[4];
@@ -287,8 +288,9 @@ CHB_D void chf_fft_time_to_spec(Grp &grp, cd *buf, const ChfLoop &L, bool skip_l
 CHB_HD void chf_load4(const double *p, int aligned16, double *v) {
 #if defined(__CUDA_ARCH__)
     if (aligned16) {
-        const double2 a = __ldg((const double2 *)p), b = __ldg((const double2 *)(p + 2));
-        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+        // streamed once: keep the small L1 (228 KB - shared memory) for the twiddle tables
+        asm("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(v[0]), "=d"(v[1]) : "l"(p));
+        asm("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(v[2]), "=d"(v[3]) : "l"(p + 2));
         return;
     }
 #endif
@@ -387,17 +389,30 @@ struct ChfXS {
     int base;
 };
 
-// 1 / k for a positive integer k: fp32 seed + two Newton steps (full fp64 accuracy, no special cases to branch on)
-CHB_HD double chf_rcp(int k) {
+// 1 / d for a normal positive d: hardware seed (MUFU.RCP64H, about 20 bits) + two Newton steps; no special cases
+CHB_HD double chf_rcp(double d) {
 #if defined(__CUDA_ARCH__)
-    const double d = (double)k;
-    const double x0 = (double)__frcp_rn((float)k);
+    double x0;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x0) : "d"(d));
     double e = fma(-d, x0, 1.0);
     const double x1 = fma(x0, e, x0);
     e = fma(-d, x1, 1.0);
     return fma(x1, e, x1);
 #else
-    return 1.0 / (double)k;
+    return 1.0 / d;
+#endif
+}
+// d^(-1/2) for a normal positive d: hardware seed (MUFU.RSQ64H) + two Newton steps
+CHB_HD double chf_rsqrt(double d) {
+#if defined(__CUDA_ARCH__)
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+    double e = fma(-d * y, y, 1.0);
+    y = fma(y * e, fma(e, 0.375, 0.5), y);
+    e = fma(-d * y, y, 1.0);
+    return fma(y * e, 0.5, y);
+#else
+    return 1.0 / sqrt(d);
 #endif
 }
 
@@ -413,7 +428,7 @@ CHB_D void chf_load_pass(Grp &grp, const ChfSys &F, const ChfLoop &L, const doub
     constexpr int H = R / 2;
     const int M = L.N / R, npairs = (M + 1) / 2, half = grp.T / 2;
     const double *rows = vec_b + L.mom_off - L.nco_in;
-    const double lm = L.loopmul / (double)L.ncm;
+    const double lm = L.loopmul / (double)L.ncm, dM = (double)M;
     for (int p0 = 0; p0 < npairs; p0 += half) {
         grp.template par_xchg<ChfXS<R>, H>(
             [&](int tid, int T, ChfXS<R> &s) {
@@ -430,9 +445,9 @@ CHB_D void chf_load_pass(Grp &grp, const ChfSys &F, const ChfLoop &L, const doub
                 }
                 s.base = klo >= 0 ? L.rev[klo] : 0;
                 double kin = 0.0;
+                const double dklo = (double)klo;
 #pragma unroll
                 for (int q = 0; q < H; ++q) {
-                    const int k = klo + q * M;
                     if (klo == 0 && q == 0) {
                         // DC row: the c2r ignores Im of the zero-frequency term; removed parameters are zero
                         const double c0 = L.co0 >= 0 ? vec_b[L.mom_off + L.co0] : 0.0;
@@ -440,7 +455,7 @@ CHB_D void chf_load_pass(Grp &grp, const ChfSys &F, const ChfLoop &L, const doub
                         s.a[q] = mk(c0 * L.loopmul, c2 * L.loopmul);
                         s.x[q] = mk(0.0, 0.0);
                     } else {
-                        const double sc = klo >= 0 ? lm * chf_rcp(k) : 0.0;
+                        const double sc = klo >= 0 ? lm * chf_rcp(fma((double)q, dM, dklo)) : 0.0;
                         kin += (p[q][0] * p[q][0] + p[q][1] * p[q][1]) + (p[q][2] * p[q][2] + p[q][3] * p[q][3]);
                         // X0 = (p0 + i p1) sc, X1 = (p2 + i p3) sc ; Z[k] = X0 + i X1 ; Z[N-k] = conj(X0) + i conj(X1)
                         s.a[q] = mk((p[q][0] - p[q][3]) * sc, (p[q][1] + p[q][2]) * sc);
@@ -474,7 +489,7 @@ CHB_D void chf_store_pass(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd 
     constexpr int H = R / 2;
     const int M = L.N / R, npairs = (M + 1) / 2, half = grp.T / 2;
     const long long off = L.mom_off - L.nco_in;
-    const double lm = L.loopmul / (double)L.ncm;
+    const double lm = L.loopmul / (double)L.ncm, dM = (double)M;
     for (int p0 = 0; p0 < npairs; p0 += half) {
         grp.template par_xchg<ChfXS<R>, H>(
             [&](int tid, int T, ChfXS<R> &s) {
@@ -509,6 +524,7 @@ CHB_D void chf_store_pass(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd 
                     }
                 }
                 double kin = 0.0;
+                const double dklo = (double)klo;
 #pragma unroll
                 for (int t = 0; t < H; ++t) {
                     const int k = klo + t * M;
@@ -519,7 +535,7 @@ CHB_D void chf_store_pass(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd 
                         if (L.co0 >= 0) out_b[L.mom_off + L.co0] = A.x * L.loopmul;
                         if (L.co2 >= 0) out_b[L.mom_off + L.co2] = A.y * L.loopmul;
                     } else {
-                        const double sc = lm * chf_rcp(k);
+                        const double sc = lm * chf_rcp(fma((double)t, dM, dklo));
                         // Y_0 = (A + conj(Bm))/2, Y_1 = (A - conj(Bm))/(2i); the adjoint carries a factor 2 for k > 0
                         double v[4] = {(A.x + Bm.x) * sc, (A.y - Bm.y) * sc, (A.y + Bm.y) * sc, (Bm.x - A.x) * sc};
                         if (kin_b) {
@@ -684,6 +700,82 @@ CHB_D void chf_pair(Ctx &ctx, const ChfSys &F, cd *sm, bool have_fwd, const doub
     });
 }
 
+// Pair phase of the common layout (F.pair_fast): gravity, one interaction per unordered segment pair, no rotations.
+// V = -r, V' = r^3 / 2, V'' = -3 r^5 / 4 with r = (x^2)^(-1/2) (inline_gravity_pot, :111-118, in closed form), so a pair
+// sample costs one rsqrt and ~17 fp64 instructions; the interaction weights sit in registers for the whole phase.
+template <int NSEG, int PMODE, class Ctx>
+CHB_D void chf_pair_fast(Ctx &ctx, const ChfSys &F, cd *sm, bool have_fwd, const double *seg_in_b, double *seg_out_b,
+                          double *red) {
+    ctx.par([&](int tid, int nthr) {
+        const int size = F.segm_size;
+        const double inv_size = 1.0 / (double)size;
+        double w[NSEG][NSEG];
+        int off[NSEG], swm[NSEG];
+#pragma unroll
+        for (int s = 0; s < NSEG; ++s) {
+            const ChfLoop &L = F.loops[F.segs[s].loop];
+            off[s] = L.smem_off + F.segs[s].row0;  // row0 is a multiple of segm_size: the swizzle acts on i alone when
+            swm[s] = L.swm;                        // segm_size % 256 == 0, which pair_fast requires with a swizzle
+#pragma unroll
+            for (int t = 0; t < NSEG; ++t) w[s][t] = t > s ? F.pairs[s * CHF_MAX_SEGS + t].fac * inv_size : 0.0;
+        }
+        double e = 0.0;
+        for (int i = tid; i < size; i += nthr) {
+            cd x[NSEG], dx[NSEG], g[NSEG];
+            int slot[NSEG];
+#pragma unroll
+            for (int s = 0; s < NSEG; ++s) {
+                slot[s] = off[s] + chf_swz(i, swm[s]);
+                cd v = mk(0.0, 0.0);
+                if (have_fwd) v = sm[slot[s]];
+                if (PMODE == 2) {
+                    dx[s] = v;
+                    x[s] = ((const cd *)seg_in_b)[(long long)s * size + i];
+                } else {
+                    x[s] = seg_in_b ? ((const cd *)seg_in_b)[(long long)s * size + i] : v;
+                    dx[s] = mk(0.0, 0.0);
+                }
+                if (seg_out_b) ((cd *)seg_out_b)[(long long)s * size + i] = v;
+                g[s] = mk(0.0, 0.0);
+            }
+            if (PMODE != 3) {
+#pragma unroll
+                for (int s = 0; s < NSEG; ++s) {
+#pragma unroll
+                    for (int t = s + 1; t < NSEG; ++t) {
+                        const cd d = csub(x[s], x[t]);
+                        const double r = chf_rsqrt(fma(d.x, d.x, d.y * d.y));
+                        if (PMODE <= 1) e = fma(w[s][t], r, e);
+                        if (PMODE >= 1) {
+                            const double r2 = r * r;
+                            const double c = w[s][t] * (r2 * r);
+                            if (PMODE == 1) {  // -2 w V' d = -w r^3 d on the source, + on the target
+                                g[s].x = fma(-c, d.x, g[s].x);
+                                g[s].y = fma(-c, d.y, g[s].y);
+                                g[t].x = fma(c, d.x, g[t].x);
+                                g[t].y = fma(c, d.y, g[t].y);
+                            } else {  // -2 w (2 V'' (d.dd) d + V' dd) = w r^3 (3 r^2 (d.dd) d - dd)
+                                const cd dd = csub(dx[s], dx[t]);
+                                const double k3 = 3.0 * r2 * fma(d.x, dd.x, d.y * dd.y);
+                                const double hx = c * fma(k3, d.x, -dd.x), hy = c * fma(k3, d.y, -dd.y);
+                                g[s].x += hx;
+                                g[s].y += hy;
+                                g[t].x -= hx;
+                                g[t].y -= hy;
+                            }
+                        }
+                    }
+                }
+            }
+            if (PMODE == 1 || PMODE == 2) {
+#pragma unroll
+                for (int s = 0; s < NSEG; ++s) sm[slot[s]] = g[s];
+            }
+        }
+        if (PMODE <= 1) red[tid] += e;  // - potential
+    });
+}
+
 // ------------------------------------------------------------------------------------------------
 // the CTA program
 // ------------------------------------------------------------------------------------------------
@@ -714,7 +806,10 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
             }
         }
     });
-    chf_pair<NSEG, PMODE>(ctx, F, sm, have_fwd, seg_in_b, seg_out_b, red);
+    if (F.pair_fast)
+        chf_pair_fast<NSEG, PMODE>(ctx, F, sm, have_fwd, seg_in_b, seg_out_b, red);
+    else
+        chf_pair<NSEG, PMODE>(ctx, F, sm, have_fwd, seg_in_b, seg_out_b, red);
     if (out_b) {
         ctx.groups(F.nloop, F.T, [&](auto &grp) {
             const ChfLoop &L = F.loops[grp.g];
