@@ -70,7 +70,8 @@ struct chb_plan {
     std::vector<ChbLoop> h_loops;      // host mirror (device pointers inside)
     ChbSys sys;                        // passed by value to kernels
     int64_t chunk_user = 0;
-    int fused_enabled = 2;  // 0 staged kernels only, 1 fused v1 (separate load/store phases), 2 fused v2
+    int fused_enabled = 3;  // 0 staged kernels only, 1 fused v1 (separate load/store phases), 2 fused v2, 3 fused v3
+    int fused_resident = 148;
     int fused_active = 0;
     int64_t launches = 0;
     size_t smem_limit = 0;  // max dynamic shared memory per block (opt-in)
@@ -467,7 +468,21 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
     {   // co-resident CTAs = distance (in states) of the L2 prefetch
         const size_t per_cta = p->fused_smem + 1024;
         int occ = (int)std::min<size_t>((size_t)(228 * 1024) / per_cta, (size_t)(2048 / p->fused_threads));
-        F.pf_stride = std::max(1, occ) * p->num_sms;
+        occ = std::max(1, std::min(occ, 32));
+        F.pf_stride = occ * p->num_sms;
+        p->fused_resident = occ * p->num_sms;
+        // tensor-memory stash of ver 3: 8 words per parameter row, R/2 rows per butterfly, one butterfly per pair iteration
+        int cols_thread = 0;
+        for (int il = 0; il < T.nloop; ++il) {
+            const ChfLoop &FL = F.loops[il];
+            const int R = FL.fac[FL.nfac - 1], M = FL.N / R, npairs = (M + 1) / 2, half = Tg / 2;
+            cols_thread = std::max(cols_thread, ((npairs + half - 1) / half) * 4 * R);
+        }
+        const int blocks = (p->fused_threads / 32 + 3) / 4;
+        int cols = 32;
+        while (cols < blocks * cols_thread) cols *= 2;
+        F.tmem_thread_cols = cols_thread;
+        F.tmem_cols = (cols <= 512 && occ * cols <= 512 && cols_thread <= 512) ? cols : 0;
     }
     // tables, shared between loops of equal length
     for (int il = 0; il < T.nloop; ++il) {
@@ -818,7 +833,11 @@ extern "C" int chb_plan_set_chunk(chb_plan *p, int64_t chunk) {
 }
 extern "C" int chb_plan_set_fused(chb_plan *p, int enable) {
     CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_fused: NULL plan");
-    p->fused_enabled = enable < 0 ? 0 : (enable > 2 ? 2 : enable);
+    #ifdef CHF_KEEP_OLD
+    p->fused_enabled = enable < 0 ? 0 : (enable > 3 ? 3 : enable);
+#else
+    p->fused_enabled = enable > 0 ? 3 : 0;  // the older fused variants (1, 2) are compiled only with -DCHF_KEEP_OLD
+#endif
     return CHB_OK;
 }
 
@@ -874,8 +893,59 @@ extern "C" int chb_workspace_bytes(const chb_plan *p, int64_t batch, size_t *out
 // kernels (GPU) / block loops (hostsim)
 // ------------------------------------------------------------------------------------------------
 #ifndef CHB_HOSTSIM
+// tensor-memory stash: ND doubles of this thread <-> columns [col, col + 2 ND) of its lane (warp-collective)
+template <int ND>
+__device__ __forceinline__ void dev_tmem_st(unsigned taddr, const double *v) {
+#pragma unroll
+    for (int i = 0; i < ND; i += 4) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr + 2 * i),
+                     "r"(__double2loint(v[i])), "r"(__double2hiint(v[i])), "r"(__double2loint(v[i + 1])),
+                     "r"(__double2hiint(v[i + 1])), "r"(__double2loint(v[i + 2])), "r"(__double2hiint(v[i + 2])),
+                     "r"(__double2loint(v[i + 3])), "r"(__double2hiint(v[i + 3]))
+                     : "memory");
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+template <int ND>
+__device__ __forceinline__ void dev_tmem_ld(unsigned taddr, double *v) {
+    unsigned w[2 * ND];
+#pragma unroll
+    for (int i = 0; i < ND; i += 4) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=r"(w[2 * i]), "=r"(w[2 * i + 1]), "=r"(w[2 * i + 2]), "=r"(w[2 * i + 3]), "=r"(w[2 * i + 4]),
+                       "=r"(w[2 * i + 5]), "=r"(w[2 * i + 6]), "=r"(w[2 * i + 7])
+                     : "r"(taddr + 2 * i)
+                     : "memory");
+    }
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < ND; ++i) v[i] = __hiloint2double((int)w[2 * i + 1], (int)w[2 * i]);
+}
 struct DevGrp {
     int g, T;
+    unsigned taddr;  // tensor-memory address of this thread's stash (lane quarter of its warp, column block of warp / 4)
+    template <int ND>
+    __device__ __forceinline__ void tmem_st(int col, const double *v) { dev_tmem_st<ND>(taddr + (unsigned)col, v); }
+    template <int ND>
+    __device__ __forceinline__ void tmem_ld(int col, double *v) { dev_tmem_ld<ND>(taddr + (unsigned)col, v); }
+    template <class S, int NX, class F1, class F2, class F3>
+    __device__ __forceinline__ void par_xchg2(F1 f1, F2 f2, F3 f3) {
+        S s;
+        const int tid = (int)threadIdx.x - g * T;
+        f1(tid, T, s);
+#pragma unroll
+        for (int i = 0; i < NX; ++i) {
+            s.x[i].x = __shfl_xor_sync(0xffffffffu, s.x[i].x, s.xm);
+            s.x[i].y = __shfl_xor_sync(0xffffffffu, s.x[i].y, s.xm);
+        }
+        f2(tid, T, s);
+#pragma unroll
+        for (int i = 0; i < NX; ++i) {
+            s.x[i].x = __shfl_xor_sync(0xffffffffu, s.x[i].x, s.xm);
+            s.x[i].y = __shfl_xor_sync(0xffffffffu, s.x[i].y, s.xm);
+        }
+        f3(tid, T, s);
+    }
     // phase of one thread group: the group's own named barrier, so groups drift apart and overlap each other
     template <class F>
     __device__ __forceinline__ void par(F f) {
@@ -903,6 +973,7 @@ struct DevGrp {
     }
 };
 struct DevCtx {
+    unsigned tmem_thread;
     template <class F>
     __device__ __forceinline__ void par(F f) {
         f((int)threadIdx.x, (int)blockDim.x);
@@ -912,7 +983,7 @@ struct DevCtx {
     template <class F>
     __device__ __forceinline__ void groups(int ngroups, int T, F f) {
         (void)ngroups;
-        DevGrp grp{(int)threadIdx.x / T, T};
+        DevGrp grp{(int)threadIdx.x / T, T, tmem_thread};
         f(grp);
         __syncthreads();
     }
@@ -921,11 +992,38 @@ extern __shared__ __align__(16) unsigned char chb_smem_raw[];
 #define CHB_KERNEL __global__
 #define CHB_BLOCK_ID ((long long)blockIdx.x)
 #define CHB_NTHREADS ((int)blockDim.x)
-#define CHB_CTX_DECL DevCtx ctx
+#define CHB_CTX_DECL DevCtx ctx{0u}
+#define CHB_GRID_DIM ((long long)gridDim.x)
 #define CHB_SMEM chb_smem_raw
 #else
 struct HostGrp {
     int g, T;
+    std::vector<double> *tmem;  // emulated tensor-memory stash, CHF_MAX_THREADS x 256 doubles
+    int tmem_tid;               // thread currently running (set by par_xchg2)
+    template <int ND>
+    void tmem_st(int col, const double *v) {
+        for (int i = 0; i < ND; ++i) (*tmem)[(size_t)(g * T + tmem_tid) * 256 + col / 2 + i] = v[i];
+    }
+    template <int ND>
+    void tmem_ld(int col, double *v) {
+        for (int i = 0; i < ND; ++i) v[i] = (*tmem)[(size_t)(g * T + tmem_tid) * 256 + col / 2 + i];
+    }
+    template <class S, int NX, class F1, class F2, class F3>
+    void par_xchg2(F1 f1, F2 f2, F3 f3) {
+        std::vector<S> st((size_t)T);
+        auto xchg = [&]() {
+            for (int t = 0; t < T; ++t) {
+                const int u = t ^ st[t].xm;
+                if (u > t)
+                    for (int i = 0; i < NX; ++i) std::swap(st[t].x[i], st[u].x[i]);
+            }
+        };
+        for (int t = 0; t < T; ++t) { tmem_tid = t; f1(t, T, st[t]); }
+        xchg();
+        for (int t = 0; t < T; ++t) { tmem_tid = t; f2(t, T, st[t]); }
+        xchg();
+        for (int t = 0; t < T; ++t) { tmem_tid = t; f3(t, T, st[t]); }
+    }
     template <class F>
     void par(F f) {
         for (int t = 0; t < T; ++t) f(t, T);
@@ -947,6 +1045,7 @@ struct HostGrp {
 };
 struct HostCtx {
     int nthr;
+    std::vector<double> tmem;  // emulated tensor memory, sized by k_fused
     template <class F>
     void par(F f) {
         for (int t = 0; t < nthr; ++t) f(t, nthr);
@@ -954,16 +1053,18 @@ struct HostCtx {
     template <class F>
     void groups(int ngroups, int T, F f) {
         for (int g = 0; g < ngroups; ++g) {
-            HostGrp grp{g, T};
+            HostGrp grp{g, T, &tmem, 0};
             f(grp);
         }
     }
 };
 static thread_local long long sim_block_id;
+static thread_local long long sim_grid_dim;
 static thread_local int sim_nthreads;
 static thread_local unsigned char *sim_smem;
 #define CHB_KERNEL static
 #define CHB_BLOCK_ID sim_block_id
+#define CHB_GRID_DIM sim_grid_dim
 #define CHB_NTHREADS sim_nthreads
 #define CHB_CTX_DECL HostCtx ctx{sim_nthreads}
 #define CHB_SMEM sim_smem
@@ -1044,7 +1145,37 @@ CHB_KERNEL void k_finish(double *out, const double *kin_part, int nk, const doub
 template <int NSEG, int PMODE>
 CHB_KERNEL void CHF_BOUNDS k_fused(ChfSys F, ChfArgs A) {
     CHB_CTX_DECL;
-    cta_fused<NSEG, PMODE>(ctx, F, A, CHB_BLOCK_ID, (double *)CHB_SMEM, (cd *)(CHB_SMEM + CHF_RED_BYTES));
+    const bool use_tmem = F.ver >= 3 && F.tmem_cols > 0;
+#ifndef CHB_HOSTSIM
+    __shared__ unsigned tmem_base_s;
+    unsigned tmem_base = 0;
+    if (use_tmem) {  // one warp allocates the columns, everybody reads the base address after a fenced barrier
+        if (threadIdx.x < 32) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             (unsigned)__cvta_generic_to_shared(&tmem_base_s)), "r"((unsigned)F.tmem_cols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        tmem_base = tmem_base_s;
+        const unsigned warp = threadIdx.x >> 5;
+        ctx.tmem_thread = tmem_base + (((warp & 3u) * 32u) << 16) + (warp >> 2) * (unsigned)F.tmem_thread_cols;
+    }
+#else
+    if (use_tmem) ctx.tmem.assign((size_t)CHF_MAX_THREADS * 256, 0.0);
+#endif
+    // persistent CTAs: the grid is one resident wave, every CTA walks the batch with the grid stride
+    for (long long b = CHB_BLOCK_ID; b < A.nstates; b += CHB_GRID_DIM)
+        cta_fused<NSEG, PMODE>(ctx, F, A, b, (double *)CHB_SMEM, (cd *)(CHB_SMEM + CHF_RED_BYTES));
+#ifndef CHB_HOSTSIM
+    if (use_tmem) {
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x < 32)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((unsigned)F.tmem_cols) : "memory");
+    }
+#endif
 }
 
 #ifndef CHB_HOSTSIM
@@ -1064,6 +1195,7 @@ CHB_KERNEL void CHF_BOUNDS k_fused(ChfSys F, ChfArgs A) {
         sim_smem = smem_buf_.data();                                    \
         sim_smem += (16 - ((uintptr_t)sim_smem & 15)) & 15;             \
         sim_nthreads = (int)(block);                                    \
+        sim_grid_dim = (long long)(grid);                               \
         for (long long blk_ = 0; blk_ < (long long)(grid); ++blk_) {    \
             sim_block_id = blk_;                                        \
             kern(__VA_ARGS__);                                          \
@@ -1152,6 +1284,14 @@ static int launch_fused(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A0, c
     ChfArgs A = A0;
     A.nstates = nb;
     p->fsys.ver = p->fused_enabled;
+    const int64_t nb_states = nb;
+    if (p->fused_enabled >= 3) nb = std::min<int64_t>(nb, (int64_t)p->fused_resident);  // persistent grid = one resident wave
+    p->fsys.pf_stride = (int)std::min<int64_t>(nb, (int64_t)p->fused_resident);
+    (void)nb_states;
+    {
+        const char *dbg = getenv("CHB_FUSED_DBG");  // profiling only: results are wrong when phases are skipped
+        p->fsys.dbg = dbg ? atoi(dbg) : 0;
+    }
     switch (p->fsys.nseg) {
         case 1: return launch_fused_n<1>(p, pmode, nb, A, st);
         case 2: return launch_fused_n<2>(p, pmode, nb, A, st);

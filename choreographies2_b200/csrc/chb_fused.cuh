@@ -51,7 +51,11 @@ struct ChfPair {
 struct ChfSys {
     int nloop, nseg, T, segm_size;
     int aligned16, law_kind;
-    int ver;        // 2: parameter load / result store fused into the first / last FFT pass (lane-pair exchange), 1: separate phases
+    int tmem_cols;  // > 0: tensor-memory columns each CTA allocates for the parameter-row stash of ver 3 (power of two >= 32)
+    int tmem_thread_cols;  // columns per thread (pair iterations * 4 R), threads of warp w use block w / 4 of their lane quarter
+    int ver;        // 3: ver 2 + half-row coalescing of every global access + rows stashed in tensor memory for the kinetic term;
+                    // 2: parameter load / result store fused into the first / last FFT pass (lane-pair exchange), 1: separate phases
+    int dbg;        // profiling only (env CHB_FUSED_DBG): bit 0..5 skip load pass / inverse passes / pair / forward passes / store pass / reduce
     int pair_fast;  // gravity, every pair s < t interacts once with identity rotation, segments are plain slices
     int pf_stride;  // > 0: CTA b asks L2 for the parameters of state b + pf_stride while it computes (co-resident CTA count)
     long long nparams, segsz;
@@ -551,25 +555,251 @@ CHB_D void chf_store_pass(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd 
     grp.sync();
 }
 
+// ------------------------------------------------------------------------------------------------
+// v3: same pass structure as v2, but (measured with tools/memphase_bench.cu: 32-byte rows at a 32-byte lane stride
+// move at 2.8 TB/s, contiguous 16-byte lanes at 4.5 TB/s)
+//   * every global access is a HALF row per lane: the two lanes of a pair share each row (lane h reads / writes
+//     doubles 2h, 2h+1), so a warp-level instruction covers contiguous 512-byte runs; a second shuffle exchange moves
+//     the halves to the lane that owns the row;
+//   * the parameter rows a thread has loaded are parked in TENSOR MEMORY (tcgen05.st, 64 columns per butterfly) and
+//     read back by the same thread in the store pass for the kinetic term (tcgen05.ld): the rows are neither re-read
+//     from L2 nor kept in registers across the transforms.  Blackwell's 256 KB of TMEM per SM is otherwise idle here.
+// ------------------------------------------------------------------------------------------------
+CHB_HD void chf_pair_rows(int pr, int M, int npairs, int *ka, int *kb) {
+    *ka = chf_pair_klo(pr, 0, M, npairs);
+    *kb = chf_pair_klo(pr, 1, M, npairs);
+}
+CHB_HD void chf_load2(const double *p, int aligned16, cd *v) {
+#if defined(__CUDA_ARCH__)
+    if (aligned16) {
+        asm("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(v->x), "=d"(v->y) : "l"(p));
+        return;
+    }
+#endif
+    (void)aligned16;
+    *v = mk(p[0], p[1]);
+}
+CHB_HD void chf_store2(double *p, int aligned16, cd v) {
+#if defined(__CUDA_ARCH__)
+    if (aligned16) {
+        *(double2 *)p = v;
+        return;
+    }
+#endif
+    (void)aligned16;
+    p[0] = v.x; p[1] = v.y;
+}
+
+template <int R, class Grp>
+CHB_D void chf_load_pass3(Grp &grp, const ChfSys &F, const ChfLoop &L, const double *vec_b, cd *buf, double *red,
+                           bool want_kin, bool stash) {
+    constexpr int H = R / 2;
+    const int M = L.N / R, npairs = (M + 1) / 2, half = grp.T / 2;
+    const double *rows = vec_b + L.mom_off - L.nco_in;
+    const double lm = L.loopmul / (double)L.ncm, dM = (double)M;
+    int it = 0;
+    for (int p0 = 0; p0 < npairs; p0 += half, ++it) {
+        grp.template par_xchg2<ChfXS<R>, H>(
+            [&](int tid, int T, ChfXS<R> &s) {  // half rows of both butterflies of the pair
+                (void)T;
+                const int pr = p0 + (tid >> 1), h = tid & 1;
+                int ka, kb;
+                chf_pair_rows(pr, M, npairs, &ka, &kb);
+                cd u[H], w[H];
+#pragma unroll
+                for (int q = 0; q < H; ++q) {
+                    u[q] = w[q] = mk(0.0, 0.0);
+                    if (ka > 0 || (ka == 0 && q > 0)) chf_load2(rows + 4LL * (ka + q * M) + 2 * h, F.aligned16, &u[q]);
+                    if (kb > 0) chf_load2(rows + 4LL * (kb + q * M) + 2 * h, F.aligned16, &w[q]);
+                }
+#pragma unroll
+                for (int q = 0; q < H; ++q) {
+                    s.a[q] = h == 0 ? u[q] : w[q];  // half of the own row
+                    s.x[q] = h == 0 ? w[q] : u[q];  // half of the partner's row
+                }
+                s.klo = h == 0 ? ka : kb;
+                s.xm = 1;
+            },
+            [&](int tid, int T, ChfXS<R> &s) {  // whole own rows: stash, spectrum values for this butterfly and its mirror
+                (void)T;
+                const int pr = p0 + (tid >> 1), h = tid & 1;
+                const int klo = s.klo;
+                double p[H][4];
+#pragma unroll
+                for (int q = 0; q < H; ++q) {
+                    const cd lo = h == 0 ? s.a[q] : s.x[q], hi = h == 0 ? s.x[q] : s.a[q];
+                    p[q][0] = lo.x; p[q][1] = lo.y; p[q][2] = hi.x; p[q][3] = hi.y;
+                }
+                if (stash) grp.template tmem_st<4 * H>(it * 8 * H, &p[0][0]);
+                s.base = klo >= 0 ? L.rev[klo] : 0;
+                double kin = 0.0;
+                const double dklo = (double)klo;
+#pragma unroll
+                for (int q = 0; q < H; ++q) {
+                    if (klo == 0 && q == 0) {
+                        const double c0 = L.co0 >= 0 ? vec_b[L.mom_off + L.co0] : 0.0;
+                        const double c2 = L.co2 >= 0 ? vec_b[L.mom_off + L.co2] : 0.0;
+                        s.a[q] = mk(c0 * L.loopmul, c2 * L.loopmul);
+                        s.x[q] = mk(0.0, 0.0);
+                    } else {
+                        const double sc = klo >= 0 ? lm * chf_rcp(fma((double)q, dM, dklo)) : 0.0;
+                        kin += (p[q][0] * p[q][0] + p[q][1] * p[q][1]) + (p[q][2] * p[q][2] + p[q][3] * p[q][3]);
+                        s.a[q] = mk((p[q][0] - p[q][3]) * sc, (p[q][1] + p[q][2]) * sc);
+                        s.x[q] = mk((p[q][0] + p[q][3]) * sc, (p[q][2] - p[q][1]) * sc);
+                    }
+                }
+                if (want_kin && klo >= 0) red[grp.g * grp.T + tid] += 0.5 * kin;
+                s.xm = pr == 0 ? 0 : 1;
+            },
+            [&](int tid, int T, ChfXS<R> &s) {
+                (void)tid; (void)T;
+                if (s.klo < 0) return;
+                const bool dc = s.klo == 0;
+#pragma unroll
+                for (int q = H; q < R; ++q) {
+                    const cd gen = s.x[R - 1 - q];
+                    const cd spc = q == H ? mk(0.0, 0.0) : s.x[(R - q) < H ? (R - q) : 0];
+                    s.a[q] = dc ? spc : gen;
+                }
+                ChfDft<R, +1>::run(s.a);
+#pragma unroll
+                for (int t = 0; t < R; ++t) buf[chf_swz(s.base + t, L.swm)] = s.a[t];
+            });
+    }
+    grp.sync();
+}
+
+template <int R, class Grp>
+CHB_D void chf_store_pass3(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd *buf, const double *kin_b, double *out_b,
+                            double *red, bool want_kin, bool stash) {
+    constexpr int H = R / 2;
+    const int M = L.N / R, npairs = (M + 1) / 2, half = grp.T / 2;
+    const long long off = L.mom_off - L.nco_in;
+    const double lm = L.loopmul / (double)L.ncm, dM = (double)M;
+    int it = 0;
+    for (int p0 = 0; p0 < npairs; p0 += half, ++it) {
+        grp.template par_xchg2<ChfXS<R>, H>(
+            [&](int tid, int T, ChfXS<R> &s) {
+                (void)T;
+                const int pr = p0 + (tid >> 1);
+                const int klo = chf_pair_klo(pr, tid & 1, M, npairs);
+                s.klo = klo;
+                s.xm = pr == 0 ? 0 : 1;
+                s.base = klo >= 0 ? L.rev[klo] : 0;
+#pragma unroll
+                for (int q = 0; q < R; ++q) s.a[q] = klo >= 0 ? buf[chf_swz(s.base + q, L.swm)] : mk(0.0, 0.0);
+                ChfDft<R, -1>::run(s.a);  // a[t] = Y[klo + t M]
+                const bool dc = klo == 0;
+#pragma unroll
+                for (int t = 0; t < H; ++t) {
+                    const cd gen = s.a[R - 1 - t];
+                    const cd spc = t == 0 ? mk(0.0, 0.0) : s.a[R - t];
+                    s.x[t] = dc ? spc : gen;
+                }
+            },
+            [&](int tid, int T, ChfXS<R> &s) {  // result rows of the own butterfly; halves for the partner in x
+                (void)T;
+                const int h = tid & 1;
+                const int klo = s.klo;
+                double kin = 0.0;
+                const double dklo = (double)klo;
+                constexpr int HC = H < 4 ? H : 4;  // rows per tensor-memory read: keeps the live registers below the cap
+#pragma unroll
+                for (int t0 = 0; t0 < H; t0 += HC) {
+                    double p[HC][4];
+                    if (stash) {
+                        grp.template tmem_ld<4 * HC>(it * 8 * H + 8 * t0, &p[0][0]);
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < HC; ++u) {
+                            p[u][0] = p[u][1] = p[u][2] = p[u][3] = 0.0;
+                            if (kin_b && (klo > 0 || (klo == 0 && t0 + u > 0)))
+                                chf_load4(kin_b + off + 4LL * (klo + (t0 + u) * M), F.aligned16, p[u]);
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < HC; ++u) {
+                        const int t = t0 + u;
+                        const cd A = s.a[t], Bm = s.x[t];
+                        double v[4] = {0.0, 0.0, 0.0, 0.0};
+                        if (klo == 0 && t == 0) {
+                            for (int c = 0; c < 4 - L.nco_in; ++c) out_b[L.mom_off + c] = 0.0;
+                            if (L.co0 >= 0) out_b[L.mom_off + L.co0] = A.x * L.loopmul;
+                            if (L.co2 >= 0) out_b[L.mom_off + L.co2] = A.y * L.loopmul;
+                        } else if (klo >= 0) {
+                            const double sc = lm * chf_rcp(fma((double)t, dM, dklo));
+                            v[0] = (A.x + Bm.x) * sc; v[1] = (A.y - Bm.y) * sc; v[2] = (A.y + Bm.y) * sc; v[3] = (Bm.x - A.x) * sc;
+                            if (kin_b) {
+                                kin += (p[u][0] * p[u][0] + p[u][1] * p[u][1]) + (p[u][2] * p[u][2] + p[u][3] * p[u][3]);
+                                v[0] += p[u][0]; v[1] += p[u][1]; v[2] += p[u][2]; v[3] += p[u][3];
+                            }
+                        }
+                        // lane 0 of the pair writes doubles 0,1 of both rows, lane 1 doubles 2,3
+                        s.a[t] = h == 0 ? mk(v[0], v[1]) : mk(v[2], v[3]);
+                        s.x[t] = h == 0 ? mk(v[2], v[3]) : mk(v[0], v[1]);
+                    }
+                }
+                if (want_kin && klo >= 0) red[grp.g * grp.T + tid] += 0.5 * kin;
+                s.xm = 1;
+            },
+            [&](int tid, int T, ChfXS<R> &s) {
+                (void)T;
+                const int pr = p0 + (tid >> 1), h = tid & 1;
+                int ka, kb;
+                chf_pair_rows(pr, M, npairs, &ka, &kb);
+#pragma unroll
+                for (int t = 0; t < H; ++t) {
+                    const cd va = h == 0 ? s.a[t] : s.x[t];  // half h of row ka + t M
+                    const cd vb = h == 0 ? s.x[t] : s.a[t];  // half h of row kb + t M
+                    if (ka > 0 || (ka == 0 && t > 0)) chf_store2(out_b + off + 4LL * (ka + t * M) + 2 * h, F.aligned16, va);
+                    if (kb > 0) chf_store2(out_b + off + 4LL * (kb + t * M) + 2 * h, F.aligned16, vb);
+                }
+            });
+    }
+    grp.sync();
+}
+
 template <class Grp>
 CHB_D void chf_load_pass_r(Grp &grp, const ChfSys &F, const ChfLoop &L, const double *vec_b, cd *buf, double *red,
-                            bool want_kin) {
+                            bool want_kin, bool stash) {
+    if (F.ver >= 3) {
+        switch (L.fac[L.nfac - 1]) {
+            case 16: chf_load_pass3<16>(grp, F, L, vec_b, buf, red, want_kin, stash); break;
+            case 8: chf_load_pass3<8>(grp, F, L, vec_b, buf, red, want_kin, stash); break;
+            case 4: chf_load_pass3<4>(grp, F, L, vec_b, buf, red, want_kin, stash); break;
+            default: chf_load_pass3<2>(grp, F, L, vec_b, buf, red, want_kin, stash); break;
+        }
+        return;
+    }
+#ifdef CHF_KEEP_OLD
     switch (L.fac[L.nfac - 1]) {
         case 16: chf_load_pass<16>(grp, F, L, vec_b, buf, red, want_kin); break;
         case 8: chf_load_pass<8>(grp, F, L, vec_b, buf, red, want_kin); break;
         case 4: chf_load_pass<4>(grp, F, L, vec_b, buf, red, want_kin); break;
         default: chf_load_pass<2>(grp, F, L, vec_b, buf, red, want_kin); break;
     }
+#endif
 }
 template <class Grp>
 CHB_D void chf_store_pass_r(Grp &grp, const ChfSys &F, const ChfLoop &L, const cd *buf, const double *kin_b,
-                             double *out_b, double *red, bool want_kin) {
+                             double *out_b, double *red, bool want_kin, bool stash) {
+    if (F.ver >= 3) {
+        switch (L.fac[L.nfac - 1]) {
+            case 16: chf_store_pass3<16>(grp, F, L, buf, kin_b, out_b, red, want_kin, stash); break;
+            case 8: chf_store_pass3<8>(grp, F, L, buf, kin_b, out_b, red, want_kin, stash); break;
+            case 4: chf_store_pass3<4>(grp, F, L, buf, kin_b, out_b, red, want_kin, stash); break;
+            default: chf_store_pass3<2>(grp, F, L, buf, kin_b, out_b, red, want_kin, stash); break;
+        }
+        return;
+    }
+#ifdef CHF_KEEP_OLD
     switch (L.fac[L.nfac - 1]) {
         case 16: chf_store_pass<16>(grp, F, L, buf, kin_b, out_b, red, want_kin); break;
         case 8: chf_store_pass<8>(grp, F, L, buf, kin_b, out_b, red, want_kin); break;
         case 4: chf_store_pass<4>(grp, F, L, buf, kin_b, out_b, red, want_kin); break;
         default: chf_store_pass<2>(grp, F, L, buf, kin_b, out_b, red, want_kin); break;
     }
+#endif
 }
 
 // ask L2 for the parameter rows of a later state (the CTA that will own it is not resident yet)
@@ -787,26 +1017,31 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
     double *seg_out_b = A.seg_out ? A.seg_out + b * F.segsz : (double *)0;
     double *out_b = A.vec_out ? A.vec_out + b * F.nparams : (double *)0;
     const bool have_fwd = vec_b != (const double *)0;
+    // the rows loaded by the forward pass are the rows of the kinetic term: keep them in tensor memory
+    const bool stash = F.ver >= 3 && F.tmem_cols > 0 && have_fwd && kin_b == vec_b && out_b != (double *)0 && !(F.dbg & 64);
     ctx.groups(F.nloop, F.T, [&](auto &grp) {
         grp.par([&](int tid, int T) { red[grp.g * T + tid] = 0.0; });
         if (have_fwd) {
             const ChfLoop &L = F.loops[grp.g];
             cd *buf = sm + L.smem_off;
             if (F.ver >= 2) {
-                chf_load_pass_r(grp, F, L, vec_b, buf, red, A.kin_from == 1);
+                if (!(F.dbg & 1)) chf_load_pass_r(grp, F, L, vec_b, buf, red, A.kin_from == 1, stash);
                 if (F.pf_stride > 0 && b + F.pf_stride < A.nstates)
                     grp.one([&]() {
                         chf_prefetch_l2(A.vec_in + (b + F.pf_stride) * F.nparams, L.mom_off - L.nco_in, 4LL * L.npr,
                                         A.vec_in + A.nstates * F.nparams);
                     });
-                chf_fft_spec_to_time(grp, buf, L, true);
+                if (!(F.dbg & 2)) chf_fft_spec_to_time(grp, buf, L, true);
             } else {
+#ifdef CHF_KEEP_OLD
                 chf_load_loop(grp, F, L, vec_b, buf, red, A.kin_from == 1);
                 chf_fft_spec_to_time(grp, buf, L);
+#endif
             }
         }
     });
-    if (F.pair_fast)
+    if (F.dbg & 4) {
+    } else if (F.pair_fast)
         chf_pair_fast<NSEG, PMODE>(ctx, F, sm, have_fwd, seg_in_b, seg_out_b, red);
     else
         chf_pair<NSEG, PMODE>(ctx, F, sm, have_fwd, seg_in_b, seg_out_b, red);
@@ -815,15 +1050,17 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
             const ChfLoop &L = F.loops[grp.g];
             cd *buf = sm + L.smem_off;
             if (F.ver >= 2) {
-                chf_fft_time_to_spec(grp, buf, L, true);
-                chf_store_pass_r(grp, F, L, buf, kin_b, out_b, red, A.kin_from == 2);
+                if (!(F.dbg & 8)) chf_fft_time_to_spec(grp, buf, L, true);
+                if (!(F.dbg & 16)) chf_store_pass_r(grp, F, L, buf, kin_b, out_b, red, A.kin_from == 2, stash);
             } else {
+#ifdef CHF_KEEP_OLD
                 chf_fft_time_to_spec(grp, buf, L);
                 chf_store_loop(grp, F, L, buf, kin_b, out_b, red, A.kin_from == 2);
+#endif
             }
         });
     }
-    if (A.scalar_out) {
+    if (A.scalar_out && !(F.dbg & 32)) {
         cta_reduce(ctx, red);
         ctx.par([&](int tid, int nthr) {
             if (tid == 0) A.scalar_out[b] = red[0];

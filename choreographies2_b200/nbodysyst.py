@@ -116,7 +116,7 @@ class NBodySystB200:
     def set_fused(self, enable) -> None:
         """False/0: generic staged kernels only; True/2: fused kernel (default); 1: fused kernel with separate
         load/store phases (kept for A/B measurements)."""
-        level = 2 if enable is True else int(enable)
+        level = 3 if enable is True else int(enable)
         L.check(self._lib, self._lib.chb_plan_set_fused(self._plan, level))
 
     # ------------------------------------------------------------------ plumbing
