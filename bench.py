@@ -337,7 +337,8 @@ def run_b200(args):
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "peak_source": peak_src,
-        "kernel": ("k_fused<NSEG,1>: 1 launch per step, one CTA per state, whole evaluation in shared memory" if nbs.fused else
+        "kernel": ("k_fused<NSEG,1>: 1 launch per step, persistent CTAs (one resident wave), one state at a time per CTA, whole "
+                   "evaluation in shared memory, parameter rows stashed in tensor memory" if nbs.fused else
                    f"staged path: {launches_per_step} launches per step (k_fwd, k_pair<1>, k_adj, k_finish per chunk); "
                    "achieved = whole-step algorithmic bytes / whole-step time"),
         "alg_bytes_per_unit": alg_bytes_per_unit, "units_per_launch": B,

@@ -521,7 +521,40 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
                 }
             rc = level_upload(p, tw, &FL.tw[i]);
             if (rc) return -1;
+            FL.tw_len[i] = Lp > 1 ? Lp * nb : 0;
+            FL.tw_soff[i] = -1;
             Lcur = Lp;
+        }
+    }
+    for (int il = 0; il < T.nloop; ++il) {
+        ChfLoop &FL = F.loops[il];
+        const int src = first_loop_of_N[FL.N];
+        for (int i = 0; i < FL.nfac; ++i) { FL.tw_len[i] = F.loops[src].tw_len[i]; FL.tw_soff[i] = -1; }
+    }
+    {   // shared-memory copy of the twiddle tables of the longest loop's length when they fit behind the loop buffers
+        int src = 0;
+        for (int il = 1; il < T.nloop; ++il)
+            if (F.loops[il].N > F.loops[src].N) src = il;
+        src = first_loop_of_N[F.loops[src].N];
+        int need = 0;
+        for (int i = 0; i < F.loops[src].nfac; ++i) need += F.loops[src].tw_len[i];
+        const size_t total = p->fused_smem + (size_t)need * sizeof(cd);
+        F.tw_smem_len = 0;
+        if (need > 0 && total <= p->smem_limit && (size_t)(228 * 1024) / (total + 1024) >= (size_t)std::max(1, p->fused_resident / p->num_sms)) {
+            int off = 0;
+            for (int il = 0; il < T.nloop; ++il) {
+                if (F.loops[il].N != F.loops[src].N) continue;
+                int o = 0;
+                for (int i = 0; i < F.loops[il].nfac; ++i) {
+                    F.loops[il].tw_soff[i] = F.loops[il].tw_len[i] > 0 ? o : -1;
+                    o += F.loops[il].tw_len[i];
+                }
+                off = o;
+            }
+            F.tw_src_loop = src;
+            F.tw_smem_off = smem_cd;
+            F.tw_smem_len = off;
+            p->fused_smem = total;
         }
     }
     return 1;
@@ -1165,6 +1198,7 @@ CHB_KERNEL void CHF_BOUNDS k_fused(ChfSys F, ChfArgs A) {
 #else
     if (use_tmem) ctx.tmem.assign((size_t)CHF_MAX_THREADS * 256, 0.0);
 #endif
+    cta_fused_prologue(ctx, F, (cd *)(CHB_SMEM + CHF_RED_BYTES));
     // persistent CTAs: the grid is one resident wave, every CTA walks the batch with the grid stride
     for (long long b = CHB_BLOCK_ID; b < A.nstates; b += CHB_GRID_DIM)
         cta_fused<NSEG, PMODE>(ctx, F, A, b, (double *)CHB_SMEM, (cd *)(CHB_SMEM + CHF_RED_BYTES));

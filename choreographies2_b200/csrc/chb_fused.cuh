@@ -36,6 +36,8 @@ struct ChfLoop {
     int fac[CHF_MAX_FAC];        // DIF radices, product N
     const int *rev;              // [N] slot of spectral index k after the DIF passes
     const cd *tw[CHF_MAX_FAC];   // DIF stage s: base twiddles exp(-2 pi i j 2^e / L_s), [Lp_s][nbase(r_s)]
+    int tw_soff[CHF_MAX_FAC];    // >= 0: the stage's table is also kept in shared memory at this offset (cd) of the twiddle region
+    int tw_len[CHF_MAX_FAC];     // table length in cd
     long long mom_off;
     double loopmul;  // 1/sqrt(loopnb*loopmass*4pi^2)
 };
@@ -55,6 +57,8 @@ struct ChfSys {
     int tmem_thread_cols;  // columns per thread (pair iterations * 4 R), threads of warp w use block w / 4 of their lane quarter
     int ver;        // 3: ver 2 + half-row coalescing of every global access + rows stashed in tensor memory for the kinetic term;
                     // 2: parameter load / result store fused into the first / last FFT pass (lane-pair exchange), 1: separate phases
+    int tw_smem_off, tw_smem_len;  // twiddle region (cd slots after the loop buffers), filled once per persistent CTA
+    int tw_src_loop;               // loop whose tables the region holds (loops of equal length share them)
     int dbg;        // profiling only (env CHB_FUSED_DBG): bit 0..5 skip load pass / inverse passes / pair / forward passes / store pass / reduce
     int pair_fast;  // gravity, every pair s < t interacts once with identity rotation, segments are plain slices
     int pf_stride;  // > 0: CTA b asks L2 for the parameters of state b + pf_stride while it computes (co-resident CTA count)
@@ -235,6 +239,73 @@ CHB_HD void chf_twiddle(cd *a, const cd *base) {
     }
 }
 
+// w[t] = w^t for t = 1..R-1 from the base powers w^(2^e) (conjugated for SIGN > 0)
+template <int R, int SIGN>
+CHB_HD void chf_twiddle_powers(cd *w, const cd *base) {
+#pragma unroll
+    for (int e = 0; (1 << e) < R; ++e) {
+        cd v = base[e];
+        if (SIGN > 0) v.y = -v.y;
+        w[1 << e] = v;
+    }
+#pragma unroll
+    for (int t = 3; t < R; ++t) {
+        if ((t & (t - 1)) != 0) {
+            int hb = 1;
+            while (hb * 2 <= t) hb *= 2;
+            w[t] = cmul(w[hb], w[t - hb]);
+        }
+    }
+}
+
+// Radix-16 passes of a 16-aligned length with the index arithmetic folded for the two strides every 16^k-type length
+// uses (Lp = 256: the swizzle does not depend on q, the 16 slots are compile-time offsets from one address; Lp = 16:
+// the swizzle reduces to j ^ q and both butterflies of a thread share their twiddles).  Same arithmetic as chf_pass.
+template <int SIGN, bool DIT, class Grp>
+CHB_D void chf_pass16_lp256(Grp &grp, cd *buf, int N, const cd *tw) {
+    const int nbf = N / 16;
+    grp.par([&](int tid, int T) {
+        for (int b = tid; b < nbf; b += T) {
+            const int j = b & 255;
+            cd *p = buf + ((b >> 8) << 12) + (j ^ ((j >> 4) & 15));
+            cd a[16];
+#pragma unroll
+            for (int q = 0; q < 16; ++q) a[q] = p[q * 256];
+            if (DIT) chf_twiddle<16, SIGN>(a, tw + j * 4);
+            ChfDft<16, SIGN>::run(a);
+            if (!DIT) chf_twiddle<16, SIGN>(a, tw + j * 4);
+#pragma unroll
+            for (int t = 0; t < 16; ++t) p[t * 256] = a[t];
+        }
+    });
+}
+template <int SIGN, bool DIT, class Grp>
+CHB_D void chf_pass16_lp16(Grp &grp, cd *buf, int N, const cd *tw) {
+    const int nbf = N / 16;
+    grp.par([&](int tid, int T) {
+        const int j = tid & 15;  // T is a multiple of 32: every butterfly of this thread has the same j
+        cd w[16];
+        chf_twiddle_powers<16, SIGN>(w, tw + j * 4);
+        for (int b = tid; b < nbf; b += T) {
+            cd *p = buf + ((b >> 4) << 8);
+            cd a[16];
+#pragma unroll
+            for (int q = 0; q < 16; ++q) a[q] = p[q * 16 + (j ^ q)];
+            if (DIT) {
+#pragma unroll
+                for (int t = 1; t < 16; ++t) a[t] = cmul(a[t], w[t]);
+            }
+            ChfDft<16, SIGN>::run(a);
+            if (!DIT) {
+#pragma unroll
+                for (int t = 1; t < 16; ++t) a[t] = cmul(a[t], w[t]);
+            }
+#pragma unroll
+            for (int t = 0; t < 16; ++t) p[t * 16 + (j ^ t)] = a[t];
+        }
+    });
+}
+
 // one pass over the N/R butterflies of a stage with current length L (DIF: twiddle the outputs, DIT: the inputs)
 template <int R, int SIGN, bool DIT, class Grp>
 CHB_D void chf_pass(Grp &grp, cd *buf, int swm, int N, int L, const cd *tw) {
@@ -255,7 +326,11 @@ CHB_D void chf_pass(Grp &grp, cd *buf, int swm, int N, int L, const cd *tw) {
     });
 }
 template <int SIGN, bool DIT, class Grp>
-CHB_D void chf_pass_r(Grp &grp, cd *buf, int swm, int N, int L, int r, const cd *tw) {
+CHB_D void chf_pass_r(Grp &grp, cd *buf, int swm, int N, int L, int r, const cd *tw, int generic = 0) {
+    if (r == 16 && swm == 15 && !generic) {
+        if (L == 4096) { chf_pass16_lp256<SIGN, DIT>(grp, buf, N, tw); return; }
+        if (L == 256) { chf_pass16_lp16<SIGN, DIT>(grp, buf, N, tw); return; }
+    }
     switch (r) {
         case 16: chf_pass<16, SIGN, DIT>(grp, buf, swm, N, L, tw); break;
         case 8: chf_pass<8, SIGN, DIT>(grp, buf, swm, N, L, tw); break;
@@ -268,20 +343,22 @@ CHB_D void chf_pass_r(Grp &grp, cd *buf, int swm, int N, int L, int r, const cd 
 }
 // backward (SIGN +1) transform, spectrum Z[k] in slot rev[k]  ->  z[n] in slot n  (decimation in time)
 template <class Grp>
-CHB_D void chf_fft_spec_to_time(Grp &grp, cd *buf, const ChfLoop &L, bool skip_first = false) {
+CHB_D void chf_fft_spec_to_time(Grp &grp, cd *buf, const ChfLoop &L, bool skip_first = false, const cd *twsm = (const cd *)0, int generic = 0) {
     int len = 1;
     for (int s = L.nfac - 1; s >= 0; --s) {
         len *= L.fac[s];
         if (skip_first && s == L.nfac - 1) continue;  // done by chf_load_pass
-        chf_pass_r<+1, true>(grp, buf, L.swm, L.N, len, L.fac[s], L.tw[s]);
+        const cd *tw = (twsm && L.tw_soff[s] >= 0) ? twsm + L.tw_soff[s] : L.tw[s];
+        chf_pass_r<+1, true>(grp, buf, L.swm, L.N, len, L.fac[s], tw, generic);
     }
 }
 // forward (SIGN -1) transform, g[n] in slot n  ->  Y[k] in slot rev[k]  (decimation in frequency)
 template <class Grp>
-CHB_D void chf_fft_time_to_spec(Grp &grp, cd *buf, const ChfLoop &L, bool skip_last = false) {
+CHB_D void chf_fft_time_to_spec(Grp &grp, cd *buf, const ChfLoop &L, bool skip_last = false, const cd *twsm = (const cd *)0, int generic = 0) {
     int len = L.N;
     for (int s = 0; s < L.nfac - (skip_last ? 1 : 0); ++s) {  // the last pass is chf_store_pass when skipped
-        chf_pass_r<-1, false>(grp, buf, L.swm, L.N, len, L.fac[s], L.tw[s]);
+        const cd *tw = (twsm && L.tw_soff[s] >= 0) ? twsm + L.tw_soff[s] : L.tw[s];
+        chf_pass_r<-1, false>(grp, buf, L.swm, L.N, len, L.fac[s], tw, generic);
         len /= L.fac[s];
     }
 }
@@ -1006,6 +1083,20 @@ CHB_D void chf_pair_fast(Ctx &ctx, const ChfSys &F, cd *sm, bool have_fwd, const
     });
 }
 
+// once per (persistent) CTA: copy the twiddle tables of the passes into the shared-memory region behind the loop buffers
+template <class Ctx>
+CHB_D void cta_fused_prologue(Ctx &ctx, const ChfSys &F, cd *sm) {
+    if (F.tw_smem_len <= 0) return;
+    const ChfLoop &L = F.loops[F.tw_src_loop];
+    ctx.par([&](int tid, int nthr) {
+        for (int s = 0; s < L.nfac; ++s) {
+            if (L.tw_soff[s] < 0) continue;
+            cd *dst = sm + F.tw_smem_off + L.tw_soff[s];
+            for (int i = tid; i < L.tw_len[s]; i += nthr) dst[i] = L.tw[s][i];
+        }
+    });
+}
+
 // ------------------------------------------------------------------------------------------------
 // the CTA program
 // ------------------------------------------------------------------------------------------------
@@ -1017,6 +1108,7 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
     double *seg_out_b = A.seg_out ? A.seg_out + b * F.segsz : (double *)0;
     double *out_b = A.vec_out ? A.vec_out + b * F.nparams : (double *)0;
     const bool have_fwd = vec_b != (const double *)0;
+    const cd *twsm = (F.tw_smem_len > 0 && !(F.dbg & 128)) ? sm + F.tw_smem_off : (const cd *)0;
     // the rows loaded by the forward pass are the rows of the kinetic term: keep them in tensor memory
     const bool stash = F.ver >= 3 && F.tmem_cols > 0 && have_fwd && kin_b == vec_b && out_b != (double *)0 && !(F.dbg & 64);
     ctx.groups(F.nloop, F.T, [&](auto &grp) {
@@ -1031,7 +1123,7 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
                         chf_prefetch_l2(A.vec_in + (b + F.pf_stride) * F.nparams, L.mom_off - L.nco_in, 4LL * L.npr,
                                         A.vec_in + A.nstates * F.nparams);
                     });
-                if (!(F.dbg & 2)) chf_fft_spec_to_time(grp, buf, L, true);
+                if (!(F.dbg & 2)) chf_fft_spec_to_time(grp, buf, L, true, twsm, F.dbg & 256);
             } else {
 #ifdef CHF_KEEP_OLD
                 chf_load_loop(grp, F, L, vec_b, buf, red, A.kin_from == 1);
@@ -1050,7 +1142,7 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
             const ChfLoop &L = F.loops[grp.g];
             cd *buf = sm + L.smem_off;
             if (F.ver >= 2) {
-                if (!(F.dbg & 8)) chf_fft_time_to_spec(grp, buf, L, true);
+                if (!(F.dbg & 8)) chf_fft_time_to_spec(grp, buf, L, true, twsm, F.dbg & 256);
                 if (!(F.dbg & 16)) chf_store_pass_r(grp, F, L, buf, kin_b, out_b, red, A.kin_from == 2, stash);
             } else {
 #ifdef CHF_KEEP_OLD
