@@ -448,7 +448,8 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
         for (int s = 0; s < T.nsegm && fast; ++s) {
             const ChfSeg &sg = F.segs[s];
             const ChfLoop &FL = F.loops[sg.loop];
-            fast = sg.isid && sg.timerev > 0 && (FL.swm == 0 || segm_size % 256 == 0);
+            fast = sg.isid && sg.timerev > 0;
+            (void)FL;
             for (int t = 0; t < T.nsegm && fast; ++t) {
                 const ChfPair &P = F.pairs[s * CHF_MAX_SEGS + t];
                 fast = t > s ? (P.on && P.isid) : !P.on;
@@ -517,7 +518,7 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
                 for (int e = 0; e < nb; ++e) {
                     double c, sn;
                     exact_root((long long)j * (1LL << e), Lcur, &c, &sn);
-                    tw[(size_t)j * nb + e] = mk(c, sn);
+                    tw[(size_t)e * Lp + j] = mk(c, sn);  // [e][j]: conflict-free / coalesced for consecutive j
                 }
             rc = level_upload(p, tw, &FL.tw[i]);
             if (rc) return -1;

@@ -79,7 +79,9 @@ struct ChfArgs {
     long long nstates;      // batch size (bound of the L2 prefetch)
 };
 
-CHB_HD int chf_swz(int i, int m) { return i ^ ((i >> 4) & m); }
+// XOR swizzle of the low nibble with the next two nibbles: every access pattern of the passes (lanes along any one of the
+// three hex digits of a 4096-point loop, the fused load / store passes included) and of the pair phase is conflict-free
+CHB_HD int chf_swz(int i, int m) { return i ^ (((i >> 4) ^ (i >> 8)) & m); }
 CHB_HD int chf_nbase(int r) { return r == 2 ? 1 : (r <= 4 ? 2 : (r <= 8 ? 3 : 4)); }
 
 // ------------------------------------------------------------------------------------------------
@@ -220,11 +222,11 @@ struct ChfDft<7, SIGN> : ChfDftOdd<7, SIGN> {};
 
 // a[t] *= w^t for t = 1..R-1, w^(2^e) read from the base table (conjugated for SIGN > 0)
 template <int R, int SIGN>
-CHB_HD void chf_twiddle(cd *a, const cd *base) {
+CHB_HD void chf_twiddle(cd *a, const cd *base, int stride) {
     cd w[R];
 #pragma unroll
     for (int e = 0; (1 << e) < R; ++e) {
-        cd v = base[e];
+        cd v = base[e * stride];  // table layout [e][j]: lanes read consecutive entries
         if (SIGN > 0) v.y = -v.y;
         w[1 << e] = v;
     }
@@ -241,10 +243,10 @@ CHB_HD void chf_twiddle(cd *a, const cd *base) {
 
 // w[t] = w^t for t = 1..R-1 from the base powers w^(2^e) (conjugated for SIGN > 0)
 template <int R, int SIGN>
-CHB_HD void chf_twiddle_powers(cd *w, const cd *base) {
+CHB_HD void chf_twiddle_powers(cd *w, const cd *base, int stride) {
 #pragma unroll
     for (int e = 0; (1 << e) < R; ++e) {
-        cd v = base[e];
+        cd v = base[e * stride];  // table layout [e][j]: lanes read consecutive entries
         if (SIGN > 0) v.y = -v.y;
         w[1 << e] = v;
     }
@@ -267,15 +269,16 @@ CHB_D void chf_pass16_lp256(Grp &grp, cd *buf, int N, const cd *tw) {
     grp.par([&](int tid, int T) {
         for (int b = tid; b < nbf; b += T) {
             const int j = b & 255;
-            cd *p = buf + ((b >> 8) << 12) + (j ^ ((j >> 4) & 15));
+            cd *p = buf + ((b >> 8) << 12) + (j & 0xF0);
+            const int x = (j ^ (j >> 4)) & 15;  // slot nibble = x ^ q: bits 8..11 of the slot index are q
             cd a[16];
 #pragma unroll
-            for (int q = 0; q < 16; ++q) a[q] = p[q * 256];
-            if (DIT) chf_twiddle<16, SIGN>(a, tw + j * 4);
+            for (int q = 0; q < 16; ++q) a[q] = p[q * 256 + (x ^ q)];
+            if (DIT) chf_twiddle<16, SIGN>(a, tw + j, 256);
             ChfDft<16, SIGN>::run(a);
-            if (!DIT) chf_twiddle<16, SIGN>(a, tw + j * 4);
+            if (!DIT) chf_twiddle<16, SIGN>(a, tw + j, 256);
 #pragma unroll
-            for (int t = 0; t < 16; ++t) p[t * 256] = a[t];
+            for (int t = 0; t < 16; ++t) p[t * 256 + (x ^ t)] = a[t];
         }
     });
 }
@@ -285,12 +288,13 @@ CHB_D void chf_pass16_lp16(Grp &grp, cd *buf, int N, const cd *tw) {
     grp.par([&](int tid, int T) {
         const int j = tid & 15;  // T is a multiple of 32: every butterfly of this thread has the same j
         cd w[16];
-        chf_twiddle_powers<16, SIGN>(w, tw + j * 4);
+        chf_twiddle_powers<16, SIGN>(w, tw + j, 16);
         for (int b = tid; b < nbf; b += T) {
             cd *p = buf + ((b >> 4) << 8);
+            const int x = (j ^ (b >> 4)) & 15;  // bits 8..11 of the slot index are the block number
             cd a[16];
 #pragma unroll
-            for (int q = 0; q < 16; ++q) a[q] = p[q * 16 + (j ^ q)];
+            for (int q = 0; q < 16; ++q) a[q] = p[q * 16 + (x ^ q)];
             if (DIT) {
 #pragma unroll
                 for (int t = 1; t < 16; ++t) a[t] = cmul(a[t], w[t]);
@@ -301,7 +305,7 @@ CHB_D void chf_pass16_lp16(Grp &grp, cd *buf, int N, const cd *tw) {
                 for (int t = 1; t < 16; ++t) a[t] = cmul(a[t], w[t]);
             }
 #pragma unroll
-            for (int t = 0; t < 16; ++t) p[t * 16 + (j ^ t)] = a[t];
+            for (int t = 0; t < 16; ++t) p[t * 16 + (x ^ t)] = a[t];
         }
     });
 }
@@ -317,9 +321,9 @@ CHB_D void chf_pass(Grp &grp, cd *buf, int swm, int N, int L, const cd *tw) {
             cd a[R];
 #pragma unroll
             for (int q = 0; q < R; ++q) a[q] = buf[chf_swz(base + q * Lp, swm)];
-            if (DIT && Lp > 1) chf_twiddle<R, SIGN>(a, tw + (long long)j * chf_nbase(R));
+            if (DIT && Lp > 1) chf_twiddle<R, SIGN>(a, tw + j, Lp);
             ChfDft<R, SIGN>::run(a);
-            if (!DIT && Lp > 1) chf_twiddle<R, SIGN>(a, tw + (long long)j * chf_nbase(R));
+            if (!DIT && Lp > 1) chf_twiddle<R, SIGN>(a, tw + j, Lp);
 #pragma unroll
             for (int t = 0; t < R; ++t) buf[chf_swz(base + t * Lp, swm)] = a[t];
         }
@@ -1021,8 +1025,8 @@ CHB_D void chf_pair_fast(Ctx &ctx, const ChfSys &F, cd *sm, bool have_fwd, const
 #pragma unroll
         for (int s = 0; s < NSEG; ++s) {
             const ChfLoop &L = F.loops[F.segs[s].loop];
-            off[s] = L.smem_off + F.segs[s].row0;  // row0 is a multiple of segm_size: the swizzle acts on i alone when
-            swm[s] = L.swm;                        // segm_size % 256 == 0, which pair_fast requires with a swizzle
+            off[s] = L.smem_off;
+            swm[s] = L.swm;
 #pragma unroll
             for (int t = 0; t < NSEG; ++t) w[s][t] = t > s ? F.pairs[s * CHF_MAX_SEGS + t].fac * inv_size : 0.0;
         }
@@ -1032,7 +1036,7 @@ CHB_D void chf_pair_fast(Ctx &ctx, const ChfSys &F, cd *sm, bool have_fwd, const
             int slot[NSEG];
 #pragma unroll
             for (int s = 0; s < NSEG; ++s) {
-                slot[s] = off[s] + chf_swz(i, swm[s]);
+                slot[s] = off[s] + chf_swz(F.segs[s].row0 + i, swm[s]);
                 cd v = mk(0.0, 0.0);
                 if (have_fwd) v = sm[slot[s]];
                 if (PMODE == 2) {
