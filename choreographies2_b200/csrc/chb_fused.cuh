@@ -1122,7 +1122,7 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
             cd *buf = sm + L.smem_off;
             if (F.ver >= 2) {
                 if (!(F.dbg & 1)) chf_load_pass_r(grp, F, L, vec_b, buf, red, A.kin_from == 1, stash);
-                if (F.pf_stride > 0 && b + F.pf_stride < A.nstates)
+                if (F.pf_stride > 0 && b + F.pf_stride < A.nstates && !(F.dbg & 512))
                     grp.one([&]() {
                         chf_prefetch_l2(A.vec_in + (b + F.pf_stride) * F.nparams, L.mom_off - L.nco_in, 4LL * L.npr,
                                         A.vec_in + A.nstates * F.nparams);
