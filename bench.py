@@ -48,7 +48,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=4096, help="states per GPU")
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--no-fused", action="store_true")
-    ap.add_argument("--fused-ver", type=int, default=3, help="2 = load/store fused into the FFT passes (default), 1 = separate phases")
+    ap.add_argument("--fused-ver", type=int, default=4, help="4 = newest fused kernel the layout supports (default), 3 = force version 3")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample", type=int, default=0, help="states in the cpu_baseline sample (0 = auto)")

@@ -22,6 +22,7 @@
 #include <cuda_runtime.h>
 #endif
 #include "chb_fused.cuh"
+#include "chb_fused4.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // errors
@@ -70,7 +71,9 @@ struct chb_plan {
     std::vector<ChbLoop> h_loops;      // host mirror (device pointers inside)
     ChbSys sys;                        // passed by value to kernels
     int64_t chunk_user = 0;
-    int fused_enabled = 3;  // 0 staged kernels only, 1 fused v1 (separate load/store phases), 2 fused v2, 3 fused v3
+    int fused_enabled = 4;  // 0 staged kernels only, 1 fused v1 (separate load/store phases), 2 fused v2, 3 fused v3,
+                            // 4 fused v4 where the layout allows it (chb_fused4.cuh), else v3
+    int fused4_ok = 0;      // the level's layout is served by k_fused4
     int fused_resident = 148;
     int fused_active = 0;
     int64_t launches = 0;
@@ -558,6 +561,18 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
             p->fused_smem = total;
         }
     }
+    {   // version 4 (chb_fused4.cuh): every loop 4096 = 16^3 samples covered by one identity segment, gravity fast pairs,
+        // 16-byte aligned rows (bulk copies), tables in shared memory, the tensor-memory stash available
+        bool ok = F.pair_fast && F.aligned16 && F.tmem_cols > 0 && F.tw_smem_len > 0 && T.nsegm == T.nloop && T.nloop <= 3 &&
+                  Tg == CH4_T && segm_size == CH4_N;
+        for (int il = 0; il < T.nloop && ok; ++il) {
+            const ChfLoop &FL = F.loops[il];
+            ok = FL.N == CH4_N && FL.nfac == 3 && FL.fac[0] == 16 && FL.fac[1] == 16 && FL.fac[2] == 16 && FL.nco_in % 2 == 0 &&
+                 FL.nco_in <= 2 && FL.tw_soff[0] >= 0 && FL.tw_soff[1] >= 0;
+        }
+        for (int s = 0; s < T.nsegm && ok; ++s) ok = F.segs[s].row0 == 0 && F.segs[s].loop == s;
+        p->fused4_ok = ok ? 1 : 0;
+    }
     return 1;
 }
 
@@ -820,6 +835,7 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
     p->nint = nint;
     p->ready = true;
     p->fused_active = 0;
+    p->fused4_ok = 0;
     {
         int rcf = fused_setup(p, loops, segm_size);
         if (rcf < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: fused setup failed"); }
@@ -844,7 +860,7 @@ extern "C" int chb_plan_query(const chb_plan *p, int what, int64_t *v) {
         case CHB_Q_SEGM_SIZE: *v = p->sys.segm_size; break;
         case CHB_Q_SEGM_STORE: *v = p->sys.segm_store; break;
         case CHB_Q_SEGMPOS_SIZE: *v = p->sys.segsz; break;
-        case CHB_Q_FUSED: *v = (p->fused_enabled && p->fused_active) ? 1 : 0; break;
+        case CHB_Q_FUSED: *v = (p->fused_enabled && p->fused_active) ? ((p->fused_enabled >= 4 && p->fused4_ok) ? 4 : std::min(p->fused_enabled, 3)) : 0; break;
         case CHB_Q_CHUNK: {
             int64_t c = p->chunk_user;
             if (c <= 0) {
@@ -868,9 +884,9 @@ extern "C" int chb_plan_set_chunk(chb_plan *p, int64_t chunk) {
 extern "C" int chb_plan_set_fused(chb_plan *p, int enable) {
     CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_fused: NULL plan");
     #ifdef CHF_KEEP_OLD
-    p->fused_enabled = enable < 0 ? 0 : (enable > 3 ? 3 : enable);
+    p->fused_enabled = enable < 0 ? 0 : (enable > 4 ? 4 : enable);
 #else
-    p->fused_enabled = enable > 0 ? 3 : 0;  // the older fused variants (1, 2) are compiled only with -DCHF_KEEP_OLD
+    p->fused_enabled = enable > 0 ? (enable >= 4 ? 4 : 3) : 0;  // the older fused variants (1, 2) are compiled only with -DCHF_KEEP_OLD
 #endif
     return CHB_OK;
 }
@@ -958,6 +974,51 @@ __device__ __forceinline__ void dev_tmem_ld(unsigned taddr, double *v) {
 struct DevGrp {
     int g, T;
     unsigned taddr;  // tensor-memory address of this thread's stash (lane quarter of its warp, column block of warp / 4)
+    unsigned bar_base;  // shared-memory address of the CTA's mbarrier array (two per group: chunk A, chunk B)
+    // ---- bulk asynchronous copies (cp.async.bulk) used by the version-4 fused kernel; called by ONE thread of the group
+    // one mbarrier per (warp of the CTA, pass): the rows of the warp's butterflies of that pass
+    __device__ __forceinline__ unsigned bar_addr(int warp, int it) const {
+        return bar_base + 8u * (unsigned)(2 * (g * (T >> 5) + warp) + it);
+    }
+    __device__ __forceinline__ void tma_expect(int warp, int it, unsigned bytes) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr(warp, it)), "r"(bytes) : "memory");
+    }
+    __device__ __forceinline__ void tma_load(void *smem_dst, const void *gsrc, unsigned bytes, int warp, int it) {
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         (unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(bytes), "r"(bar_addr(warp, it)) : "memory");
+    }
+    // every thread: wait until the rows of its warp's butterflies of pass `it` have landed
+    __device__ __forceinline__ void tma_wait(int it, unsigned parity) {
+        unsigned done = 0;
+        const unsigned a = bar_addr(((int)threadIdx.x - g * T) >> 5, it);
+        while (!done) {
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(a), "r"(parity) : "memory");
+        }
+    }
+    __device__ __forceinline__ void tma_store(void *gdst, const void *smem_src, unsigned bytes) {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(
+                         (unsigned)__cvta_generic_to_shared(smem_src)), "r"(bytes) : "memory");
+    }
+    __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+    __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+    __device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+    __device__ __forceinline__ void warp_sync() { __syncwarp(); }
+    // f(warp of the group, lane) on every thread, no barrier
+    template <class F>
+    __device__ __forceinline__ void lanes(F f) {
+        const int tid = (int)threadIdx.x - g * T;
+        f(tid >> 5, tid & 31);
+    }
+    // f1, warp barrier, f2: the threads of a warp exchange data through shared memory between the two halves
+    template <class S, class F1, class F2>
+    __device__ __forceinline__ void par2(F1 f1, F2 f2) {
+        S s;
+        const int tid = (int)threadIdx.x - g * T;
+        f1(tid, T, s);
+        __syncwarp();
+        f2(tid, T, s);
+    }
     template <int ND>
     __device__ __forceinline__ void tmem_st(int col, const double *v) { dev_tmem_st<ND>(taddr + (unsigned)col, v); }
     template <int ND>
@@ -1008,6 +1069,7 @@ struct DevGrp {
 };
 struct DevCtx {
     unsigned tmem_thread;
+    unsigned bar_base;
     template <class F>
     __device__ __forceinline__ void par(F f) {
         f((int)threadIdx.x, (int)blockDim.x);
@@ -1017,7 +1079,7 @@ struct DevCtx {
     template <class F>
     __device__ __forceinline__ void groups(int ngroups, int T, F f) {
         (void)ngroups;
-        DevGrp grp{(int)threadIdx.x / T, T, tmem_thread};
+        DevGrp grp{(int)threadIdx.x / T, T, tmem_thread, bar_base};
         f(grp);
         __syncthreads();
     }
@@ -1026,7 +1088,7 @@ extern __shared__ __align__(16) unsigned char chb_smem_raw[];
 #define CHB_KERNEL __global__
 #define CHB_BLOCK_ID ((long long)blockIdx.x)
 #define CHB_NTHREADS ((int)blockDim.x)
-#define CHB_CTX_DECL DevCtx ctx{0u}
+#define CHB_CTX_DECL DevCtx ctx{0u, 0u}
 #define CHB_GRID_DIM ((long long)gridDim.x)
 #define CHB_SMEM chb_smem_raw
 #else
@@ -1066,16 +1128,35 @@ struct HostGrp {
     template <class S, int NX, class F1, class F2>
     void par_xchg(F1 f1, F2 f2) {
         std::vector<S> st((size_t)T);
-        for (int t = 0; t < T; ++t) f1(t, T, st[t]);
+        for (int t = 0; t < T; ++t) { tmem_tid = t; f1(t, T, st[t]); }
         for (int t = 0; t < T; ++t) {
             const int u = t ^ st[t].xm;
             if (u > t)
                 for (int i = 0; i < NX; ++i) std::swap(st[t].x[i], st[u].x[i]);
         }
-        for (int t = 0; t < T; ++t) f2(t, T, st[t]);
+        for (int t = 0; t < T; ++t) { tmem_tid = t; f2(t, T, st[t]); }
     }
     template <class F>
     void one(F f) { f(); }
+    // bulk copies complete at once in the emulation
+    void tma_expect(int, int, unsigned) {}
+    void tma_load(void *dst, const void *src, unsigned bytes, int, int) { memcpy(dst, src, bytes); }
+    void tma_wait(int, unsigned) {}
+    void warp_sync() {}
+    template <class F>
+    void lanes(F f) {
+        for (int t = 0; t < T; ++t) f(t >> 5, t & 31);
+    }
+    void tma_store(void *dst, const void *src, unsigned bytes) { memcpy(dst, src, bytes); }
+    void tma_store_commit() {}
+    void tma_store_wait_read() {}
+    void fence_async() {}
+    template <class S, class F1, class F2>
+    void par2(F1 f1, F2 f2) {
+        std::vector<S> st((size_t)T);
+        for (int t = 0; t < T; ++t) f1(t, T, st[t]);
+        for (int t = 0; t < T; ++t) f2(t, T, st[t]);
+    }
 };
 struct HostCtx {
     int nthr;
@@ -1213,6 +1294,66 @@ CHB_KERNEL void CHF_BOUNDS k_fused(ChfSys F, ChfArgs A) {
 #endif
 }
 
+// version 4 of the fused kernel (chb_fused4.cuh): persistent CTAs, rows moved by bulk asynchronous copies
+template <int NSEG, int PMODE>
+CHB_KERNEL void CHF_BOUNDS k_fused4(ChfSys F, ChfArgs A) {
+    CHB_CTX_DECL;
+#ifndef CHB_HOSTSIM
+    __shared__ unsigned tmem_base_s;
+    __shared__ __align__(8) unsigned long long load_bars[2 * (CHF_MAX_THREADS / 32)];
+    unsigned tmem_base = 0;
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         (unsigned)__cvta_generic_to_shared(&tmem_base_s)), "r"((unsigned)F.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2 * (CHF_MAX_THREADS / 32); ++i)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned)__cvta_generic_to_shared(&load_bars[i])) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    tmem_base = tmem_base_s;
+    {
+        const unsigned warp = threadIdx.x >> 5;
+        ctx.tmem_thread = tmem_base + (((warp & 3u) * 32u) << 16) + (warp >> 2) * (unsigned)F.tmem_thread_cols;
+        ctx.bar_base = (unsigned)__cvta_generic_to_shared(&load_bars[0]);
+    }
+    if (F.stagger_ns > 0 && A.nstates > (long long)gridDim.x) {
+        // all CTAs do identical work: without a stagger their copy phases coincide and the memory system sees bursts.
+        // CTA i starts i / gridDim of one state period late (the CTAs with the higher indices own fewer states).
+        if (threadIdx.x == 0) {
+            unsigned long long t0, t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            const unsigned long long wait = (unsigned long long)F.stagger_ns * blockIdx.x / gridDim.x;
+            do {
+                __nanosleep(500);
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            } while (t1 - t0 < wait);
+        }
+        __syncthreads();
+    }
+#else
+    ctx.tmem.assign((size_t)CHF_MAX_THREADS * 256, 0.0);
+#endif
+    double *red = (double *)CHB_SMEM;
+    cd *sm = (cd *)(CHB_SMEM + CHF_RED_BYTES);
+    cta_fused4_first_loads(ctx, F, A, CHB_BLOCK_ID, sm);
+    cta_fused4_prologue(ctx, F, sm);
+    unsigned parity = 0;
+    for (long long b = CHB_BLOCK_ID; b < A.nstates; b += CHB_GRID_DIM, parity ^= 1u)
+        cta_fused4<NSEG, PMODE>(ctx, F, A, b, b + CHB_GRID_DIM, parity, red, sm);
+#ifndef CHB_HOSTSIM
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the result rows of the last state have left shared memory
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x < 32)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((unsigned)F.tmem_cols) : "memory");
+#endif
+}
+
 #ifndef CHB_HOSTSIM
 #define CHB_LAUNCH(p, kern, grid, block, smem, stream, ...)                                                  \
     do {                                                                                                     \
@@ -1327,6 +1468,32 @@ static int launch_fused(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A0, c
         const char *dbg = getenv("CHB_FUSED_DBG");  // profiling only: results are wrong when phases are skipped
         p->fsys.dbg = dbg ? atoi(dbg) : 0;
     }
+    // version 4: U1 (action + gradient) and U2 (Hessian-vector on cached segment positions) with the kinetic rows = the
+    // transformed rows, 16-byte aligned vectors
+    if (p->fused_enabled >= 4 && p->fused4_ok && (pmode == 1 || pmode == 2) && A.vec_in && A.kin_src == A.vec_in && A.vec_out &&
+        (pmode == 1 || A.seg_in) && (((uintptr_t)A.vec_in | (uintptr_t)A.vec_out | (uintptr_t)A.seg_in | (uintptr_t)A.seg_out) & 15) == 0) {
+        p->fsys.ver = 4;
+        {
+            const char *sg = getenv("CHB_FUSED_STAGGER_NS");
+            p->fsys.stagger_ns = sg ? atoi(sg) : 0;  // measured: no gain (profiles/README.md), kept as a knob
+        }
+        if (p->fsys.nseg == 3) {
+            if (pmode == 1) CHB_LAUNCH(p, (k_fused4<3, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
+            else CHB_LAUNCH(p, (k_fused4<3, 2>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
+            return CHB_OK;
+        }
+        if (p->fsys.nseg == 2) {
+            if (pmode == 1) CHB_LAUNCH(p, (k_fused4<2, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
+            else CHB_LAUNCH(p, (k_fused4<2, 2>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
+            return CHB_OK;
+        }
+        if (p->fsys.nseg == 1) {
+            if (pmode == 1) CHB_LAUNCH(p, (k_fused4<1, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
+            else CHB_LAUNCH(p, (k_fused4<1, 2>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
+            return CHB_OK;
+        }
+    }
+    if (p->fsys.ver > 3) p->fsys.ver = 3;
     switch (p->fsys.nseg) {
         case 1: return launch_fused_n<1>(p, pmode, nb, A, st);
         case 2: return launch_fused_n<2>(p, pmode, nb, A, st);

@@ -109,6 +109,11 @@ class NBodySystB200:
     def fused(self) -> bool:
         return bool(self._q(L.Q_FUSED))
 
+    @property
+    def fused_version(self) -> int:
+        """0 = staged kernels, 3 / 4 = version of the fused kernel serving this nint level."""
+        return self._q(L.Q_FUSED)
+
     def set_chunk(self, chunk: int) -> None:
         L.check(self._lib, self._lib.chb_plan_set_chunk(self._plan, int(chunk)))
         self._ws = None
@@ -116,7 +121,7 @@ class NBodySystB200:
     def set_fused(self, enable) -> None:
         """False/0: generic staged kernels only; True/2: fused kernel (default); 1: fused kernel with separate
         load/store phases (kept for A/B measurements)."""
-        level = 3 if enable is True else int(enable)
+        level = 4 if enable is True else int(enable)
         L.check(self._lib, self._lib.chb_plan_set_fused(self._plan, level))
 
     # ------------------------------------------------------------------ plumbing

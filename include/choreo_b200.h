@@ -115,7 +115,7 @@ enum chb_query {
     CHB_Q_DEVICE = 8,
     CHB_Q_CHUNK = 9,          /* states processed per internal launch group             */
     CHB_Q_LAUNCHES = 10,      /* kernels launched by this plan since creation (counter)  */
-    CHB_Q_FUSED = 11,         /* 1 if the fused single-kernel action+grad path is active */
+    CHB_Q_FUSED = 11,         /* 0: staged kernels; else the version of the fused single-kernel path that serves this level (3 or 4) */
     CHB_Q_SEGMPOS_SIZE = 12   /* nsegm*segm_store*geodim                                 */
 };
 
@@ -131,8 +131,9 @@ int chb_plan_destroy(chb_plan *plan);
 int chb_plan_query(const chb_plan *plan, int what, int64_t *value_out);
 /* 0 = auto; otherwise number of states per internal launch group (L2 residency knob) */
 int chb_plan_set_chunk(chb_plan *plan, int64_t chunk);
-/* 0 = generic staged kernels only; 2 = fused kernel when the layout supports it (default): parameter load and result
- * store are part of the first / last FFT pass; 1 = same kernel with separate load / store phases (A/B measurements) */
+/* 0 = generic staged kernels only; 4 (default) = newest fused kernel the layout supports: version 4 (rows moved by bulk
+ * asynchronous copies, natural-order in-place passes) for 4096-sample RFFT loops, else version 3; 3 = force version 3
+ * (A/B measurements) */
 int chb_plan_set_fused(chb_plan *plan, int enable);
 
 /* bytes of device workspace any *_dev operator below needs for `batch` states */

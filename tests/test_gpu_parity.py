@@ -140,6 +140,40 @@ def test_full_size_batch_properties(chb):
     assert float(((s1 - s2).abs() / s1.abs().clamp_min(1e-300)).max()) < 1e-9
 
 
+def test_fused_v4_matches_v3_and_oracle(chb):
+    """Version 4 of the fused kernel (bulk asynchronous row copies, natural-order in-place passes) against version 3 and the
+    oracle, with several states per persistent CTA (load barriers change phase, buffers are refilled while stores drain)."""
+    import torch
+    from oracle.choreo_oracle import OracleSyst
+    T = _tables("3B")
+    nbs = chb.NBodySystB200(T, 4096)
+    assert nbs.fused_version == 4
+    B = 148 * 3 + 17
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.rand((B, nbs.nparams), dtype=torch.float64, device="cuda", generator=gen)
+    dx = torch.rand((B, nbs.nparams), dtype=torch.float64, device="cuda", generator=gen)
+    a4, g4 = nbs.params_to_action_and_grad(x)
+    seg = nbs.params_to_segmpos(x)
+    h4 = nbs.segmpos_dparams_to_action_hess(seg, dx)
+    nbs.set_fused(3)
+    assert nbs.fused_version == 3
+    a3, g3 = nbs.params_to_action_and_grad(x)
+    h3 = nbs.segmpos_dparams_to_action_hess(seg, dx)
+    nbs.set_fused(True)
+    assert float(((a4 - a3).abs() / a3.abs()).max()) < TOL_ACTION
+    assert float(((g4 - g3).abs().amax(1) / g3.abs().amax(1)).max()) < TOL_GRAD
+    assert float(((h4 - h3).abs().amax(1) / h3.abs().amax(1)).max()) < TOL_HESS
+    O = OracleSyst(T, 4096, backend="fft")
+    for b in (0, 147, 148, B - 1):
+        xb, dxb = x[b].cpu().numpy(), dx[b].cpu().numpy()
+        assert relerr(a4[b].item(), O.params_to_action(xb)) < TOL_ACTION
+        assert relerr(g4[b].cpu().numpy(), O.params_to_action_grad(xb)) < TOL_GRAD
+        assert relerr(h4[b].cpu().numpy(), O.segmpos_dparams_to_action_hess(seg[b].cpu().numpy(), dxb)) < TOL_HESS
+    # the host-pointer path (pipelined slices) runs the same kernel
+    ah, gh = nbs.params_to_action_and_grad(x[:5].cpu().numpy())
+    assert relerr(ah, a4[:5].cpu().numpy()) < TOL_ACTION and relerr(gh, g4[:5].cpu().numpy()) < TOL_GRAD
+
+
 def test_gradient_is_derivative_of_action(chb):
     """Finite differences with the non-singular law (tests/test_NBodySyst.py:377-455)."""
     import dataclasses

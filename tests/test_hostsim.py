@@ -129,3 +129,29 @@ def test_krylov_jacobian_glue(sim, golden_cache):
     jac.setup(x.copy(), nbs.params_to_action_grad(x), nbs.params_to_action_grad)
     assert relerr(jac.matvec(v("dparams")), v("hess_cached")) < TOL_HESS
     assert relerr(jac.segmpos, v("segmpos")) < TOL_TRANSFORM
+
+
+def test_hostsim_fused_v4_persistent_batch(sim):
+    """Version 4 of the fused CTA program (chb_fused4.cuh) with more states than CTAs in the emulated grid: every CTA
+    refills its buffers from the next state's rows; results must equal version 3 to rounding and the oracle to tolerance."""
+    import os
+    from conftest import ROOT
+    from oracle.choreo_oracle import OracleSyst
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3B.npz"))
+    nbs = NBodySystB200(T, 4096, _lib_handle=sim)
+    assert nbs.fused_version == 4
+    B = 150  # the emulated grid has 148 CTAs: states 148, 149 are second states
+    rng = np.random.default_rng(5)
+    x, dx = rng.random((B, nbs.nparams)), rng.random((B, nbs.nparams))
+    a4, g4 = nbs.params_to_action_and_grad(x)
+    seg = nbs.params_to_segmpos(x[-2:])
+    h4 = nbs.segmpos_dparams_to_action_hess(seg, dx[-2:])
+    nbs.set_fused(3)
+    assert nbs.fused_version == 3
+    a3, g3 = nbs.params_to_action_and_grad(x)
+    h3 = nbs.segmpos_dparams_to_action_hess(seg, dx[-2:])
+    assert relerr(a4, a3) < TOL_ACTION and relerr(g4, g3) < TOL_GRAD and relerr(h4, h3) < TOL_HESS
+    O = OracleSyst(T, 4096, backend="fft")
+    for b in (0, 148, 149):
+        assert relerr(a4[b], O.params_to_action(x[b])) < TOL_ACTION
+        assert relerr(g4[b], O.params_to_action_grad(x[b])) < TOL_GRAD
