@@ -337,8 +337,10 @@ def run_b200(args):
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "peak_source": peak_src,
-        "kernel": ("k_fused<NSEG,1>: 1 launch per step, persistent CTAs (one resident wave), one state at a time per CTA, whole "
-                   "evaluation in shared memory, parameter rows stashed in tensor memory" if nbs.fused else
+        "kernel": (("k_fused4<NSEG,1>" if nbs.fused_version >= 4 else "k_fused<NSEG,1>") +
+                   ": 1 launch per step, persistent CTAs (one resident wave), one state at a time per CTA, whole evaluation "
+                   "in shared memory, parameter rows stashed in tensor memory" +
+                   (", rows moved by cp.async.bulk per warp" if nbs.fused_version >= 4 else "") if nbs.fused else
                    f"staged path: {launches_per_step} launches per step (k_fwd, k_pair<1>, k_adj, k_finish per chunk); "
                    "achieved = whole-step algorithmic bytes / whole-step time"),
         "alg_bytes_per_unit": alg_bytes_per_unit, "units_per_launch": B,
@@ -381,7 +383,7 @@ def run_b200(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": workload_config(args, npar, world),
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-            "fused": bool(nbs.fused),
+            "fused": bool(nbs.fused), "fused_version": int(nbs.fused_version),
         }
         if stages:
             line["stages"] = stages

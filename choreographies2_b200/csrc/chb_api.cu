@@ -571,6 +571,12 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
                  FL.nco_in <= 2 && FL.tw_soff[0] >= 0 && FL.tw_soff[1] >= 0;
         }
         for (int s = 0; s < T.nsegm && ok; ++s) ok = F.segs[s].row0 == 0 && F.segs[s].loop == s;
+        if (ok && p->fused_smem + 256 * sizeof(cd) + 512 <= p->smem_limit) {  // full 16 x 16 twiddle table of pass "k1"
+            F.tw4_off = (int)((p->fused_smem - CHF_RED_BYTES) / sizeof(cd));
+            p->fused_smem += 256 * sizeof(cd);
+        } else {
+            ok = false;
+        }
         p->fused4_ok = ok ? 1 : 0;
     }
     return 1;
@@ -1002,6 +1008,7 @@ struct DevGrp {
     }
     __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
     __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+    __device__ __forceinline__ void tma_store_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
     __device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
     __device__ __forceinline__ void warp_sync() { __syncwarp(); }
     // f(warp of the group, lane) on every thread, no barrier
@@ -1150,6 +1157,7 @@ struct HostGrp {
     void tma_store(void *dst, const void *src, unsigned bytes) { memcpy(dst, src, bytes); }
     void tma_store_commit() {}
     void tma_store_wait_read() {}
+    void tma_store_wait_read1() {}
     void fence_async() {}
     template <class S, class F1, class F2>
     void par2(F1 f1, F2 f2) {

@@ -61,6 +61,7 @@ struct ChfSys {
     int tw_src_loop;               // loop whose tables the region holds (loops of equal length share them)
     int dbg;        // profiling only (env CHB_FUSED_DBG): bit 0..5 skip load pass / inverse passes / pair / forward passes / store pass / reduce
     int pair_fast;  // gravity, every pair s < t interacts once with identity rotation, segments are plain slices
+    int tw4_off;    // version 4: cd offset (from the loop buffers' base) of the full table w256^(q t), [q][t], of pass "k1"
     int stagger_ns; // version 4: CTA i starts i / gridDim * stagger_ns late so that the CTAs' copy phases do not coincide
     int pf_stride;  // > 0: CTA b asks L2 for the parameters of state b + pf_stride while it computes (co-resident CTA count)
     long long nparams, segsz;

@@ -34,7 +34,7 @@
 CHB_HD int ch4_nruns(int a) { return a == 0 ? 24 : 16; }
 CHB_HD void ch4_run(int a, int idx, int *r0, int *nr) {
     if (a == 0) {
-        const int q = idx / 3, kind = idx - 3 * q;
+        const int q = (idx * 11) >> 5, kind = idx - 3 * q;  // idx / 3 for idx < 24
         *r0 = 256 * q + (kind == 0 ? 0 : (kind == 1 ? 241 : 128));
         *nr = kind == 0 ? 16 : (kind == 1 ? 15 : 1);
     } else {
@@ -74,8 +74,8 @@ CHB_D void ch4_issue_stores(Grp &grp, const ChfLoop &L, double *out_b, const cd 
         int d0, nd;
         ch4_run_doubles(L, a, lane, &d0, &nd);
         grp.tma_store(rows + d0, src + d0, (unsigned)nd * 8u);
-        grp.tma_store_commit();
     }
+    grp.tma_store_commit();  // every lane commits one (possibly empty) group per pass: wait_group counts are uniform
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -218,27 +218,26 @@ struct Ch4S {
 };
 // radix 16 over k1 <-> u (length-256 stage, twiddles w256^(k1 t)): SIGN +1 reads natural / writes swizzled, -1 the reverse
 template <int SIGN, class Grp>
-CHB_D void ch4_pass_k1(Grp &grp, cd *buf, const cd *tw1) {
+CHB_D void ch4_pass_k1(Grp &grp, cd *buf, const cd *tw4) {
     for (int i = 0; i < 2; ++i) {
         grp.template par2<Ch4S>(
             [&](int tid, int T, Ch4S &s) {
                 (void)T;
                 const int t_lo = tid & 1, k0 = ((tid >> 1) & 7) + 8 * i, t_hi = tid >> 4;
                 const cd *p = buf + ((t_hi << 9) | t_lo);
-                cd w[16];
-                chf_twiddle_powers<16, SIGN>(w, tw1 + (2 * t_hi + t_lo), 16);
+                const cd *wt = tw4 + (2 * t_hi + t_lo);  // w256^(q t) at wt[16 q], conjugated for the backward transform
                 if (SIGN > 0) {
 #pragma unroll
                     for (int q = 0; q < 16; ++q) s.a[q] = p[32 * q + 2 * k0];
 #pragma unroll
-                    for (int q = 1; q < 16; ++q) s.a[q] = cmul(s.a[q], w[q]);
+                    for (int q = 1; q < 16; ++q) s.a[q] = cmul(s.a[q], cconj(wt[16 * q]));
                     ChfDft<16, SIGN>::run(s.a);
                 } else {
 #pragma unroll
                     for (int q = 0; q < 16; ++q) s.a[q] = p[32 * q + 2 * (k0 ^ (q & 3))];
                     ChfDft<16, SIGN>::run(s.a);
 #pragma unroll
-                    for (int q = 1; q < 16; ++q) s.a[q] = cmul(s.a[q], w[q]);
+                    for (int q = 1; q < 16; ++q) s.a[q] = cmul(s.a[q], wt[16 * q]);
                 }
             },
             [&](int tid, int T, Ch4S &s) {
@@ -360,6 +359,21 @@ CHB_D void cta_fused4_prologue(Ctx &ctx, const ChfSys &F, cd *sm) {
         }
         cd *d1 = sm + F.tw_smem_off + L.tw_soff[1];
         for (int i = tid; i < 4 * 16; i += nthr) d1[i] = L.tw[1][i];
+        // pass "k1": all 15 twiddles of a butterfly are read, not generated: w256^(q t) at [q][t] (exact table entries
+        // exp(-2 pi i j 2^e / 256) of stage 1 combined: q t = sum of at most four powers of two times j <= 15 ... simpler and
+        // as accurate: one correctly rounded sincospi per entry, the argument q t / 128 is exact)
+        cd *d4 = sm + F.tw4_off;
+        for (int i = tid; i < 256; i += nthr) {
+            const int q = i >> 4, t = i & 15;
+            double sn, cs;
+#if defined(__CUDA_ARCH__)
+            sincospi((double)(q * t) / 128.0, &sn, &cs);
+#else
+            sn = sin(3.14159265358979323846 * (double)(q * t) / 128.0);
+            cs = cos(3.14159265358979323846 * (double)(q * t) / 128.0);
+#endif
+            d4[i] = mk(cs, -sn);
+        }
     });
 }
 
@@ -386,7 +400,7 @@ CHB_D void cta_fused4(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, 
     double *seg_out_b = A.seg_out ? A.seg_out + b * F.segsz : (double *)0;
     double *out_b = A.vec_out + b * F.nparams;
     const cd *tw0p = sm + F.tw_smem_off + F.loops[F.tw_src_loop].tw_soff[0];
-    const cd *tw1 = sm + F.tw_smem_off + F.loops[F.tw_src_loop].tw_soff[1];
+    const cd *tw1 = sm + F.tw4_off;
     ctx.groups(F.nloop, F.T, [&](auto &grp) {
         const ChfLoop &L = F.loops[grp.g];
         cd *buf = sm + L.smem_off;
@@ -420,16 +434,17 @@ CHB_D void cta_fused4(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, 
             if (!(F.dbg & 16)) ch4_store_pass(grp, L, buf, red, A.kin_from == 2, A.kin_src != (const double *)0, it, F.dbg);
             grp.lanes([&](int warp, int lane) { ch4_issue_stores(grp, L, out_b, buf, warp, lane, it); });
         }
-        grp.lanes([&](int warp, int lane) {
-            (void)warp; (void)lane;
-            grp.tma_store_wait_read();  // the engine has read this lane's rows ...
-        });
-        grp.warp_sync();                // ... and those of the other lanes of the warp: the warp's rows may be refilled
-        if (b_next < A.nstates)
+        // the rows of pass 0 were handed over one store pass ago: refill them first, the load pass of the next state starts
+        // on them while the rows of pass 1 are still draining
+        for (int it = 0; it < 2; ++it) {
             grp.lanes([&](int warp, int lane) {
-                ch4_issue_loads(grp, L, A.vec_in + b_next * F.nparams, buf, warp, lane, 0);
-                ch4_issue_loads(grp, L, A.vec_in + b_next * F.nparams, buf, warp, lane, 1);
+                (void)warp; (void)lane;
+                if (it == 0) grp.tma_store_wait_read1(); else grp.tma_store_wait_read();  // the engine has read this lane's rows ...
             });
+            grp.warp_sync();  // ... and those of the other lanes of the warp: the warp's rows of this pass may be refilled
+            if (b_next < A.nstates)
+                grp.lanes([&](int warp, int lane) { ch4_issue_loads(grp, L, A.vec_in + b_next * F.nparams, buf, warp, lane, it); });
+        }
     });
     if (A.scalar_out && !(F.dbg & 32)) {
         cta_reduce(ctx, red);
