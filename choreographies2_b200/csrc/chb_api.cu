@@ -85,6 +85,9 @@ struct chb_plan {
     std::vector<int> loop_in_smem;
     int pair_threads = 256;
     size_t pair_smem[3] = {0, 0, 0};
+    int pair_dense_enabled = 1;  // dense pair kernel when the level's interaction graph allows it (A/B knob: CHB_PAIR_DENSE=0)
+    int dense_threads = 256;
+    size_t dense_smem[3] = {0, 0, 0};
     // staging for chb_run_host
     std::mutex host_mutex;
     void *stage_dev = nullptr;
@@ -837,6 +840,28 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
         p->pair_smem[0] = red_bytes + arr;       // energy only: spos
         p->pair_smem[1] = red_bytes + 2 * arr;   // + sout
         p->pair_smem[2] = red_bytes + 3 * arr;   // + sdpos
+        // dense pair kernel (cta_pair_dense): planar, identity BinSpaceRot everywhere, no self-interaction, and enough
+        // interactions per segment that evaluating every pair from both sides beats the coloured scatter
+        bool dense = G == 2 && T.nsegm >= 2 && T.nbin >= 2 * T.nsegm;
+        for (int b = 0; b < T.nbin && dense; ++b) dense = T.bin_isid[b] && T.bin_src[b] != T.bin_tgt[b];
+        const int spad = (T.nsegm + 31) / 32 * 32;
+        if (dense && spad <= 256) {
+            std::vector<double> Wm((size_t)T.nsegm * spad, 0.0);
+            for (int b = 0; b < T.nbin; ++b) {
+                Wm[(size_t)T.bin_src[b] * spad + T.bin_tgt[b]] += T.bin_fac[b];
+                Wm[(size_t)T.bin_tgt[b] * spad + T.bin_src[b]] += T.bin_fac[b];
+            }
+            int rcw = level_upload(p, Wm, &S.pair_w);
+            if (rcw) { free_level(p); return rcw; }
+            S.pair_spad = spad;
+            const size_t arrd = (size_t)tile * spad * sizeof(cd), wbytes = (size_t)T.nsegm * spad * sizeof(double);
+            p->dense_threads = 256 / spad * spad >= spad ? 256 : spad;
+            p->dense_smem[0] = red_bytes + wbytes + arrd;
+            p->dense_smem[1] = red_bytes + wbytes + 2 * arrd;
+            p->dense_smem[2] = red_bytes + wbytes + 3 * arrd;
+            S.pair_dense = p->dense_smem[2] <= p->smem_limit ? 1 : 0;
+        }
+        if (getenv("CHB_PAIR_DENSE") && atoi(getenv("CHB_PAIR_DENSE")) == 0) S.pair_dense = 0;
     }
     p->nint = nint;
     p->ready = true;
@@ -1238,6 +1263,22 @@ CHB_KERNEL void k_pair(ChbSys S, const double *seg, const double *dseg, double *
                    globalmul, spos, sdpos, sout, red);
 }
 
+template <int MODE>
+CHB_KERNEL void k_pair_dense(ChbSys S, const double *seg, const double *dseg, double *out, double *pot_part, double globalmul) {
+    CHB_CTX_DECL;
+    const long long blk = CHB_BLOCK_ID;
+    const int tile = (int)(blk % S.pair_ntiles);
+    const long long b = blk / S.pair_ntiles;
+    double *red = (double *)CHB_SMEM;
+    double *sw = red + 1024;
+    cd *spos = (cd *)(sw + (size_t)S.nsegm * S.pair_spad);
+    cd *sout = spos + (size_t)S.pair_tile * S.pair_spad;
+    cd *sdpos = sout + (size_t)S.pair_tile * S.pair_spad;
+    cta_pair_dense<MODE>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
+                         out ? out + b * S.segsz : (double *)0, pot_part ? pot_part + b * S.pair_ntiles + tile : (double *)0, tile,
+                         globalmul, CHB_NTHREADS, spos, sdpos, sout, sw, red);
+}
+
 CHB_KERNEL void k_kin(ChbSys S, const double *params, double *kin_out, int kin_stride) {
     CHB_CTX_DECL;
     const long long b = CHB_BLOCK_ID;
@@ -1435,6 +1476,15 @@ static int launch_adj(chb_plan *p, int64_t nb, const double *seg, double *out, c
 static int launch_pair(chb_plan *p, int mode, int64_t nb, const double *seg, const double *dseg, double *out,
                        double *pot_part, double globalmul, chb_stream_t st) {
     const long long grid = nb * p->sys.pair_ntiles;
+    if (p->sys.pair_dense) {
+        if (mode == 0)
+            CHB_LAUNCH(p, k_pair_dense<0>, grid, p->dense_threads, p->dense_smem[1], st, p->sys, seg, dseg, out, pot_part, globalmul);
+        else if (mode == 1)
+            CHB_LAUNCH(p, k_pair_dense<1>, grid, p->dense_threads, p->dense_smem[1], st, p->sys, seg, dseg, out, pot_part, globalmul);
+        else
+            CHB_LAUNCH(p, k_pair_dense<2>, grid, p->dense_threads, p->dense_smem[2], st, p->sys, seg, dseg, out, pot_part, globalmul);
+        return CHB_OK;
+    }
     if (mode == 0)
         CHB_LAUNCH(p, k_pair<0>, grid, p->pair_threads, p->pair_smem[0], st, p->sys, seg, dseg, out, pot_part, globalmul);
     else if (mode == 1)

@@ -110,6 +110,10 @@ struct ChbSys {
     int nround;
     const int *round_off;  // [nround+1]
     int pair_tile, pair_ntiles;
+    // dense pair kernel (cta_pair_dense): symmetric weight matrix W[s][t] = sum of BinProdChargeSum over the bins {s,t},
+    // [nsegm][pair_spad], pair_spad = nsegm rounded up to a multiple of 32; pair_dense = 1 when the level uses it
+    int pair_dense, pair_spad;
+    const double *pair_w;
     long long scratch_per_state;  // cd slots
 };
 
@@ -730,4 +734,123 @@ CHB_HD double chb_finish_action(const double *kin_part, int nk, const double *po
     for (int i = 0; i < nk; ++i) k += kin_part[i];
     for (int i = 0; i < np; ++i) p += pot_part[i];
     return k + psign * p;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Dense pair kernel for the compute-bound regime (64 segments, 2016 interactions per sample).
+// Conditions (checked at plan time): planar, every BinSpaceRot the identity.  Then the scatter of segm_pos_to_pot_nrg_grad /
+// _hess (:6502-6529, :6927-6958) is symmetric: segment t receives  -f_st [V' d]  resp.  -f_st [2 V'' (d.dd) d + V' dd]
+// from every partner s, with d = x_s - x_t, dd = dx_s - dx_t, f_st = 2 w_i W[s][t] / segm_size * globalmul, whether t is the
+// bin's source or its target.  One thread owns (sample i, segment t) and accumulates in REGISTERS over all s: x_s is a
+// broadcast read (the lanes of a warp share i), W[s][t] a conflict-free one; no shared-memory read-modify-write, no colour
+// rounds, no barriers inside the loop.  Every unordered pair is evaluated twice (once per side): that doubles the FP64 work of
+// the pair sum but removes the scatter, which is what bounded the generic kernel (cta_pair) on this shape.
+// Gravity uses the closed forms V = -r, V' = r^3/2, V'' = -3 r^5/4 with r = (x^2)^(-1/2) from the hardware seed and one
+// third-order correction step (relative error of the seed 2^-20 -> below 2^-55).
+// ------------------------------------------------------------------------------------------------
+CHB_HD double chb_rsqrt_fast(double d) {
+#if defined(__CUDA_ARCH__)
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+    const double e = fma(-d * y, y, 1.0);
+    return fma(y * e, fma(e, 0.375, 0.5), y);
+#else
+    return 1.0 / sqrt(d);
+#endif
+}
+
+template <int MODE, class Ctx>
+CHB_D void cta_pair_dense(Ctx &ctx, const ChbSys &S, const double *seg_b, const double *dseg_b, double *out_b,
+                           double *pot_out, int tile, double globalmul, int nthreads, cd *spos, cd *sdpos, cd *sout,
+                           double *sw, double *red) {
+    const int T = S.pair_tile, store = S.segm_store, nS = S.nsegm, SP = S.pair_spad;
+    const int i0 = tile * T;
+    const int n = (store - i0) < T ? (store - i0) : T;
+    ctx.par([&](int tid, int nthr) {
+        for (int idx = tid; idx < nS * n; idx += nthr) {
+            const int s = idx / n, i = idx - s * n;
+            const long long src = (long long)s * store + i0 + i;
+            spos[i * SP + s] = ((const cd *)seg_b)[src];
+            if (MODE == 2) sdpos[i * SP + s] = ((const cd *)dseg_b)[src];
+        }
+        for (int idx = tid; idx < nS * SP; idx += nthr) sw[idx] = S.pair_w[idx];
+        red[tid] = 0.0;
+    });
+    const double inv_size = 1.0 / (double)S.segm_size;
+    const int nI = nthreads / SP;  // samples in flight
+    ctx.par([&](int tid, int nthr) {
+        (void)nthr;
+        const int t = tid % SP, il = tid / SP;
+        if (t >= nS || il >= nI) return;
+        double esum = 0.0;
+        for (int i = il; i < n; i += nI) {
+            const int gi = i0 + i;
+            const double wi = (store != S.segm_size && (gi == 0 || gi == store - 1)) ? 0.5 : 1.0;
+            const cd *xrow = spos + i * SP;
+            const cd *drow = sdpos + i * SP;
+            const cd xt = xrow[t];
+            cd dxt = mk(0.0, 0.0);
+            if (MODE == 2) dxt = drow[t];
+            double gx = 0.0, gy = 0.0, e = 0.0;
+#pragma unroll 4
+            for (int s = 0; s < nS; ++s) {
+                const double w = sw[s * SP + t];
+                const cd xs = xrow[s];
+                const double dx = xs.x - xt.x, dy = xs.y - xt.y;
+                double xsq = fma(dx, dx, dy * dy);
+                xsq = (s == t) ? 1.0 : xsq;  // W[t][t] = 0: the term vanishes, keep it finite
+                if (S.law_kind == 0) {
+                    const double r = chb_rsqrt_fast(xsq);
+                    const double r2 = r * r;
+                    const double c = w * (r2 * r);    // 2 V' w
+                    if (MODE <= 1) e = fma(w, r, e);  // -V w
+                    if (MODE == 1) {
+                        gx = fma(c, dx, gx);
+                        gy = fma(c, dy, gy);
+                    } else if (MODE == 2) {  // 2 (2 V'' (d.dd) d + V' dd) = r^3 (dd - 3 r^2 (d.dd) d)
+                        const cd ds = drow[s];
+                        const double ddx = ds.x - dxt.x, ddy = ds.y - dxt.y;
+                        const double k3 = 3.0 * r2 * fma(dx, ddx, dy * ddy);
+                        gx = fma(c, fma(-k3, dx, ddx), gx);
+                        gy = fma(c, fma(-k3, dy, ddy), gy);
+                    }
+                } else {
+                    double V, V1, V2;
+                    chb_inter_law(S, xsq, &V, &V1, &V2);
+                    if (MODE <= 1) e = fma(-w, V, e);
+                    if (MODE == 1) {
+                        const double c = 2.0 * w * V1;
+                        gx = fma(c, dx, gx);
+                        gy = fma(c, dy, gy);
+                    } else if (MODE == 2) {
+                        const cd ds = drow[s];
+                        const double ddx = ds.x - dxt.x, ddy = ds.y - dxt.y;
+                        const double bb = 2.0 * V2 * fma(dx, ddx, dy * ddy);
+                        gx = fma(2.0 * w, fma(bb, dx, V1 * ddx), gx);
+                        gy = fma(2.0 * w, fma(bb, dy, V1 * ddy), gy);
+                    }
+                }
+            }
+            // g_t = -w_i / segm_size * globalmul * sum_s [...] (the factor 2 and W[s][t] are inside the sums)
+            const double f = -wi * inv_size * globalmul;
+            if (MODE >= 1) sout[i * SP + t] = mk(f * gx, f * gy);
+            esum = fma(-0.5 * wi * inv_size, e, esum);  // ordered pairs count every bin twice; e holds -sum V w
+        }
+        if (MODE <= 1) red[tid] += esum;
+    });
+    if (MODE >= 1) {
+        ctx.par([&](int tid, int nthr) {
+            for (int idx = tid; idx < nS * n; idx += nthr) {
+                const int s = idx / n, i = idx - s * n;
+                ((cd *)out_b)[(long long)s * store + i0 + i] = sout[i * SP + s];
+            }
+        });
+    }
+    if (MODE <= 1 && pot_out) {
+        cta_reduce(ctx, red);
+        ctx.par([&](int tid, int nthr) {
+            (void)nthr;
+            if (tid == 0) *pot_out = red[0];
+        });
+    }
 }
