@@ -1,0 +1,296 @@
+"""Batched lock-step Newton-Krylov root solve of ``grad Action(x) = 0`` over many independent states.
+
+Restates, for a batch, the solver the reference drives one state at a time:
+  * outer iteration, inexact-Newton forcing terms, termination: ``choreo/scipy_plus/nonlin.py:54-171`` (``nonlin_solve_pp``);
+  * line search: ``nonlin.py:190-234`` (``_nonlin_line_search_pp``) with scipy's ``scalar_search_armijo`` (c1 = 1e-4,
+    quadratic then cubic interpolation, ``amin = smin``; fall back to ``s = smin``);
+  * linear solves: scipy ``KrylovJacobian(method='gmres')`` as wired by ``NBodySyst.GetKrylovJacobian``
+    (``_NBodySyst.pyx:2004-2032``): GMRES(restart = inner_maxiter = 20, maxiter = 1, atol = 0, rtol = tol), zero initial guess,
+    matvec = ``segmpos_dparams_to_action_hess(segmpos, v)`` with ``segmpos = params_to_segmpos(x)`` cached per Newton step.
+
+All states advance in lock step; a state that has converged (or failed) is masked out, and every evaluation runs only on the
+compacted set of states that still need it.  The heavy operations are the library's batched operators (U1 / U2 of SURVEY
+8(d)); the vector algebra between them (dot products, axpys, Givens rotations on [B, 21] arrays) is array-carrier work:
+NumPy for host arrays, torch for CUDA tensors.  Summation order differs from scipy's one-state GMRES, so iterates agree to
+rounding and converged orbits to the solver tolerance, not bit for bit.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Any, Optional
+
+import numpy as np
+
+
+class _XP:
+    """The few array operations the driver needs, for NumPy arrays or torch tensors."""
+
+    def __init__(self, like: Any):
+        self.torch = type(like).__module__.startswith("torch")
+        if self.torch:
+            import torch
+            self.t = torch
+            self.dev = like.device
+
+    def zeros(self, shape, dtype="f8"):
+        if self.torch:
+            dt = {"f8": self.t.float64, "i8": self.t.int64, "b": self.t.bool}[dtype]
+            return self.t.zeros(shape, dtype=dt, device=self.dev)
+        return np.zeros(shape, dtype={"f8": np.float64, "i8": np.int64, "b": bool}[dtype])
+
+    def full(self, shape, v):
+        return self.zeros(shape) + v
+
+    def copy(self, a):
+        return a.clone() if self.torch else a.copy()
+
+    def dot(self, a, b):  # row-wise
+        return (a * b).sum(-1)
+
+    def norm(self, a):
+        return self.sqrt(self.dot(a, a))
+
+    def maxabs(self, a):
+        return a.abs().amax(-1) if self.torch else np.abs(a).max(-1)
+
+    def sqrt(self, a):
+        return self.t.sqrt(a) if self.torch else np.sqrt(a)
+
+    def abs(self, a):
+        return a.abs() if self.torch else np.abs(a)
+
+    def where(self, c, a, b):
+        return self.t.where(c, a, b) if self.torch else np.where(c, a, b)
+
+    def minimum(self, a, b):
+        return self.t.minimum(a, b) if self.torch else np.minimum(a, b)
+
+    def maximum(self, a, b):
+        return self.t.maximum(a, b) if self.torch else np.maximum(a, b)
+
+    def nonzero(self, m):
+        return self.t.nonzero(m).reshape(-1) if self.torch else np.nonzero(m)[0]
+
+    def any(self, m) -> bool:
+        return bool(m.any())
+
+    def isfinite_rows(self, a):
+        return self.t.isfinite(a).all(-1) if self.torch else np.isfinite(a).all(-1)
+
+    def to_numpy(self, a):
+        return a.detach().cpu().numpy() if self.torch else np.asarray(a)
+
+
+@dataclass
+class NewtonResult:
+    x: Any                 # [B, nparams] final iterates
+    status: np.ndarray     # [B] 1 converged, 2 iteration limit, 3 non-finite residual
+    nit: np.ndarray        # [B] Newton iterations used
+    fnorm: np.ndarray      # [B] max-norm of the final gradient
+    n_grad_evals: int      # U1 evaluations (states x calls)
+    n_hess_evals: int      # U2 evaluations
+
+
+def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20):
+    """One GMRES(restart) cycle per row of ``rhs`` ([A, n]) from a zero initial guess; row b stops at the first inner
+    iteration whose residual estimate is <= rtol[b] * |rhs[b]| (scipy.sparse.linalg.gmres with atol = 0, maxiter = 1).
+    ``matvec(idx, v)`` applies the operator of rows ``idx`` (None = all rows) to ``v``.  Modified Gram-Schmidt + Givens
+    rotations, as in scipy's implementation.  Returns (solution [A, n], inner iterations per row, number of row-matvecs)."""
+    A = rhs.shape[0]
+    m = int(restart)
+    beta = xp.norm(rhs)
+    safe_beta = xp.where(beta > 0, beta, beta + 1.0)
+    V = [rhs / safe_beta[:, None]]
+    R = xp.zeros((A, m + 1, m))
+    cs, sn = xp.zeros((A, m)), xp.zeros((A, m))
+    g = xp.zeros((A, m + 1))
+    g[:, 0] = beta
+    target = rtol * beta
+    done = ~(beta > 0)
+    kdone = xp.zeros((A,), "i8")
+    nmv = 0
+    for j in range(m):
+        idx = xp.nonzero(~done)
+        na = int(idx.shape[0])
+        if na == 0:
+            break
+        if na == A:
+            w = matvec(None, V[j])
+        else:
+            w = xp.zeros(rhs.shape)
+            w[idx] = matvec(idx, V[j][idx])
+        nmv += na
+        h = xp.zeros((A, m + 1))
+        for i in range(j + 1):
+            hij = xp.dot(w, V[i])
+            h[:, i] = hij
+            w = w - hij[:, None] * V[i]
+        hn = xp.norm(w)
+        h[:, j + 1] = hn
+        V.append(w / xp.where(hn > 0, hn, hn + 1.0)[:, None])
+        for i in range(j):  # previous rotations on the new column
+            t = cs[:, i] * h[:, i] + sn[:, i] * h[:, i + 1]
+            h[:, i + 1] = -sn[:, i] * h[:, i] + cs[:, i] * h[:, i + 1]
+            h[:, i] = t
+        den = xp.sqrt(h[:, j] * h[:, j] + h[:, j + 1] * h[:, j + 1])
+        den = xp.where(den > 0, den, den + 1.0)
+        c, s = h[:, j] / den, h[:, j + 1] / den
+        cs[:, j], sn[:, j] = c, s
+        h[:, j] = c * h[:, j] + s * h[:, j + 1]
+        h[:, j + 1] = 0.0
+        gj = g[:, j]
+        gnew = -s * gj
+        keep = done  # rows that stopped earlier keep their factorisation
+        R[:, :, j] = xp.where(keep[:, None], R[:, :, j], h)
+        g[:, j + 1] = xp.where(keep, g[:, j + 1], gnew)
+        g[:, j] = xp.where(keep, gj, c * gj)
+        kdone = xp.where(keep, kdone, kdone * 0 + (j + 1))
+        done = done | (xp.abs(g[:, j + 1]) <= target)
+    # back substitution on each row's own k x k triangle (columns >= k are the identity with a zero right-hand side)
+    y = xp.zeros((A, m))
+    for j in range(m - 1, -1, -1):
+        inside = kdone > j
+        acc = g[:, j]
+        for l in range(j + 1, m):
+            acc = acc - R[:, j, l] * y[:, l]
+        djj = xp.where(inside & (R[:, j, j] != 0), R[:, j, j], R[:, j, j] * 0 + 1.0)
+        y[:, j] = xp.where(inside, acc / djj, acc * 0)
+    sol = xp.zeros(rhs.shape)
+    for j in range(min(m, len(V))):
+        sol = sol + y[:, j][:, None] * V[j]
+    return sol, kdone, nmv
+
+
+def _take(xp: _XP, a, idx):
+    return a if idx is None else a[idx]
+
+
+def newton_krylov_batched(nbs, x0, f_tol: float = 1e-10, maxiter: int = 50, restart: int = 20, smin: float = 1e-2,
+                          line_search: Optional[str] = "armijo") -> NewtonResult:
+    """Solve ``nbs.params_to_action_grad(x) = 0`` for every row of ``x0`` ([B, nparams]; NumPy array or torch CUDA tensor).
+
+    Termination like the reference's ``TerminationCondition(f_tol=...)`` with the max norm (``nonlin.py:77-78``): a state is
+    converged when ``max |F| <= f_tol``; ``maxiter`` Newton iterations otherwise (status 2)."""
+    xp = _XP(x0)
+    x = xp.copy(x0)
+    B = x.shape[0]
+    n_grad = n_hess = 0
+
+    def func(idx, xs):
+        nonlocal n_grad
+        n_grad += int(xs.shape[0])
+        return nbs.params_to_action_grad(xs)
+
+    Fx = func(None, x)
+    Fnorm = xp.norm(Fx)
+    eta = xp.full((B,), 1e-3)
+    gamma, eta_max, eta_threshold = 0.9, 0.9999, 0.1  # nonlin.py:101-105
+    status = xp.zeros((B,), "i8")
+    nit = xp.zeros((B,), "i8")
+    for _ in range(int(maxiter)):
+        bad = ~xp.isfinite_rows(Fx)
+        status = xp.where((status == 0) & bad, status * 0 + 3, status)
+        conv = (status == 0) & (xp.maxabs(Fx) <= f_tol)
+        status = xp.where(conv, status * 0 + 1, status)
+        act = xp.nonzero(status == 0)
+        na = int(act.shape[0])
+        if na == 0:
+            break
+        allact = na == B
+        ia = None if allact else act
+        xa, Fa, Fna, etaa = _take(xp, x, ia), _take(xp, Fx, ia), _take(xp, Fnorm, ia), _take(xp, eta, ia)
+        seg = nbs.params_to_segmpos(xa)  # jacobian.setup / update (:2013-2019)
+
+        def matvec(idx, v):
+            nonlocal n_hess
+            n_hess += int(v.shape[0])
+            return nbs.segmpos_dparams_to_action_hess(seg if idx is None else seg[idx], v)
+
+        tol = xp.minimum(etaa, etaa * Fna)  # nonlin.py:113
+        sol, _, _ = gmres_batched(xp, matvec, Fa, tol, restart)
+        dx = -sol
+        # ---- line search on phi(s) = |F(x + s dx)|^2, scalar_search_armijo(phi, phi0, -phi0, amin=smin) per state ----
+        phi0 = Fna * Fna
+        if line_search is None:
+            s_fin = xp.full((na,), smin)
+            F_fin = func(None, xa + s_fin[:, None] * dx)
+        else:
+            c1 = 1e-4
+            s_fin = xp.full((na,), smin)
+            F_fin = xp.zeros(Fa.shape)
+            have = xp.zeros((na,), "b")          # F_fin holds F(x + s_fin dx)
+            search = xp.zeros((na,), "b") | True  # still searching
+            a0, a1 = xp.full((na,), 1.0), xp.full((na,), 1.0)
+            p0, p1 = xp.zeros((na,)), xp.zeros((na,))
+            for trial in range(40):
+                ids = xp.nonzero(search)
+                if int(ids.shape[0]) == 0:
+                    break
+                if trial == 0:
+                    alpha = a0
+                elif trial == 1:
+                    den = 2.0 * (p0 - phi0 + phi0 * a0)
+                    alpha = phi0 * a0 * a0 / xp.where(den != 0, den, den + 1e-300)
+                    a1 = alpha
+                else:
+                    factor = a0 * a0 * a1 * a1 * (a1 - a0)
+                    factor = xp.where(factor != 0, factor, factor + 1e-300)
+                    ca = (a0 * a0 * (p1 - phi0 + phi0 * a1) - a1 * a1 * (p0 - phi0 + phi0 * a0)) / factor
+                    cb = (-a0 * a0 * a0 * (p1 - phi0 + phi0 * a1) + a1 * a1 * a1 * (p0 - phi0 + phi0 * a0)) / factor
+                    ca = xp.where(ca != 0, ca, ca + 1e-300)
+                    alpha = (-cb + xp.sqrt(xp.abs(cb * cb + 3.0 * ca * phi0))) / (3.0 * ca)
+                sub_all = int(ids.shape[0]) == na
+                al = alpha if sub_all else alpha[ids]
+                Ft = func(None, (xa if sub_all else xa[ids]) + al[:, None] * (dx if sub_all else dx[ids]))
+                fin = xp.isfinite_rows(Ft)
+                pt = xp.where(fin, xp.dot(Ft, Ft), al * 0 + float("inf"))  # _safe_norm_pp
+                ph0 = phi0 if sub_all else phi0[ids]
+                ok = pt <= ph0 - c1 * al * ph0
+                if sub_all:
+                    ptf, okf = pt, ok
+                else:
+                    ptf = xp.full((na,), float("inf"))
+                    ptf[ids] = pt
+                    okf = xp.zeros((na,), "b")
+                    okf[ids] = ok
+                acc = search & okf
+                s_fin = xp.where(acc, alpha, s_fin)
+                if sub_all:
+                    F_fin = xp.where(acc[:, None], Ft, F_fin)
+                else:
+                    F_fin[ids[ok]] = Ft[ok]
+                have = have | acc
+                search = search & ~okf
+                if trial == 0:
+                    p0 = ptf
+                elif trial == 1:
+                    p1 = ptf
+                else:
+                    a2 = alpha
+                    halve = ((a1 - a2) > a1 / 2.0) | ((1.0 - a2 / a1) < 0.96)
+                    a2 = xp.where(halve, a1 / 2.0, a2)
+                    a0, a1, p0, p1 = a1, a2, p1, ptf
+                if trial >= 1:
+                    search = search & (a1 > smin)  # while alpha1 > amin (the failed ones fall back to s = smin)
+            miss = xp.nonzero(~have)
+            if int(miss.shape[0]) > 0:
+                F_fin[miss] = func(None, xa[miss] + s_fin[miss][:, None] * dx[miss])
+        xn = xa + s_fin[:, None] * dx
+        Fn_new = xp.norm(F_fin)
+        # forcing terms (nonlin.py:146-151)
+        eta_A = gamma * (Fn_new / Fna) ** 2
+        low = gamma * etaa * etaa < eta_threshold
+        eta_new = xp.where(low, xp.minimum(eta_A * 0 + eta_max, eta_A),
+                           xp.minimum(eta_A * 0 + eta_max, xp.maximum(eta_A, gamma * etaa * etaa)))
+        if allact:
+            x, Fx, Fnorm, eta = xn, F_fin, Fn_new, eta_new
+            nit = nit + 1
+        else:
+            x[act], Fx[act], Fnorm[act], eta[act] = xn, F_fin, Fn_new, eta_new
+            nit[act] = nit[act] + 1
+    else:
+        conv = (status == 0) & (xp.maxabs(Fx) <= f_tol)
+        status = xp.where(conv, status * 0 + 1, status)
+    status = xp.where(status == 0, status * 0 + 2, status)
+    return NewtonResult(x=x, status=xp.to_numpy(status), nit=xp.to_numpy(nit), fnorm=xp.to_numpy(xp.maxabs(Fx)),
+                        n_grad_evals=n_grad, n_hess_evals=n_hess)

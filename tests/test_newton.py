@@ -1,0 +1,104 @@
+"""Batched Newton-Krylov driver (choreographies2_b200/newton.py) against scipy's GMRES and the reference's own solver.
+
+CPU tests run the driver over the host emulation of the kernels (tests/hostsim); the reference arm is the UNMODIFIED
+``choreo.scipy_plus.nonlin.nonlin_solve_pp`` + ``NBodySyst.GetKrylovJacobian`` from oracle/_ref (skipped when it was not
+built), started from the same vectors with the same settings."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+from choreographies2_b200 import NBodySystB200, PlanTables
+from choreographies2_b200.newton import _XP, gmres_batched, newton_krylov_batched
+
+
+def test_gmres_batched_matches_scipy():
+    import scipy.sparse.linalg as sla
+    rng = np.random.default_rng(0)
+    A, n = 6, 48
+    Ms = [np.eye(n) * 3 + 0.3 * rng.standard_normal((n, n)) for _ in range(A)]
+    rhs = rng.standard_normal((A, n))
+    rhs[3] = 0.0
+    rtol = np.array([1e-3, 1e-8, 1e-1, 1e-3, 1e-12, 0.5])
+
+    def mv(idx, v):
+        ids = range(A) if idx is None else idx
+        return np.stack([Ms[i] @ v[k] for k, i in enumerate(ids)])
+
+    sol, k, nmv = gmres_batched(_XP(rhs), mv, rhs, rtol, 20)
+    assert nmv == int(k.sum())
+    for b in range(A):
+        ref, _ = sla.gmres(Ms[b], rhs[b], rtol=rtol[b], atol=0, restart=20, maxiter=1)
+        assert np.abs(sol[b] - ref).max() < 1e-12
+    assert k[3] == 0 and k[5] < k[0] <= 20
+
+
+def _figure_eight(lib):
+    z = np.load(os.path.join(ROOT, "tests", "golden", "sols.npz"))
+    name = "3C-Figure_eight"
+    pre = f"{name}/T/"
+    T = PlanTables.from_dict({k[len(pre):]: z[k] for k in z.files if k.startswith(pre)})
+    return NBodySystB200(T, int(z[f"{name}/nint"]), _lib_handle=lib), z[f"{name}/params"], float(z[f"{name}/stored_action"])
+
+
+@pytest.fixture(scope="module")
+def sim():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from hostsim import build_hostsim
+    return build_hostsim.load()
+
+
+def test_batched_newton_converges_to_fixture(sim):
+    nbs, xs, action = _figure_eight(sim)
+    rng = np.random.default_rng(0)
+    x0 = np.stack([xs + a * rng.standard_normal(nbs.nparams) for a in (1e-4, 1e-3, 1e-2, 0.0)])
+    res = newton_krylov_batched(nbs, x0, f_tol=1e-11, maxiter=30)
+    assert (res.status == 1).all() and res.nit[3] == 0 and (res.fnorm <= 1e-11).all()
+    for i in range(4):
+        assert abs(nbs.params_to_action(res.x[i]) - action) < 1e-9
+    # states do not influence each other: a batch equals the same states solved alone
+    one = newton_krylov_batched(nbs, x0[2:3], f_tol=1e-11, maxiter=30)
+    assert np.array_equal(one.x[0], res.x[2]) and one.nit[0] == res.nit[2]
+
+
+def test_batched_newton_matches_reference_solver(sim):
+    from oracle import ref_loader
+    if not ref_loader.reference_available():
+        pytest.skip("oracle/_ref not built")
+    choreo = ref_loader.import_reference()
+    from choreo.scipy_plus.nonlin import nonlin_solve_pp
+    NBS = ref_loader.build_named("3C")
+    nint = 3 * 2 * 32
+    NBS.nint = nint
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nbs = NBodySystB200(T, nint, _lib_handle=sim)
+    assert nbs.nparams == NBS.nparams
+    # starts like find.py:105-108,158: x = x_avg + x_ptp * U[0,1)
+    x_min, x_max = NBS.Make_params_bounds(0.1, 3, 50, 1e-16)
+    x_min, x_max = np.asarray(x_min), np.asarray(x_max)
+    x_avg, x_ptp = (x_min + x_min) / 2, x_max - x_min  # sic: find.py:106-107
+    starts = []
+    for seed in range(6):
+        np.random.seed(seed)
+        starts.append(x_avg + x_ptp * np.random.random(NBS.nparams))
+    x0 = np.stack(starts)
+    res = newton_krylov_batched(nbs, x0, f_tol=1e-9, maxiter=60)
+    nconv = 0
+    for i in range(x0.shape[0]):
+        jac = NBS.GetKrylovJacobian(True, {"method": "gmres"})
+        try:
+            xr, info = nonlin_solve_pp(NBS.params_to_action_grad, x0[i].copy(), jacobian=jac, f_tol=1e-9, maxiter=60,
+                                       line_search="armijo", full_output=True, raise_exception=False, smin=1e-2)
+        except Exception:
+            continue
+        if info["status"] != 1:
+            continue
+        # the reference converged from this start: so must the batched driver, to the same orbit
+        assert res.status[i] == 1, i
+        nconv += 1
+        ar, ab = NBS.params_to_action(xr), nbs.params_to_action(res.x[i])
+        assert abs(ar - ab) < 1e-7 * max(1.0, abs(ar)), (i, ar, ab)
+        assert abs(int(res.nit[i]) - int(info["nit"])) <= 3, (i, res.nit[i], info["nit"])
+    assert nconv >= 1
