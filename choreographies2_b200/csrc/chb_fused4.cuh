@@ -319,7 +319,7 @@ CHB_D void ch4_pair(Ctx &ctx, const ChfSys &F, cd *sm, const double *seg_in_b, d
 #pragma unroll
                 for (int t = s + 1; t < NSEG; ++t) {
                     const cd d = csub(x[s], x[t]);
-                    const double r = chf_rsqrt(fma(d.x, d.x, d.y * d.y));
+                    const double r = chb_rsqrt_fast(fma(d.x, d.x, d.y * d.y));  // seed + one third-order step: < 2^-55 relative
                     if (PMODE == 1) e = fma(w[s][t], r, e);
                     const double r2 = r * r;
                     const double c = w[s][t] * (r2 * r);

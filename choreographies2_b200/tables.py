@@ -173,6 +173,31 @@ class PlanTables:
     # ------------------------------------------------------------------ (de)serialisation
     _SCALARS = ("geodim", "nbody", "nloop", "nsegm", "nbin", "nint_min", "greater_nstore", "inter_law")
 
+    def make_params_bounds(self, nint: int, coeff_ampl_o: float = 1e-1, k_infl: int = 1, k_max: int = 200,
+                           coeff_ampl_min: float = 1e-16) -> Tuple[np.ndarray, np.ndarray]:
+        """``NBodySyst.Make_params_bounds`` (_NBodySyst.pyx:2301-2327): amplitude envelope of ``Make_Init_bounds_coeffs``
+        (:4447-4486; flat up to harmonic ``k_infl``, then exponential decay reaching ``coeff_ampl_min`` at ``k_max``) mapped to
+        the "mom" scaling by ``changevar_mom_pos_inv`` (:4662-4743).  Returns (x_min, x_max), each ``[nparams]``; the
+        reference draws initial guesses as ``x_min + (x_max - x_min) * U[0,1)`` (find.py:105-108,158)."""
+        lvl = self.level(nint)
+        slope = np.log(abs(coeff_ampl_o / coeff_ampl_min)) / (k_max - k_infl)
+        out = np.zeros(int(lvl.mom_off[-1]), dtype=np.float64)
+        for il in range(self.nloop):
+            ncm, nnz, nppl = int(self.ncoeff_min[il]), int(self.nnz[il]), int(self.nppl[il])
+            if nnz == 0:
+                continue
+            k = (np.arange(int(lvl.npr[il]))[:, None] * ncm + self.loop_nnz_k(il)[None, :]).astype(np.float64)
+            ampl = np.where(k <= k_infl, coeff_ampl_o, coeff_ampl_o * np.exp(-slope * (k - k_infl)))
+            loopmul = np.sqrt(float(self.loopnb[il]) * float(self.loopmass[il]) * 4.0 * np.pi ** 2)
+            mom = ampl * np.where(k > 0, loopmul * k, loopmul)
+            full = np.repeat(mom[:, :, None], nppl, axis=2).reshape(-1)
+            if self.loop_has_zero_freq(il):  # the co_in == False entries of (ipr = 0, ik = 0) are not parameters
+                keep = np.ones(full.shape[0], dtype=bool)
+                keep[:nppl] = self.loop_co_in(il).astype(bool)
+                full = full[keep]
+            out[int(lvl.mom_off[il]):int(lvl.mom_off[il + 1])] = full
+        return -out, out
+
     def to_dict(self) -> Dict[str, np.ndarray]:
         out: Dict[str, np.ndarray] = {}
         for f in dataclasses.fields(self):

@@ -102,3 +102,17 @@ def test_batched_newton_matches_reference_solver(sim):
         assert abs(ar - ab) < 1e-7 * max(1.0, abs(ar)), (i, ar, ab)
         assert abs(int(res.nit[i]) - int(info["nit"])) <= 3, (i, res.nit[i], info["nit"])
     assert nconv >= 1
+
+
+def test_make_params_bounds_matches_reference():
+    from oracle import ref_loader
+    if not ref_loader.reference_available():
+        pytest.skip("oracle/_ref not built")
+    ref_loader.import_reference()
+    from choreographies2_b200 import extract_tables
+    for name, nint in (("3C", 192), ("5Dq", 80), ("3B", 64), ("3D", 48)):
+        NBS = ref_loader.build_named(name)
+        NBS.nint = nint
+        lo, hi = map(np.asarray, NBS.Make_params_bounds(0.1, 3, 50, 1e-16))
+        mlo, mhi = extract_tables(NBS).make_params_bounds(nint, 0.1, 3, 50, 1e-16)
+        assert np.abs(lo - mlo).max() < 1e-300 + 1e-15 * np.abs(lo).max() and np.abs(hi - mhi).max() < 1e-15 * np.abs(hi).max()
