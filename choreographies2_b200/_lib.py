@@ -24,7 +24,8 @@ Q_NINT, Q_NPARAMS, Q_SEGM_SIZE, Q_SEGM_STORE, Q_NSEGM, Q_GEODIM, Q_NLOOP, Q_NBIN
     Q_FUSED, Q_SEGMPOS_SIZE = range(13)
 # enum chb_op
 (OP_PARAMS_TO_SEGMPOS, OP_SEGMPOS_TO_PARAMS, OP_SEGMPOS_TO_PARAMS_T, OP_ACTION, OP_ACTION_GRAD, OP_ACTION_HESS,
- OP_SEGMPOS_ACTION, OP_SEGMPOS_ACTION_GRAD, OP_SEGMPOS_ACTION_HESS, OP_KIN, OP_POT, OP_POT_GRAD, OP_POT_HESS) = range(13)
+ OP_SEGMPOS_ACTION, OP_SEGMPOS_ACTION_GRAD, OP_SEGMPOS_ACTION_HESS, OP_KIN, OP_POT, OP_POT_GRAD, OP_POT_HESS,
+ OP_HASH) = range(14)
 
 _p64 = C.POINTER(C.c_int64)
 _p32 = C.POINTER(C.c_int32)
@@ -69,6 +70,7 @@ SYMBOLS = {
     "chb_segmpos_to_params_T_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),
     "chb_params_to_kin_nrg_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),
     "chb_segmpos_to_pot_nrg_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),
+    "chb_segmpos_to_hash_dev": (C.c_int, _dev_op + [_vp, C.c_double, _vp, _vp, _sz, _vp]),
     "chb_segmpos_to_pot_nrg_grad_dev": (C.c_int, _dev_op + [_vp, C.c_double, _vp, _vp, _sz, _vp]),
     "chb_segmpos_to_pot_nrg_hess_dev": (C.c_int, _dev_op + [_vp, _vp, C.c_double, _vp, _vp, _sz, _vp]),
     "chb_params_to_action_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),

@@ -1473,24 +1473,31 @@ static int launch_adj(chb_plan *p, int64_t nb, const double *seg, double *out, c
                mask);
     return CHB_OK;
 }
+static int launch_pair_sys(chb_plan *p, const ChbSys &Sy, int mode, int64_t nb, const double *seg, const double *dseg,
+                           double *out, double *pot_part, double globalmul, chb_stream_t st);
 static int launch_pair(chb_plan *p, int mode, int64_t nb, const double *seg, const double *dseg, double *out,
                        double *pot_part, double globalmul, chb_stream_t st) {
+    return launch_pair_sys(p, p->sys, mode, nb, seg, dseg, out, pot_part, globalmul, st);
+}
+// Sy: the plan's system, possibly with another interaction law (the hash sums of chb_segmpos_to_hash_dev)
+static int launch_pair_sys(chb_plan *p, const ChbSys &Sy, int mode, int64_t nb, const double *seg, const double *dseg,
+                           double *out, double *pot_part, double globalmul, chb_stream_t st) {
     const long long grid = nb * p->sys.pair_ntiles;
     if (p->sys.pair_dense) {
         if (mode == 0)
-            CHB_LAUNCH(p, k_pair_dense<0>, grid, p->dense_threads, p->dense_smem[1], st, p->sys, seg, dseg, out, pot_part, globalmul);
+            CHB_LAUNCH(p, k_pair_dense<0>, grid, p->dense_threads, p->dense_smem[1], st, Sy, seg, dseg, out, pot_part, globalmul);
         else if (mode == 1)
-            CHB_LAUNCH(p, k_pair_dense<1>, grid, p->dense_threads, p->dense_smem[1], st, p->sys, seg, dseg, out, pot_part, globalmul);
+            CHB_LAUNCH(p, k_pair_dense<1>, grid, p->dense_threads, p->dense_smem[1], st, Sy, seg, dseg, out, pot_part, globalmul);
         else
-            CHB_LAUNCH(p, k_pair_dense<2>, grid, p->dense_threads, p->dense_smem[2], st, p->sys, seg, dseg, out, pot_part, globalmul);
+            CHB_LAUNCH(p, k_pair_dense<2>, grid, p->dense_threads, p->dense_smem[2], st, Sy, seg, dseg, out, pot_part, globalmul);
         return CHB_OK;
     }
     if (mode == 0)
-        CHB_LAUNCH(p, k_pair<0>, grid, p->pair_threads, p->pair_smem[0], st, p->sys, seg, dseg, out, pot_part, globalmul);
+        CHB_LAUNCH(p, k_pair<0>, grid, p->pair_threads, p->pair_smem[0], st, Sy, seg, dseg, out, pot_part, globalmul);
     else if (mode == 1)
-        CHB_LAUNCH(p, k_pair<1>, grid, p->pair_threads, p->pair_smem[1], st, p->sys, seg, dseg, out, pot_part, globalmul);
+        CHB_LAUNCH(p, k_pair<1>, grid, p->pair_threads, p->pair_smem[1], st, Sy, seg, dseg, out, pot_part, globalmul);
     else
-        CHB_LAUNCH(p, k_pair<2>, grid, p->pair_threads, p->pair_smem[2], st, p->sys, seg, dseg, out, pot_part, globalmul);
+        CHB_LAUNCH(p, k_pair<2>, grid, p->pair_threads, p->pair_smem[2], st, Sy, seg, dseg, out, pot_part, globalmul);
     return CHB_OK;
 }
 static int launch_finish(chb_plan *p, int64_t nb, double *out, const double *kin_part, int nk, const double *pot_part,
@@ -1628,6 +1635,24 @@ extern "C" int chb_segmpos_to_pot_nrg_dev(chb_plan *p, int64_t batch, const doub
         int64_t nb = std::min(chunk, batch - c0);
         CHB_TRY(launch_pair(p, 0, nb, segmpos + c0 * S.segsz, nullptr, nullptr, W.pot_part, 1.0, st));
         CHB_TRY(launch_finish(p, nb, pot + c0, nullptr, 0, W.pot_part, S.pair_ntiles, st, +1.0));
+    }
+    return CHB_OK;
+}
+
+// segmpos_to_hash, :2542-2560 / cdef segm_pos_to_hash :6271-6369, one exponent per call:
+// hash[b] = sum_bins BinProdChargeSum/segm_size * sum_i w_i |R x_src - x_tgt|^(2 exponent)  (same loop as the potential)
+extern "C" int chb_segmpos_to_hash_dev(chb_plan *p, int64_t batch, const double *segmpos, double exponent, double *hash,
+                                       void *ws, size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_segmpos_to_hash_dev");
+    CHB_REQUIRE(segmpos && hash, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_to_hash_dev: NULL array");
+    CHB_SET_DEVICE();
+    ChbSys Sh = p->sys;  // V(x^2) = -law[3] (x^2)^(law[2] + 2) in chb_inter_law: (x^2)^exponent
+    Sh.law_kind = 1;
+    Sh.law[0] = 0.0; Sh.law[1] = 0.0; Sh.law[2] = exponent - 2.0; Sh.law[3] = -1.0;
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        int64_t nb = std::min(chunk, batch - c0);
+        CHB_TRY(launch_pair_sys(p, Sh, 0, nb, segmpos + c0 * S.segsz, nullptr, nullptr, W.pot_part, 1.0, st));
+        CHB_TRY(launch_finish(p, nb, hash + c0, nullptr, 0, W.pot_part, S.pair_ntiles, st, +1.0));
     }
     return CHB_OK;
 }
@@ -1857,6 +1882,7 @@ static int host_op_shapes(const chb_plan *p, int op, bool have_out0, size_t *n_i
         case CHB_OP_SEGMPOS_ACTION_HESS: *n_in0 = ns; *n_in1 = np; *n_out0 = np; break;
         case CHB_OP_KIN: *n_in0 = np; *n_out0 = 1; break;
         case CHB_OP_POT: *n_in0 = ns; *n_out0 = 1; break;
+        case CHB_OP_HASH: *n_in0 = ns; *n_out0 = 1; break;
         case CHB_OP_POT_GRAD: *n_in0 = ns; *n_out0 = ns; break;
         case CHB_OP_POT_HESS: *n_in0 = ns; *n_in1 = ns; *n_out0 = ns; break;
         default: return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_run_host: unknown op");
@@ -1880,6 +1906,7 @@ static int host_op_dispatch(chb_plan *p, int op, int64_t nb, const double *d_in0
         case CHB_OP_SEGMPOS_ACTION_HESS: return chb_segmpos_dparams_to_action_hess_dev(p, nb, d_in0, d_in1, d_out0, d_ws, wsb, st);
         case CHB_OP_KIN: return chb_params_to_kin_nrg_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
         case CHB_OP_POT: return chb_segmpos_to_pot_nrg_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
+        case CHB_OP_HASH: return chb_segmpos_to_hash_dev(p, nb, d_in0, scalar, d_out0, d_ws, wsb, st);
         case CHB_OP_POT_GRAD: return chb_segmpos_to_pot_nrg_grad_dev(p, nb, d_in0, scalar, d_out0, d_ws, wsb, st);
         case CHB_OP_POT_HESS: return chb_segmpos_to_pot_nrg_hess_dev(p, nb, d_in0, d_in1, scalar, d_out0, d_ws, wsb, st);
     }

@@ -267,6 +267,39 @@ class NBodySystB200:
         o, _ = self._host(L.OP_POT, a, self.segmpos_shape, out0_shape=())
         return self._scalar(o, a.shape[:-3])
 
+    # default exponents of the reference (``default_Hash_exp``, _NBodySyst.pyx:135)
+    Hash_exp = np.array([-0.1, -0.2, -0.3, -0.4, -0.5, -0.6, -0.7, -0.8, -0.9])
+
+    def segmpos_to_hash(self, segmpos):
+        """_NBodySyst.pyx:2542-2560 (cdef segm_pos_to_hash :6271-6369): ``len(Hash_exp)`` weighted power sums of the pair
+        distances, the orbit fingerprint used to filter duplicates (find.py:285-308, 905-935).  Returns ``[..., nexp]``."""
+        if _is_torch(segmpos):
+            import torch
+            x, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
+            out = torch.empty((len(self.Hash_exp), b), dtype=torch.float64, device=x.device)
+            for k, e in enumerate(self.Hash_exp):
+                self._dev("chb_segmpos_to_hash_dev", b, [x, float(e), out[k]], x)
+            return out.transpose(0, 1).reshape(lead + (len(self.Hash_exp),)).contiguous()
+        a = np.asarray(segmpos)
+        cols = [np.asarray(self._host(L.OP_HASH, a, self.segmpos_shape, out0_shape=(), scalar=float(e))[0]).reshape(-1)
+                for e in self.Hash_exp]
+        return np.stack(cols, axis=-1).reshape(a.shape[:-3] + (len(self.Hash_exp),))
+
+    def TestHashSame(self, Hash_a, Hash_b, rtol: float = 1e-5, detect_multiples: bool = True) -> bool:
+        """_NBodySyst.pyx:2036-2067.  For a homogeneous law (gravity / power law: Homo_exp = n) two orbits that differ by a
+        rescaling have hashes whose ratios follow a power law; otherwise the hashes must agree entry by entry."""
+        Ha, Hb = np.asarray(Hash_a, dtype=np.float64), np.asarray(Hash_b, dtype=np.float64)
+        n = self.Hash_exp.shape[0]
+        test = np.zeros(n)
+        if detect_multiples:
+            homo = -1.0 if self.tables.inter_law == 0 else 2.0 * (float(self.tables.inter_law_params[2]) + 2.0)
+            ref = (Ha[0] / Hb[0]) ** ((homo - 1) / (2 * self.Hash_exp[0]))
+            for i in range(1, n):
+                test[i] = (Ha[i] / Hb[i]) ** ((homo - 1) / (2 * self.Hash_exp[i])) - ref
+        else:
+            test = (Hb - Ha) / (Hb + Ha)
+        return bool(np.linalg.norm(test, np.inf) < rtol)
+
     def segmpos_to_pot_nrg_grad(self, segmpos, globalmul: float = 1.0):
         """cdef segm_pos_to_pot_nrg_grad, _NBodySyst.pyx:6472-6533 (into a zeroed buffer)."""
         if _is_torch(segmpos):

@@ -156,6 +156,10 @@ int chb_params_to_kin_nrg_dev(chb_plan *plan, int64_t batch, const double *param
 /* segm_pos_to_pot_nrg, cdef :6372-6469 ; pot[batch] */
 int chb_segmpos_to_pot_nrg_dev(chb_plan *plan, int64_t batch, const double *segmpos, double *pot,
                                void *workspace, size_t workspace_bytes, void *stream);
+/* segmpos_to_hash, :2542-2560 / cdef segm_pos_to_hash :6271-6369, ONE exponent per call (the reference's Hash_exp has 9):
+ * hash[b] = sum over bins of BinProdChargeSum/segm_size * sum_i w_i |R x_src - x_tgt|^(2*exponent) ; hash[batch] */
+int chb_segmpos_to_hash_dev(chb_plan *plan, int64_t batch, const double *segmpos, double exponent, double *hash,
+                            void *workspace, size_t workspace_bytes, void *stream);
 /* segm_pos_to_pot_nrg_grad, cdef :6472-6533 ; grad_segmpos is overwritten (reference accumulates into a zeroed buffer) */
 int chb_segmpos_to_pot_nrg_grad_dev(chb_plan *plan, int64_t batch, const double *segmpos, double globalmul,
                                     double *grad_segmpos, void *workspace, size_t workspace_bytes, void *stream);
@@ -216,7 +220,8 @@ enum chb_op {
     CHB_OP_KIN = 9,
     CHB_OP_POT = 10,
     CHB_OP_POT_GRAD = 11,
-    CHB_OP_POT_HESS = 12
+    CHB_OP_POT_HESS = 12,
+    CHB_OP_HASH = 13 /* in0=segmpos out0=hash (scalar = exponent) */
 };
 int chb_run_host(chb_plan *plan, int op, int64_t batch, const double *in0, const double *in1, double scalar,
                  double *out0, double *out1);
