@@ -574,9 +574,10 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
                  FL.nco_in <= 2 && FL.tw_soff[0] >= 0 && FL.tw_soff[1] >= 0;
         }
         for (int s = 0; s < T.nsegm && ok; ++s) ok = F.segs[s].row0 == 0 && F.segs[s].loop == s;
-        if (ok && p->fused_smem + 256 * sizeof(cd) + 512 <= p->smem_limit) {  // full 16 x 16 twiddle table of pass "k1"
+        if (ok && p->fused_smem + 256 * sizeof(cd) + CHF_RED_BYTES + 512 <= p->smem_limit) {
+            // full 16 x 16 twiddle table of pass "k1", then the second buffer of partial sums
             F.tw4_off = (int)((p->fused_smem - CHF_RED_BYTES) / sizeof(cd));
-            p->fused_smem += 256 * sizeof(cd);
+            p->fused_smem += 256 * sizeof(cd) + CHF_RED_BYTES;
         } else {
             ok = false;
         }
@@ -1102,6 +1103,16 @@ struct DevGrp {
 struct DevCtx {
     unsigned tmem_thread;
     unsigned bar_base;
+    // sum of red[0 .. blockDim) by the first warp (strided partial sums, then a shuffle tree), stored by thread 0; NO barrier
+    __device__ __forceinline__ void reduce_store(const double *red, double *out) {
+        if (threadIdx.x < 32) {
+            double s = 0.0;
+            for (int j = (int)threadIdx.x; j < (int)blockDim.x; j += 32) s += red[j];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (threadIdx.x == 0) *out = s;
+        }
+    }
     template <class F>
     __device__ __forceinline__ void par(F f) {
         f((int)threadIdx.x, (int)blockDim.x);
@@ -1194,6 +1205,16 @@ struct HostGrp {
 struct HostCtx {
     int nthr;
     std::vector<double> tmem;  // emulated tensor memory, sized by k_fused
+    void reduce_store(const double *red, double *out) {  // same association as the device version
+        double part[32];
+        for (int l = 0; l < 32; ++l) {
+            part[l] = 0.0;
+            for (int j = l; j < nthr; j += 32) part[l] += red[j];
+        }
+        for (int o = 16; o > 0; o >>= 1)
+            for (int l = 0; l < o; ++l) part[l] += part[l + o];
+        *out = part[0];
+    }
     template <class F>
     void par(F f) {
         for (int t = 0; t < nthr; ++t) f(t, nthr);
@@ -1392,8 +1413,9 @@ CHB_KERNEL void CHF_BOUNDS k_fused4(ChfSys F, ChfArgs A) {
     cta_fused4_first_loads(ctx, F, A, CHB_BLOCK_ID, sm);
     cta_fused4_prologue(ctx, F, sm);
     unsigned parity = 0;
+    double *red_alt = (double *)(sm + F.tw4_off + 256);  // second buffer of partial sums, behind the twiddle tables
     for (long long b = CHB_BLOCK_ID; b < A.nstates; b += CHB_GRID_DIM, parity ^= 1u)
-        cta_fused4<NSEG, PMODE>(ctx, F, A, b, b + CHB_GRID_DIM, parity, red, sm);
+        cta_fused4<NSEG, PMODE>(ctx, F, A, b, b + CHB_GRID_DIM, parity, parity ? red_alt : red, sm);
 #ifndef CHB_HOSTSIM
     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the result rows of the last state have left shared memory
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");

@@ -260,19 +260,27 @@ CHB_D void ch4_pass_k1(Grp &grp, cd *buf, const cd *tw4) {
 template <int SIGN, class Grp>
 CHB_D void ch4_pass_k0(Grp &grp, cd *buf, const cd *tw0p) {
     grp.par([&](int tid, int T) {
-        for (int b = tid; b < 256; b += T) {
-            const int t_lo = b & 1, u = (b >> 1) & 15, t_hi = b >> 5;
-            cd *p = buf + ((t_hi << 9) | (u << 5) | t_lo);
-            const int x = u & 3;
-            cd a[16];
+        (void)T;  // T = 128: butterflies tid and tid + 128 (t_hi and t_hi + 4: 2048 slots apart, same u and t_lo)
+        const int t_lo = tid & 1, u = (tid >> 1) & 15, t_hi = tid >> 5;
+        cd *p = buf + ((t_hi << 9) | (u << 5) | t_lo);
+        const int x = u & 3;
+        // both butterflies' inputs are requested before the first one is computed: the second set of shared-memory reads
+        // overlaps the first butterfly's FP64 work (12 warps per SM run the same phase, nothing else hides that latency)
+        cd a[16], c[16];
 #pragma unroll
-            for (int q = 0; q < 16; ++q) a[q] = p[2 * (q ^ x)];
-            if (SIGN > 0) chf_twiddle<16, SIGN>(a, tw0p + b, 256);
-            ChfDft<16, SIGN>::run(a);
-            if (SIGN < 0) chf_twiddle<16, SIGN>(a, tw0p + b, 256);
+        for (int q = 0; q < 16; ++q) a[q] = p[2 * (q ^ x)];
 #pragma unroll
-            for (int t = 0; t < 16; ++t) p[2 * (t ^ x)] = a[t];
-        }
+        for (int q = 0; q < 16; ++q) c[q] = p[2048 + 2 * (q ^ x)];
+        if (SIGN > 0) chf_twiddle<16, SIGN>(a, tw0p + tid, 256);
+        ChfDft<16, SIGN>::run(a);
+        if (SIGN < 0) chf_twiddle<16, SIGN>(a, tw0p + tid, 256);
+#pragma unroll
+        for (int t = 0; t < 16; ++t) p[2 * (t ^ x)] = a[t];
+        if (SIGN > 0) chf_twiddle<16, SIGN>(c, tw0p + tid + 128, 256);
+        ChfDft<16, SIGN>::run(c);
+        if (SIGN < 0) chf_twiddle<16, SIGN>(c, tw0p + tid + 128, 256);
+#pragma unroll
+        for (int t = 0; t < 16; ++t) p[2048 + 2 * (t ^ x)] = c[t];
     });
 }
 
@@ -446,11 +454,7 @@ CHB_D void cta_fused4(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, 
                 grp.lanes([&](int warp, int lane) { ch4_issue_loads(grp, L, A.vec_in + b_next * F.nparams, buf, warp, lane, it); });
         }
     });
-    if (A.scalar_out && !(F.dbg & 32)) {
-        cta_reduce(ctx, red);
-        ctx.par([&](int tid, int nthr) {
-            (void)nthr;
-            if (tid == 0) A.scalar_out[b] = red[0];
-        });
-    }
+    // the partial sums live in one of two buffers (state parity): the first warp adds them up and stores the action while
+    // the other warps already start the next state -- no block-wide barrier behind the reduction
+    if (A.scalar_out && !(F.dbg & 32)) ctx.reduce_store(red, A.scalar_out + b);
 }
