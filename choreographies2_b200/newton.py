@@ -38,6 +38,9 @@ class _XP:
             return self.t.zeros(shape, dtype=dt, device=self.dev)
         return np.zeros(shape, dtype={"f8": np.float64, "i8": np.int64, "b": bool}[dtype])
 
+    def empty(self, shape):
+        return self.t.empty(shape, dtype=self.t.float64, device=self.dev) if self.torch else np.empty(shape)
+
     def full(self, shape, v):
         return self.zeros(shape) + v
 
@@ -97,17 +100,18 @@ class NewtonResult:
 def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20):
     """One GMRES(restart) cycle per row of ``rhs`` ([A, n]) from a zero initial guess; row b stops at the first inner
     iteration whose residual estimate is <= rtol[b] * |rhs[b]| (scipy.sparse.linalg.gmres with atol = 0, maxiter = 1).
-    ``matvec(idx, v)`` applies the operator of rows ``idx`` (None = all rows) to ``v``.  Arnoldi with classical Gram-Schmidt
-    applied twice (as stable as scipy's modified Gram-Schmidt, but two batched contractions per pass instead of j + 1
-    separate dot products) + Givens rotations.  Returns (solution [A, n], inner iterations per row, number of row-matvecs)."""
+    ``matvec(idx, v)`` applies the operator of rows ``idx`` (None = all rows) to ``v``.  Arnoldi on the shifted operator with
+    batched classical Gram-Schmidt (see the comment in the loop) + Givens rotations.  Returns (solution [A, n], inner iterations per row, number of row-matvecs)."""
     A = rhs.shape[0]
     m = int(restart)
     beta = xp.norm(rhs)
     safe_beta = xp.where(beta > 0, beta, beta + 1.0)
-    V = xp.zeros((m + 1,) + tuple(rhs.shape))
+    V = xp.zeros((m + 1,) + tuple(rhs.shape))  # rows that stop early multiply the unused vectors by 0: they must be finite
     V[0] = rhs / safe_beta[:, None]
     R = xp.zeros((A, m + 1, m))
-    cs, sn = xp.zeros((A, m)), xp.zeros((A, m))
+    Q = xp.zeros((A, m + 1, m + 1))
+    for i in range(m + 1):
+        Q[:, i, i] = 1.0
     g = xp.zeros((A, m + 1))
     g[:, 0] = beta
     target = rtol * beta
@@ -127,25 +131,35 @@ def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20):
         nmv += na
         h = xp.zeros((A, m + 1))
         Vj = V[:j + 1]
+        # Arnoldi on A - I (same Krylov space, H_A = H_(A-I) + I): the action Hessian is the identity (kinetic term) plus the
+        # potential part, so A v_j is dominated by v_j itself and orthogonalising it would cancel most of its digits; without that
+        # component one classical Gram-Schmidt pass (two batched contractions) is enough, a second one runs only if some row
+        # still lost more than a factor 10
+        w = w - V[j]
+        n0 = xp.norm(w)
         h1 = xp.einsum("jan,an->ja", Vj, w)
         w = w - xp.einsum("ja,jan->an", h1, Vj)
-        h2 = xp.einsum("jan,an->ja", Vj, w)
-        w = w - xp.einsum("ja,jan->an", h2, Vj)
+        weak = xp.norm(w) < 0.1 * n0
+        if xp.any(weak):  # second pass, applied only to the rows that need it (rows never influence each other)
+            h2 = xp.einsum("jan,an->ja", Vj, w) * weak[None, :]
+            w = w - xp.einsum("ja,jan->an", h2, Vj)
+            h1 = h1 + h2
         if xp.torch:
-            h[:, :j + 1] = (h1 + h2).transpose(0, 1)
+            h[:, :j + 1] = h1.transpose(0, 1)
         else:
-            h[:, :j + 1] = (h1 + h2).T
+            h[:, :j + 1] = h1.T
+        h[:, j] = h[:, j] + 1.0
         hn = xp.norm(w)
         h[:, j + 1] = hn
         V[j + 1] = w / xp.where(hn > 0, hn, hn + 1.0)[:, None]
-        for i in range(j):  # previous rotations on the new column
-            t = cs[:, i] * h[:, i] + sn[:, i] * h[:, i + 1]
-            h[:, i + 1] = -sn[:, i] * h[:, i] + cs[:, i] * h[:, i + 1]
-            h[:, i] = t
+        # previous rotations on the new column in one small batched product: Q accumulates them ([A, m+1, m+1])
+        h = xp.einsum("aik,ak->ai", Q, h)
         den = xp.sqrt(h[:, j] * h[:, j] + h[:, j + 1] * h[:, j + 1])
         den = xp.where(den > 0, den, den + 1.0)
         c, s = h[:, j] / den, h[:, j + 1] / den
-        cs[:, j], sn[:, j] = c, s
+        qj, qj1 = xp.copy(Q[:, j, :]), xp.copy(Q[:, j + 1, :])
+        Q[:, j, :] = c[:, None] * qj + s[:, None] * qj1
+        Q[:, j + 1, :] = -s[:, None] * qj + c[:, None] * qj1
         h[:, j] = c * h[:, j] + s * h[:, j + 1]
         h[:, j + 1] = 0.0
         gj = g[:, j]
@@ -160,9 +174,7 @@ def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20):
     y = xp.zeros((A, m))
     for j in range(m - 1, -1, -1):
         inside = kdone > j
-        acc = g[:, j]
-        for l in range(j + 1, m):
-            acc = acc - R[:, j, l] * y[:, l]
+        acc = g[:, j] - (R[:, j, j + 1:] * y[:, j + 1:]).sum(-1) if j + 1 < m else g[:, j]
         djj = xp.where(inside & (R[:, j, j] != 0), R[:, j, j], R[:, j, j] * 0 + 1.0)
         y[:, j] = xp.where(inside, acc / djj, acc * 0)
     sol = xp.einsum("aj,jan->an", y, V[:m])
