@@ -18,6 +18,8 @@
 #include <string>
 #include <vector>
 
+#include "chb_krylov.cuh"
+
 #ifndef CHB_HOSTSIM
 #include <cuda_runtime.h>
 #endif
@@ -1677,6 +1679,60 @@ extern "C" int chb_segmpos_to_hash_dev(chb_plan *p, int64_t batch, const double 
         CHB_TRY(launch_finish(p, nb, hash + c0, nullptr, 0, W.pot_part, S.pair_ntiles, st, +1.0));
     }
     return CHB_OK;
+}
+
+// One Arnoldi step of the batched GMRES for every state of the batch (chb_krylov.cuh); V is [>= j+2][batch][n], w = A v_j
+// ([batch][n]), skip (nullable, one byte per state) marks states whose GMRES has stopped, h is [batch][ldh]: entries 0..j
+// receive the Hessenberg column of A (the +1 of the shift included), entry j+1 the norm; V[j+1] receives the new basis vector.
+static int arnoldi_launch(chb_plan *p, const char *name, int64_t batch, int64_t n, int j, int ldh, double *V, const double *w,
+                          const unsigned char *skip, double *h, const ChkGivens &G, void *stream) {
+    (void)name;
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_arnoldi_step_dev / chb_gmres_step_dev: NULL plan");
+    CHB_REQUIRE(batch >= 0 && n >= 1 && j >= 0 && j < 62, CHB_ERR_INVALID_ARGUMENT,
+                "chb_arnoldi_step_dev / chb_gmres_step_dev: need batch >= 0, n >= 1, 0 <= j < 62");
+    if (batch == 0) return CHB_OK;
+    CHB_REQUIRE(V && w, CHB_ERR_INVALID_ARGUMENT, "chb_arnoldi_step_dev / chb_gmres_step_dev: NULL array");
+    CHB_SET_DEVICE();
+    chb_stream_t st = (chb_stream_t)stream;
+#ifndef CHB_HOSTSIM
+    const long long ne = (n + CHK_THREADS - 1) / CHK_THREADS;
+    if (ne <= 4)
+        CHB_LAUNCH(p, k_arnoldi_reg<4>, batch, CHK_THREADS, 0, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
+    else if (ne <= 8)
+        CHB_LAUNCH(p, k_arnoldi_reg<8>, batch, CHK_THREADS, 0, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
+    else if (ne <= 12)
+        CHB_LAUNCH(p, k_arnoldi_reg<12>, batch, CHK_THREADS, 0, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
+    else if (ne <= 16)
+        CHB_LAUNCH(p, k_arnoldi_reg<16>, batch, CHK_THREADS, 0, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
+    else {
+        const size_t smem = sizeof(double) * (size_t)n;
+        CHB_REQUIRE(smem <= 200 * 1024, CHB_ERR_UNSUPPORTED,
+                    "chb_arnoldi_step_dev / chb_gmres_step_dev: more than 25600 parameters per state");
+        CHB_LAUNCH(p, k_arnoldi_smem, batch, CHK_THREADS, smem, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
+    }
+#else
+    (void)st;
+    chk_arnoldi_host(batch, n, j, ldh, V, w, skip, h, G);
+    p->launches++;
+#endif
+    return CHB_OK;
+}
+extern "C" int chb_arnoldi_step_dev(chb_plan *p, int64_t batch, int64_t n, int j, int ldh, double *V, const double *w,
+                                    const unsigned char *skip, double *h, void *stream) {
+    CHB_REQUIRE(h && ldh >= j + 2, CHB_ERR_INVALID_ARGUMENT, "chb_arnoldi_step_dev: h missing or ldh < j + 2");
+    ChkGivens G = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0};
+    return arnoldi_launch(p, "chb_arnoldi_step_dev", batch, n, j, ldh, V, w, skip, h, G, stream);
+}
+// One whole inner iteration of the batched GMRES(m): the Arnoldi step above, then per state the Givens rotations on the new
+// Hessenberg column, the update of R and g, the iteration count and the stopping test |g[j+1]| <= target (done is both the
+// skip mask on entry and the stop flag on exit).
+extern "C" int chb_gmres_step_dev(chb_plan *p, int64_t batch, int64_t n, int j, int m, double *V, const double *w,
+                                  unsigned char *done, double *R, double *g, double *cs, const double *target,
+                                  int64_t *kdone, void *stream) {
+    CHB_REQUIRE(done && R && g && cs && target && kdone && j < m, CHB_ERR_INVALID_ARGUMENT,
+                "chb_gmres_step_dev: NULL array or j >= m");
+    ChkGivens G = {R, g, cs, target, (long long *)kdone, done, m};
+    return arnoldi_launch(p, "chb_gmres_step_dev", batch, n, j, 0, V, w, done, nullptr, G, stream);
 }
 
 extern "C" int chb_segmpos_to_pot_nrg_grad_dev(chb_plan *p, int64_t batch, const double *segmpos, double globalmul,

@@ -1,0 +1,268 @@
+// One Arnoldi step of the batched lock-step GMRES of the Newton-Krylov driver (choreographies2_b200/newton.py), for every
+// state of the batch in ONE launch: w' = w - v_j (Arnoldi on the shifted operator A - I), Gram-Schmidt against v_0..v_j,
+// re-orthogonalisation of the rows that lost more than a factor 10, norm, v_(j+1) = w''/|w''|.
+//
+// It replaces what scipy's gmres does per state inside the reference's solver (choreo/scipy_plus/nonlin.py:55-134 ->
+// scipy.optimize.nonlin.KrylovJacobian -> scipy.sparse.linalg.gmres, restart 20): there the Krylov basis of ONE state lives
+// in cache; here the bases of thousands of states are [restart+1, batch, nparams] in HBM and the step is HBM-bound, so the
+// kernel reads every basis vector exactly once per step (one CTA owns one state; the candidate vector stays in registers /
+// shared memory; modified Gram-Schmidt: the dot product with v_i uses the vector already purged of v_0..v_(i-1)).
+// Algorithmic bytes per state and step: 8 n (j + 3)  [v_0..v_j and w read, v_(j+1) written].
+#pragma once
+#include <cmath>
+#include <cstdint>
+
+#define CHK_THREADS 512
+#define CHK_MAX_NE 16
+
+#if defined(__CUDACC__) && !defined(CHB_HOSTSIM)
+#define CHK_HD __host__ __device__ __forceinline__
+#else
+#define CHK_HD inline
+#endif
+
+// Least-squares side of GMRES, kept per state (all optional: R == nullptr leaves only the Hessenberg column in h):
+//   R [batch][m+1][m] triangular factor, g [batch][m+1] rotated right-hand side, cs [batch][m][2] the Givens rotations,
+//   target [batch] stopping threshold on |g[k+1]|, kdone [batch] inner iterations done, done [batch] stop flags (also the
+//   skip mask of the step).
+struct ChkGivens {
+    double *R, *g, *cs;
+    const double *target;
+    long long *kdone;
+    unsigned char *done;
+    int m;
+};
+
+// one thread per state: previous rotations on the new column, the new rotation, R / g update, stopping test
+// (the tail of one inner iteration of scipy.sparse.linalg.gmres)
+CHK_HD void chk_givens_update(const ChkGivens &G, long long a, int j, double *hcol /* [j + 2] */) {
+    const int m = G.m;
+    const double *cs = G.cs + (size_t)a * m * 2;
+    for (int k = 0; k < j; ++k) {
+        const double c = cs[2 * k], s = cs[2 * k + 1];
+        const double t = c * hcol[k] + s * hcol[k + 1];
+        hcol[k + 1] = -s * hcol[k] + c * hcol[k + 1];
+        hcol[k] = t;
+    }
+    double den = sqrt(hcol[j] * hcol[j] + hcol[j + 1] * hcol[j + 1]);
+    if (!(den > 0.0)) den += 1.0;
+    const double c = hcol[j] / den, s = hcol[j + 1] / den;
+    hcol[j] = c * hcol[j] + s * hcol[j + 1];
+    hcol[j + 1] = 0.0;
+    G.cs[(size_t)a * m * 2 + 2 * j] = c;
+    G.cs[(size_t)a * m * 2 + 2 * j + 1] = s;
+    double *R = G.R + (size_t)a * (m + 1) * m;
+    for (int i = 0; i <= j + 1; ++i) R[(size_t)i * m + j] = hcol[i];
+    double *g = G.g + (size_t)a * (m + 1);
+    const double gj = g[j];
+    g[j + 1] = -s * gj;
+    g[j] = c * gj;
+    G.kdone[a] = j + 1;
+    if (fabs(g[j + 1]) <= G.target[a]) G.done[a] = 1;
+}
+
+#ifndef CHB_HOSTSIM
+__device__ __forceinline__ double chk_block_sum(double v, double (*sred)[CHK_THREADS / 32], int &ph) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) sred[ph][threadIdx.x >> 5] = v;
+    __syncthreads();
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < CHK_THREADS / 32; ++k) s += sred[ph][k];
+    ph ^= 1;  // the buffer used two sums ago is free again: every thread passed the barrier in between after reading it
+    return s;
+}
+
+// n <= CHK_THREADS * NE: the candidate vector and two basis rows (current + prefetched next) live in registers
+template <int NE>
+__global__ void __launch_bounds__(CHK_THREADS, 1)
+k_arnoldi_reg(long long rows, long long n, int j, int ldh, double *V, const double *w, const unsigned char *skip, double *h,
+              ChkGivens G) {
+    __shared__ double sred[2][CHK_THREADS / 32];
+    __shared__ double sh[64];
+    const long long a = blockIdx.x;
+    const int tid = threadIdx.x;
+    const size_t vs = (size_t)rows * (size_t)n;
+    double *vout = V + (size_t)(j + 1) * vs + (size_t)a * n;
+    if (skip && skip[a]) {
+        for (long long e = tid; e < n; e += CHK_THREADS) vout[e] = 0.0;
+        if (h && tid <= j + 1) h[(size_t)a * ldh + tid] = 0.0;
+        return;
+    }
+    if (tid < 64) sh[tid] = 0.0;
+    int ph = 0;
+    double acc[NE], vc[NE], vn[NE];
+    const double *vj = V + (size_t)j * vs + (size_t)a * n;
+    const double *wr = w + (size_t)a * n;
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+        const long long e = tid + (long long)CHK_THREADS * k;
+        vc[k] = e < n ? vj[e] : 0.0;
+        acc[k] = e < n ? wr[e] - vc[k] : 0.0;
+    }
+    double part = 0.0;
+#pragma unroll
+    for (int k = 0; k < NE; ++k) part = fma(acc[k], acc[k], part);
+    const double n0 = sqrt(chk_block_sum(part, sred, ph));
+    double hn = 0.0;
+    for (int pass = 0; pass < 2; ++pass) {
+        // basis order j, 0, 1, .., j-1 (v_j is in registers already)
+        for (int t = 0; t <= j; ++t) {
+            const int i = t == 0 ? j : t - 1;
+            if (t < j) {
+                const double *vr = V + (size_t)t * vs + (size_t)a * n;  // next one: index t
+#pragma unroll
+                for (int k = 0; k < NE; ++k) {
+                    const long long e = tid + (long long)CHK_THREADS * k;
+                    vn[k] = e < n ? vr[e] : 0.0;
+                }
+            }
+            part = 0.0;
+#pragma unroll
+            for (int k = 0; k < NE; ++k) part = fma(vc[k], acc[k], part);
+            const double hi = chk_block_sum(part, sred, ph);
+#pragma unroll
+            for (int k = 0; k < NE; ++k) acc[k] = fma(-hi, vc[k], acc[k]);
+            if (tid == 0) sh[i] += hi;
+#pragma unroll
+            for (int k = 0; k < NE; ++k) vc[k] = vn[k];
+        }
+        part = 0.0;
+#pragma unroll
+        for (int k = 0; k < NE; ++k) part = fma(acc[k], acc[k], part);
+        hn = sqrt(chk_block_sum(part, sred, ph));
+        if (pass == 0 && hn < 0.1 * n0) {
+#pragma unroll
+            for (int k = 0; k < NE; ++k) {
+                const long long e = tid + (long long)CHK_THREADS * k;
+                vc[k] = e < n ? vj[e] : 0.0;
+            }
+            continue;
+        }
+        break;
+    }
+    const double inv = hn > 0.0 ? 1.0 / hn : 1.0;
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+        const long long e = tid + (long long)CHK_THREADS * k;
+        if (e < n) vout[e] = acc[k] * inv;
+    }
+    if (tid == 0) {
+        sh[j] += 1.0;
+        sh[j + 1] = hn;
+        if (h)
+            for (int i = 0; i <= j + 1; ++i) h[(size_t)a * ldh + i] = sh[i];
+        if (G.R) chk_givens_update(G, a, j, sh);
+    }
+}
+
+// larger rows: the candidate vector lives in shared memory (8 n bytes), every basis row is streamed once from HBM for the dot
+// product and once more for the update (an L2 hit: the same CTA just read it)
+__global__ void __launch_bounds__(CHK_THREADS, 1)
+k_arnoldi_smem(long long rows, long long n, int j, int ldh, double *V, const double *w, const unsigned char *skip, double *h,
+               ChkGivens G) {
+    extern __shared__ double chk_acc[];
+    __shared__ double sred[2][CHK_THREADS / 32];
+    __shared__ double sh[64];
+    const long long a = blockIdx.x;
+    const int tid = threadIdx.x;
+    const size_t vs = (size_t)rows * (size_t)n;
+    double *vout = V + (size_t)(j + 1) * vs + (size_t)a * n;
+    if (skip && skip[a]) {
+        for (long long e = tid; e < n; e += CHK_THREADS) vout[e] = 0.0;
+        if (h && tid <= j + 1) h[(size_t)a * ldh + tid] = 0.0;
+        return;
+    }
+    if (tid < 64) sh[tid] = 0.0;
+    int ph = 0;
+    const double *vj = V + (size_t)j * vs + (size_t)a * n;
+    const double *wr = w + (size_t)a * n;
+    double part = 0.0;
+#pragma unroll 4
+    for (long long e = tid; e < n; e += CHK_THREADS) {
+        const double d = wr[e] - vj[e];
+        chk_acc[e] = d;
+        part = fma(d, d, part);
+    }
+    const double n0 = sqrt(chk_block_sum(part, sred, ph));
+    double hn = 0.0;
+    for (int pass = 0; pass < 2; ++pass) {
+        for (int t = 0; t <= j; ++t) {
+            const int i = t == 0 ? j : t - 1;
+            const double *vr = V + (size_t)i * vs + (size_t)a * n;
+            part = 0.0;
+#pragma unroll 8
+            for (long long e = tid; e < n; e += CHK_THREADS) part = fma(vr[e], chk_acc[e], part);
+            const double hi = chk_block_sum(part, sred, ph);
+#pragma unroll 8
+            for (long long e = tid; e < n; e += CHK_THREADS) chk_acc[e] = fma(-hi, vr[e], chk_acc[e]);
+            if (tid == 0) sh[i] += hi;
+        }
+        part = 0.0;
+#pragma unroll 4
+        for (long long e = tid; e < n; e += CHK_THREADS) part = fma(chk_acc[e], chk_acc[e], part);
+        hn = sqrt(chk_block_sum(part, sred, ph));
+        if (pass == 0 && hn < 0.1 * n0) continue;
+        break;
+    }
+    const double inv = hn > 0.0 ? 1.0 / hn : 1.0;
+    for (long long e = tid; e < n; e += CHK_THREADS) vout[e] = chk_acc[e] * inv;
+    if (tid == 0) {
+        sh[j] += 1.0;
+        sh[j + 1] = hn;
+        if (h)
+            for (int i = 0; i <= j + 1; ++i) h[(size_t)a * ldh + i] = sh[i];
+        if (G.R) chk_givens_update(G, a, j, sh);
+    }
+}
+#else
+// host emulation (tests/hostsim): the same arithmetic, one state after the other
+static void chk_arnoldi_host(long long rows, long long n, int j, int ldh, double *V, const double *w,
+                             const unsigned char *skip, double *h, ChkGivens G) {
+    const size_t vs = (size_t)rows * (size_t)n;
+    std::vector<double> acc((size_t)n);
+    for (long long a = 0; a < rows; ++a) {
+        double *vout = V + (size_t)(j + 1) * vs + (size_t)a * n;
+        double hloc[64];
+        double *hr = hloc;
+        if (skip && skip[a]) {
+            for (long long e = 0; e < n; ++e) vout[e] = 0.0;
+            if (h)
+                for (int i = 0; i <= j + 1; ++i) h[(size_t)a * ldh + i] = 0.0;
+            continue;
+        }
+        const double *vj = V + (size_t)j * vs + (size_t)a * n;
+        double s = 0.0;
+        for (long long e = 0; e < n; ++e) {
+            acc[e] = w[(size_t)a * n + e] - vj[e];
+            s += acc[e] * acc[e];
+        }
+        const double n0 = std::sqrt(s);
+        for (int i = 0; i <= j; ++i) hr[i] = 0.0;
+        double hn = 0.0;
+        for (int pass = 0; pass < 2; ++pass) {
+            for (int t = 0; t <= j; ++t) {
+                const int i = t == 0 ? j : t - 1;
+                const double *vr = V + (size_t)i * vs + (size_t)a * n;
+                double hi = 0.0;
+                for (long long e = 0; e < n; ++e) hi += vr[e] * acc[e];
+                for (long long e = 0; e < n; ++e) acc[e] -= hi * vr[e];
+                hr[i] += hi;
+            }
+            s = 0.0;
+            for (long long e = 0; e < n; ++e) s += acc[e] * acc[e];
+            hn = std::sqrt(s);
+            if (pass == 0 && hn < 0.1 * n0) continue;
+            break;
+        }
+        const double inv = hn > 0.0 ? 1.0 / hn : 1.0;
+        for (long long e = 0; e < n; ++e) vout[e] = acc[e] * inv;
+        hr[j] += 1.0;
+        hr[j + 1] = hn;
+        if (h)
+            for (int i = 0; i <= j + 1; ++i) h[(size_t)a * ldh + i] = hr[i];
+        if (G.R) chk_givens_update(G, a, j, hr);
+    }
+}
+#endif

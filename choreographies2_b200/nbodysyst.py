@@ -285,6 +285,85 @@ class NBodySystB200:
                 for e in self.Hash_exp]
         return np.stack(cols, axis=-1).reshape(a.shape[:-3] + (len(self.Hash_exp),))
 
+    # ------------------------------------------------------------------ Krylov helper of the batched Newton driver
+    def arnoldi_step(self, V, j: int, w, skip, h) -> bool:
+        """One Arnoldi step of the batched GMRES for all states in one launch (``chb_arnoldi_step_dev``): orthogonalises
+        ``w - V[j]`` against ``V[0..j]``, writes ``V[j+1]`` and ``h[:, :j+2]`` (see include/choreo_b200.h).  ``V`` is
+        ``[>= j+2, batch, n]``, ``w`` ``[batch, n]``, ``skip`` ``[batch]`` bool or None, ``h`` ``[batch, ldh]``.  Returns False
+        when the arrays are not ones the library can address (NumPy arrays with the CUDA library): the caller then runs its
+        own array-level Gram-Schmidt."""
+        torch_in = _is_torch(V)
+        if not torch_in and not str(getattr(self._lib, "_name", "")).endswith("libchb_hostsim.so"):
+            return False
+        batch, n = int(w.shape[0]), int(w.shape[1])
+        if n * 8 > 200 * 1024 or j >= 62:
+            return False
+        if tuple(V.shape[1:]) != (batch, n) or V.shape[0] < j + 2 or tuple(h.shape[:1]) != (batch,) or h.shape[1] < j + 2:
+            raise ValueError("arnoldi_step: inconsistent shapes")
+        if torch_in:
+            import torch
+            for t in (V, w, h):
+                if t.dtype != torch.float64 or not t.is_cuda or not t.is_contiguous():
+                    raise ValueError("arnoldi_step: contiguous float64 CUDA tensors expected")
+            sk = None
+            if skip is not None:
+                sk = skip.to(torch.uint8) if skip.dtype != torch.uint8 else skip
+                sk = sk.contiguous()
+            stream = torch.cuda.current_stream(V.device).cuda_stream
+            L.check(self._lib, self._lib.chb_arnoldi_step_dev(
+                self._plan, batch, n, int(j), int(h.shape[1]), C.c_void_p(V.data_ptr()), C.c_void_p(w.data_ptr()),
+                C.c_void_p(sk.data_ptr()) if sk is not None else None, C.c_void_p(h.data_ptr()), C.c_void_p(stream)))
+            return True
+        for t in (V, w, h):
+            if t.dtype != np.float64 or not t.flags.c_contiguous:
+                raise ValueError("arnoldi_step: C-contiguous float64 arrays expected")
+        sk = np.ascontiguousarray(skip, dtype=np.uint8) if skip is not None else None
+        L.check(self._lib, self._lib.chb_arnoldi_step_dev(
+            self._plan, batch, n, int(j), int(h.shape[1]), C.c_void_p(V.ctypes.data), C.c_void_p(w.ctypes.data),
+            C.c_void_p(sk.ctypes.data) if sk is not None else None, C.c_void_p(h.ctypes.data), None))
+        return True
+
+    def gmres_step(self, V, j: int, w, done, R, g, cs, target, kdone) -> bool:
+        """One whole inner iteration of the batched GMRES (``chb_gmres_step_dev``): Arnoldi step + Givens rotations + R / g /
+        kdone / done updates, all in place, one launch.  Shapes: ``V [m+1, batch, n]``, ``w [batch, n]``, ``done [batch]``
+        bool, ``R [batch, m+1, m]``, ``g [batch, m+1]``, ``cs [batch, m, 2]``, ``target [batch]``, ``kdone [batch]`` int64.
+        Returns False when the library cannot address the arrays (see ``arnoldi_step``)."""
+        torch_in = _is_torch(V)
+        if not torch_in and not str(getattr(self._lib, "_name", "")).endswith("libchb_hostsim.so"):
+            return False
+        batch, n = int(w.shape[0]), int(w.shape[1])
+        m = int(R.shape[2])
+        if n * 8 > 200 * 1024 or m > 62:
+            return False
+        want = {"V": (m + 1, batch, n), "R": (batch, m + 1, m), "g": (batch, m + 1), "cs": (batch, m, 2), "target": (batch,),
+                "kdone": (batch,), "done": (batch,)}
+        got = {"V": V, "R": R, "g": g, "cs": cs, "target": target, "kdone": kdone, "done": done}
+        for k, shp in want.items():
+            if tuple(got[k].shape) != shp:
+                raise ValueError(f"gmres_step: {k} has shape {tuple(got[k].shape)}, expected {shp}")
+        if torch_in:
+            import torch
+            for k, t in got.items():
+                dt = torch.bool if k == "done" else torch.int64 if k == "kdone" else torch.float64
+                if t.dtype != dt or not t.is_cuda or not t.is_contiguous():
+                    raise ValueError(f"gmres_step: {k} must be a contiguous {dt} CUDA tensor")
+            if w.dtype != torch.float64 or not w.is_contiguous():
+                raise ValueError("gmres_step: w must be a contiguous float64 CUDA tensor")
+            ptr = lambda t: C.c_void_p(t.data_ptr())
+            stream = C.c_void_p(torch.cuda.current_stream(V.device).cuda_stream)
+        else:
+            for k, t in got.items():
+                dt = np.bool_ if k == "done" else np.int64 if k == "kdone" else np.float64
+                if t.dtype != dt or not t.flags.c_contiguous:
+                    raise ValueError(f"gmres_step: {k} must be a C-contiguous {dt} array")
+            if w.dtype != np.float64 or not w.flags.c_contiguous:
+                raise ValueError("gmres_step: w must be a C-contiguous float64 array")
+            ptr = lambda t: C.c_void_p(t.ctypes.data)
+            stream = None
+        L.check(self._lib, self._lib.chb_gmres_step_dev(self._plan, batch, n, int(j), m, ptr(V), ptr(w), ptr(done), ptr(R),
+                                                        ptr(g), ptr(cs), ptr(target), ptr(kdone), stream))
+        return True
+
     def TestHashSame(self, Hash_a, Hash_b, rtol: float = 1e-5, detect_multiples: bool = True) -> bool:
         """_NBodySyst.pyx:2036-2067.  For a homogeneous law (gravity / power law: Homo_exp = n) two orbits that differ by a
         rescaling have hashes whose ratios follow a power law; otherwise the hashes must agree entry by entry."""

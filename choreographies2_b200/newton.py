@@ -17,6 +17,7 @@ rounding and converged orbits to the solver tolerance, not bit for bit.
 from __future__ import annotations
 
 from dataclasses import dataclass
+import os
 from typing import Any, Optional
 
 import numpy as np
@@ -97,11 +98,14 @@ class NewtonResult:
     n_hess_evals: int      # U2 evaluations
 
 
-def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20):
+def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20, arnoldi=None, step=None):
     """One GMRES(restart) cycle per row of ``rhs`` ([A, n]) from a zero initial guess; row b stops at the first inner
     iteration whose residual estimate is <= rtol[b] * |rhs[b]| (scipy.sparse.linalg.gmres with atol = 0, maxiter = 1).
     ``matvec(idx, v)`` applies the operator of rows ``idx`` (None = all rows) to ``v``.  Arnoldi on the shifted operator with
-    batched classical Gram-Schmidt (see the comment in the loop) + Givens rotations.  Returns (solution [A, n], inner iterations per row, number of row-matvecs)."""
+    batched classical Gram-Schmidt (see the comment in the loop) + Givens rotations.  ``arnoldi(V, j, w, skip, h) -> bool``, when
+    given, is the library's one-launch Arnoldi step (``NBodySystB200.arnoldi_step``); it returning False selects the array-level
+    Gram-Schmidt below; ``step(V, j, w, done, R, g, cs, target, kdone) -> bool`` is the library's whole inner iteration
+    (``NBodySystB200.gmres_step``: Arnoldi step + Givens rotations + stopping test in one launch, everything in place).  Returns (solution [A, n], inner iterations per row, number of row-matvecs)."""
     A = rhs.shape[0]
     m = int(restart)
     beta = xp.norm(rhs)
@@ -118,6 +122,7 @@ def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20):
     done = ~(beta > 0)
     kdone = xp.zeros((A,), "i8")
     nmv = 0
+    cs = xp.zeros((A, m, 2)) if step is not None else None
     for j in range(m):
         idx = xp.nonzero(~done)
         na = int(idx.shape[0])
@@ -129,29 +134,37 @@ def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20):
             w = xp.zeros(rhs.shape)
             w[idx] = matvec(idx, V[j][idx])
         nmv += na
+        if step is not None:
+            if step(V, j, w, done, R, g, cs, target, kdone):
+                continue
+            step = None  # not addressable by the library (decided at j = 0): array-level path from here on
         h = xp.zeros((A, m + 1))
-        Vj = V[:j + 1]
+        if arnoldi is not None and arnoldi(V, j, w, done if na < A else None, h):
+            Vj = None
+        else:
+            Vj = V[:j + 1]
         # Arnoldi on A - I (same Krylov space, H_A = H_(A-I) + I): the action Hessian is the identity (kinetic term) plus the
         # potential part, so A v_j is dominated by v_j itself and orthogonalising it would cancel most of its digits; without that
         # component one classical Gram-Schmidt pass (two batched contractions) is enough, a second one runs only if some row
         # still lost more than a factor 10
-        w = w - V[j]
-        n0 = xp.norm(w)
-        h1 = xp.einsum("jan,an->ja", Vj, w)
-        w = w - xp.einsum("ja,jan->an", h1, Vj)
-        weak = xp.norm(w) < 0.1 * n0
-        if xp.any(weak):  # second pass, applied only to the rows that need it (rows never influence each other)
-            h2 = xp.einsum("jan,an->ja", Vj, w) * weak[None, :]
-            w = w - xp.einsum("ja,jan->an", h2, Vj)
-            h1 = h1 + h2
-        if xp.torch:
-            h[:, :j + 1] = h1.transpose(0, 1)
-        else:
-            h[:, :j + 1] = h1.T
-        h[:, j] = h[:, j] + 1.0
-        hn = xp.norm(w)
-        h[:, j + 1] = hn
-        V[j + 1] = w / xp.where(hn > 0, hn, hn + 1.0)[:, None]
+        if Vj is not None:
+            w = w - V[j]
+            n0 = xp.norm(w)
+            h1 = xp.einsum("jan,an->ja", Vj, w)
+            w = w - xp.einsum("ja,jan->an", h1, Vj)
+            weak = xp.norm(w) < 0.1 * n0
+            if xp.any(weak):  # second pass, applied only to the rows that need it (rows never influence each other)
+                h2 = xp.einsum("jan,an->ja", Vj, w) * weak[None, :]
+                w = w - xp.einsum("ja,jan->an", h2, Vj)
+                h1 = h1 + h2
+            if xp.torch:
+                h[:, :j + 1] = h1.transpose(0, 1)
+            else:
+                h[:, :j + 1] = h1.T
+            h[:, j] = h[:, j] + 1.0
+            hn = xp.norm(w)
+            h[:, j + 1] = hn
+            V[j + 1] = w / xp.where(hn > 0, hn, hn + 1.0)[:, None]
         # previous rotations on the new column in one small batched product: Q accumulates them ([A, m+1, m+1])
         h = xp.einsum("aik,ak->ai", Q, h)
         den = xp.sqrt(h[:, j] * h[:, j] + h[:, j + 1] * h[:, j + 1])
@@ -200,6 +213,10 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search) 
     xp = _XP(x0)
     x = xp.copy(x0)
     B = x.shape[0]
+    # CHB_NO_ARNOLDI=1: array-level Gram-Schmidt instead of the library's Arnoldi kernel (A/B measurements)
+    # CHB_NO_GMRES_STEP=1: the library's Arnoldi step but the Givens / stopping logic at array level
+    arnoldi = None if os.environ.get("CHB_NO_ARNOLDI", "0") not in ("", "0") else getattr(nbs, "arnoldi_step", None)
+    step = None if arnoldi is None or os.environ.get("CHB_NO_GMRES_STEP", "0") not in ("", "0") else getattr(nbs, "gmres_step", None)
     n_grad = n_hess = 0
 
     def func(idx, xs):
@@ -233,7 +250,7 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search) 
             return nbs.segmpos_dparams_to_action_hess(seg if idx is None else seg[idx], v)
 
         tol = xp.minimum(etaa, etaa * Fna)  # nonlin.py:113
-        sol, _, _ = gmres_batched(xp, matvec, Fa, tol, restart)
+        sol, _, _ = gmres_batched(xp, matvec, Fa, tol, restart, arnoldi, step)
         dx = -sol
         # ---- line search on phi(s) = |F(x + s dx)|^2, scalar_search_armijo(phi, phi0, -phi0, amin=smin) per state ----
         phi0 = Fna * Fna

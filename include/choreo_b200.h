@@ -160,6 +160,25 @@ int chb_segmpos_to_pot_nrg_dev(chb_plan *plan, int64_t batch, const double *segm
  * hash[b] = sum over bins of BinProdChargeSum/segm_size * sum_i w_i |R x_src - x_tgt|^(2*exponent) ; hash[batch] */
 int chb_segmpos_to_hash_dev(chb_plan *plan, int64_t batch, const double *segmpos, double exponent, double *hash,
                             void *workspace, size_t workspace_bytes, void *stream);
+/* One Arnoldi step of the batched GMRES(restart) inside the Newton-Krylov driver, all states in one launch.  Replaces the
+ * per-state inner loop of scipy.sparse.linalg.gmres that the reference reaches through choreo/scipy_plus/nonlin.py:55-134
+ * (nonlin_solve_pp -> KrylovJacobian(method gmres, inner_maxiter restart 20)).  No plan state is used beyond the device.
+ *   V    [>= j+2][batch][n]  Krylov bases (V[0..j] read, V[j+1] written: the new unit vector, 0 for skipped states)
+ *   w    [batch][n]          Hessian-vector products A v_j of this step
+ *   skip [batch] or NULL     one byte per state, non-zero = this state's GMRES has stopped
+ *   h    [batch][ldh]        h[b][0..j] = column j of the Hessenberg matrix of A, h[b][j+1] = |w''|   (ldh >= j + 2)
+ * The step orthogonalises w - v_j (Arnoldi on A - I; +1 is added back to h[b][j]) with modified Gram-Schmidt and a
+ * second pass for the states whose vector lost more than a factor 10. */
+int chb_arnoldi_step_dev(chb_plan *plan, int64_t batch, int64_t n, int j, int ldh, double *V, const double *w,
+                         const unsigned char *skip, double *h, void *stream);
+/* One whole inner iteration of the batched GMRES(m): chb_arnoldi_step_dev, then, per state, what the tail of an inner
+ * iteration of scipy.sparse.linalg.gmres does: previous Givens rotations on the new Hessenberg column, the new rotation,
+ * column j of R, the rotated right-hand side g, the iteration count and the stopping test.
+ *   done   [batch] bytes     in: states to skip; out: additionally set where |g[j+1]| <= target
+ *   R      [batch][m+1][m]   g [batch][m+1]   cs [batch][m][2] (c, s of rotation k)   target [batch]   kdone [batch] int64 */
+int chb_gmres_step_dev(chb_plan *plan, int64_t batch, int64_t n, int j, int m, double *V, const double *w,
+                       unsigned char *done, double *R, double *g, double *cs, const double *target, int64_t *kdone,
+                       void *stream);
 /* segm_pos_to_pot_nrg_grad, cdef :6472-6533 ; grad_segmpos is overwritten (reference accumulates into a zeroed buffer) */
 int chb_segmpos_to_pot_nrg_grad_dev(chb_plan *plan, int64_t batch, const double *segmpos, double globalmul,
                                     double *grad_segmpos, void *workspace, size_t workspace_bytes, void *stream);

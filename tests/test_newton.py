@@ -35,6 +35,37 @@ def test_gmres_batched_matches_scipy():
     assert k[3] == 0 and k[5] < k[0] <= 20
 
 
+@pytest.mark.parametrize("mode", ["arnoldi", "step"])
+def test_gmres_batched_library_steps_match_scipy(mode):
+    """The same check with the library's Arnoldi step (chb_arnoldi_step_dev) and whole inner iteration
+    (chb_gmres_step_dev) in place of the array-level Gram-Schmidt / Givens code; host emulation build."""
+    import scipy.sparse.linalg as sla
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from hostsim import build_hostsim
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nbs = NBodySystB200(T, 96, _lib_handle=build_hostsim.load())
+    rng = np.random.default_rng(1)
+    A, n = 7, 61
+    Ms = [np.eye(n) + 0.2 * rng.standard_normal((n, n)) for _ in range(A)]
+    rhs = rng.standard_normal((A, n))
+    rhs[2] = 0.0
+    rtol = np.array([1e-3, 1e-8, 1e-1, 1e-3, 1e-12, 0.5, 1e-6])
+
+    def mv(idx, v):
+        ids = range(A) if idx is None else idx
+        return np.stack([Ms[i] @ v[k] for k, i in enumerate(ids)])
+
+    l0 = nbs.kernel_launches
+    sol, k, nmv = gmres_batched(_XP(rhs), mv, rhs, rtol, 20, nbs.arnoldi_step, nbs.gmres_step if mode == "step" else None)
+    assert nbs.kernel_launches - l0 == int(k.max())  # one launch per inner iteration
+    sol0, k0, _ = gmres_batched(_XP(rhs), mv, rhs, rtol, 20)
+    assert np.array_equal(k, k0) and nmv == int(k.sum())
+    for b in range(A):
+        ref, _ = sla.gmres(Ms[b], rhs[b], rtol=rtol[b], atol=0, restart=20, maxiter=1)
+        assert np.abs(sol[b] - ref).max() < 1e-11
+    assert k[2] == 0
+
+
 def _figure_eight(lib):
     z = np.load(os.path.join(ROOT, "tests", "golden", "sols.npz"))
     name = "3C-Figure_eight"

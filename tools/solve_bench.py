@@ -66,7 +66,7 @@ def main():
         "b200": {"solves_per_hour": a.batch / dt * 3600, "seconds": dt, "converged": int((res.status == 1).sum()),
                  "iteration_limit": int((res.status == 2).sum()), "non_finite": int((res.status == 3).sum()),
                  "U1_evals": res.n_grad_evals, "U2_evals": res.n_hess_evals, "newton_iterations_mean": float(res.nit.mean())},
-        "reference_1_process": {"solves_per_hour": a.ref_seeds / tr * 3600, "seconds": tr, "seeds": a.ref_seeds,
+        "reference_1_process": {"solves_per_hour": (a.ref_seeds / tr * 3600) if tr > 0 else None, "seconds": tr, "seeds": a.ref_seeds,
                                 "converged": nconv_ref, "same_orbit_as_b200": agree},
     }))
 
