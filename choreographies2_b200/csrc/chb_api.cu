@@ -1354,8 +1354,16 @@ CHB_KERNEL void CHF_BOUNDS k_fused(ChfSys F, ChfArgs A) {
 #endif
     cta_fused_prologue(ctx, F, (cd *)(CHB_SMEM + CHF_RED_BYTES));
     // persistent CTAs: the grid is one resident wave, every CTA walks the batch with the grid stride
-    for (long long b = CHB_BLOCK_ID; b < A.nstates; b += CHB_GRID_DIM)
-        cta_fused<NSEG, PMODE>(ctx, F, A, b, (double *)CHB_SMEM, (cd *)(CHB_SMEM + CHF_RED_BYTES));
+    // or, with A.live_list, over the states it names (written by the previous GMRES step); b_pf: the state whose rows are
+    // prefetched into L2 (the one this CTA or a neighbour processes one wave later)
+    const long long nwork = A.live_list ? (long long)*A.live_count : A.nstates;
+    for (long long k = CHB_BLOCK_ID; k < nwork; k += CHB_GRID_DIM) {
+        const long long b = A.live_list ? (long long)A.live_list[k] : k;
+        if (A.skip && A.skip[b]) continue;  // CTA-uniform
+        const long long kp = k + F.pf_stride;
+        const long long b_pf = kp < nwork ? (A.live_list ? (long long)A.live_list[kp] : kp) : A.nstates;
+        cta_fused<NSEG, PMODE>(ctx, F, A, b, b_pf, (double *)CHB_SMEM, (cd *)(CHB_SMEM + CHF_RED_BYTES));
+    }
 #ifndef CHB_HOSTSIM
     if (use_tmem) {
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -1412,12 +1420,30 @@ CHB_KERNEL void CHF_BOUNDS k_fused4(ChfSys F, ChfArgs A) {
 #endif
     double *red = (double *)CHB_SMEM;
     cd *sm = (cd *)(CHB_SMEM + CHF_RED_BYTES);
-    cta_fused4_first_loads(ctx, F, A, CHB_BLOCK_ID, sm);
+    // the states of this CTA: grid stride over the batch (the ones flagged in A.skip left out) or over A.live_list; the next
+    // state is known one state ahead: its rows are requested while the current one drains
+    const long long nlive = A.live_list ? (long long)*A.live_count : 0;
+    auto settle = [&](long long k) {  // first position >= k (same CTA) that is not flagged
+        if (!A.live_list)
+            while (A.skip && k < A.nstates && A.skip[k]) k += CHB_GRID_DIM;
+        return k;
+    };
+    auto state_at = [&](long long k) {  // position -> state (nstates: none left)
+        if (A.live_list) return k < nlive ? (long long)A.live_list[k] : A.nstates;
+        return k < A.nstates ? k : A.nstates;
+    };
+    long long k = settle(CHB_BLOCK_ID);
+    const long long b_first = state_at(k);
+    cta_fused4_first_loads(ctx, F, A, b_first, sm);
     cta_fused4_prologue(ctx, F, sm);
     unsigned parity = 0;
     double *red_alt = (double *)(sm + F.tw4_off + 256);  // second buffer of partial sums, behind the twiddle tables
-    for (long long b = CHB_BLOCK_ID; b < A.nstates; b += CHB_GRID_DIM, parity ^= 1u)
-        cta_fused4<NSEG, PMODE>(ctx, F, A, b, b + CHB_GRID_DIM, parity, parity ? red_alt : red, sm);
+    for (long long b = b_first; b < A.nstates; parity ^= 1u) {
+        k = settle(k + CHB_GRID_DIM);
+        const long long bn = state_at(k);
+        cta_fused4<NSEG, PMODE>(ctx, F, A, b, bn, parity, parity ? red_alt : red, sm);
+        b = bn;
+    }
 #ifndef CHB_HOSTSIM
     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the result rows of the last state have left shared memory
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -1599,6 +1625,8 @@ static ChfArgs chf_args(const double *vec_in, const double *kin_src, const doubl
     A.nstates = 0;  // set by launch_fused
     A.vec_in = vec_in; A.kin_src = kin_src; A.seg_in = seg_in; A.seg_out = seg_out; A.vec_out = vec_out;
     A.scalar_out = scalar_out; A.kin_from = kin_from;
+    A.skip = nullptr;
+    A.live_list = nullptr; A.live_count = nullptr;
     return A;
 }
 #define CHB_TRY(x)          \
@@ -1720,7 +1748,7 @@ static int arnoldi_launch(chb_plan *p, const char *name, int64_t batch, int64_t 
 extern "C" int chb_arnoldi_step_dev(chb_plan *p, int64_t batch, int64_t n, int j, int ldh, double *V, const double *w,
                                     const unsigned char *skip, double *h, void *stream) {
     CHB_REQUIRE(h && ldh >= j + 2, CHB_ERR_INVALID_ARGUMENT, "chb_arnoldi_step_dev: h missing or ldh < j + 2");
-    ChkGivens G = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0};
+    ChkGivens G = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, nullptr};
     return arnoldi_launch(p, "chb_arnoldi_step_dev", batch, n, j, ldh, V, w, skip, h, G, stream);
 }
 // One whole inner iteration of the batched GMRES(m): the Arnoldi step above, then per state the Givens rotations on the new
@@ -1728,10 +1756,10 @@ extern "C" int chb_arnoldi_step_dev(chb_plan *p, int64_t batch, int64_t n, int j
 // skip mask on entry and the stop flag on exit).
 extern "C" int chb_gmres_step_dev(chb_plan *p, int64_t batch, int64_t n, int j, int m, double *V, const double *w,
                                   unsigned char *done, double *R, double *g, double *cs, const double *target,
-                                  int64_t *kdone, void *stream) {
+                                  int64_t *kdone, int *live_list_next, int *live_count_next, void *stream) {
     CHB_REQUIRE(done && R && g && cs && target && kdone && j < m, CHB_ERR_INVALID_ARGUMENT,
                 "chb_gmres_step_dev: NULL array or j >= m");
-    ChkGivens G = {R, g, cs, target, (long long *)kdone, done, m};
+    ChkGivens G = {R, g, cs, target, (long long *)kdone, done, m, live_list_next, live_count_next};
     return arnoldi_launch(p, "chb_gmres_step_dev", batch, n, j, 0, V, w, done, nullptr, G, stream);
 }
 
@@ -1850,21 +1878,65 @@ extern "C" int chb_segmpos_params_to_action_grad_dev(chb_plan *p, int64_t batch,
     return CHB_OK;
 }
 
-extern "C" int chb_segmpos_dparams_to_action_hess_dev(chb_plan *p, int64_t batch, const double *segmpos,
-                                                      const double *dparams, double *hess, void *ws, size_t ws_bytes,
-                                                      void *stream) {
-    CHB_OP_PROLOGUE("chb_segmpos_dparams_to_action_hess_dev");
+static int hess_common(chb_plan *p, int64_t batch, const double *segmpos, const double *dparams, const unsigned char *skip,
+                       const int *live_list, const int *live_count, double *hess, void *ws, size_t ws_bytes, void *stream) {
+    CHB_OP_PROLOGUE("chb_segmpos_dparams_to_action_hess(_masked)_dev");
     CHB_REQUIRE(segmpos && dparams && hess, CHB_ERR_INVALID_ARGUMENT,
-                "chb_segmpos_dparams_to_action_hess_dev: NULL array");
+                "chb_segmpos_dparams_to_action_hess(_masked)_dev: NULL array");
     CHB_SET_DEVICE();
-    if (use_fused(p))
-        return launch_fused(p, 2, batch, chf_args(dparams, dparams, segmpos, nullptr, hess, nullptr, 0), st);
-    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+    if (use_fused(p)) {
+        ChfArgs A = chf_args(dparams, dparams, segmpos, nullptr, hess, nullptr, 0);
+        A.skip = skip;
+        A.live_list = live_list; A.live_count = live_count;
+        return launch_fused(p, 2, batch, A, st);
+    }
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {  // staged kernels: the mask is not used, every state is computed
         int64_t nb = std::min(chunk, batch - c0);
         CHB_TRY(launch_fwd(p, nb, dparams + c0 * S.nparams, W.segB, W, false, mask, st));
         CHB_TRY(launch_pair(p, 2, nb, segmpos + c0 * S.segsz, W.segB, W.segC, nullptr, -1.0, st));
         CHB_TRY(launch_adj(p, nb, W.segC, hess + c0 * S.nparams, dparams + c0 * S.nparams, W, 0, mask, st));
     }
+    return CHB_OK;
+}
+extern "C" int chb_segmpos_dparams_to_action_hess_dev(chb_plan *p, int64_t batch, const double *segmpos,
+                                                      const double *dparams, double *hess, void *ws, size_t ws_bytes,
+                                                      void *stream) {
+    return hess_common(p, batch, segmpos, dparams, nullptr, nullptr, nullptr, hess, ws, ws_bytes, stream);
+}
+// the same operator inside the batched GMRES: states whose skip byte is non-zero (their GMRES has stopped) MAY be left out,
+// their rows of hess are then not written
+extern "C" int chb_segmpos_dparams_to_action_hess_masked_dev(chb_plan *p, int64_t batch, const double *segmpos,
+                                                             const double *dparams, const unsigned char *skip, double *hess,
+                                                             void *ws, size_t ws_bytes, void *stream) {
+    return hess_common(p, batch, segmpos, dparams, skip, nullptr, nullptr, hess, ws, ws_bytes, stream);
+}
+// ... and with the states to process given as a list in device memory (live_list[0 .. *live_count), written by
+// chb_gmres_step_dev): the persistent CTAs share the listed states evenly whatever their positions in the batch
+extern "C" int chb_segmpos_dparams_to_action_hess_listed_dev(chb_plan *p, int64_t batch, const double *segmpos,
+                                                             const double *dparams, const int *live_list, const int *live_count,
+                                                             double *hess, void *ws, size_t ws_bytes, void *stream) {
+    CHB_REQUIRE(live_list && live_count, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_dparams_to_action_hess_listed_dev: NULL list");
+    return hess_common(p, batch, segmpos, dparams, nullptr, live_list, live_count, hess, ws, ws_bytes, stream);
+}
+
+// End of a GMRES cycle for every state: back substitution on the state's own kdone x kdone triangle of R, then
+// sol = scale * sum_(j < kdone) y_j v_j (scipy.sparse.linalg.gmres: y = solve_triangular(R, g); x += V^T y)
+extern "C" int chb_gmres_solution_dev(chb_plan *p, int64_t batch, int64_t n, int m, const double *V, const double *R,
+                                      const double *g, const int64_t *kdone, double scale, double *sol, void *stream) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_gmres_solution_dev: NULL plan");
+    CHB_REQUIRE(batch >= 0 && n >= 1 && m >= 1 && m <= 62, CHB_ERR_INVALID_ARGUMENT,
+                "chb_gmres_solution_dev: need batch >= 0, n >= 1, 1 <= m <= 62");
+    if (batch == 0) return CHB_OK;
+    CHB_REQUIRE(V && R && g && kdone && sol, CHB_ERR_INVALID_ARGUMENT, "chb_gmres_solution_dev: NULL array");
+    CHB_SET_DEVICE();
+    chb_stream_t st = (chb_stream_t)stream;
+#ifndef CHB_HOSTSIM
+    CHB_LAUNCH(p, k_gmres_solution, batch, 256, 0, st, (long long)batch, (long long)n, m, V, R, g, (const long long *)kdone, scale, sol);
+#else
+    (void)st;
+    chk_solution_host(batch, n, m, V, R, g, (const long long *)kdone, scale, sol);
+    p->launches++;
+#endif
     return CHB_OK;
 }
 

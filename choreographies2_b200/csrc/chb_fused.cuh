@@ -79,6 +79,9 @@ struct ChfArgs {
     double *scalar_out;     // [B] kinetic - potential, or NULL
     int kin_from;           // 0 none, 1 kinetic energy from vec_in (load phase), 2 from kin_src (store phase)
     long long nstates;      // batch size (bound of the L2 prefetch)
+    const unsigned char *skip;  // [B] or NULL: states with a non-zero byte are left out (their outputs are not written)
+    const int *live_list;       // or NULL: the states to process (any order, each at most once) ...
+    const int *live_count;      // ... and how many of them (device memory: written by the previous kernel of the stream)
 };
 
 // XOR swizzle of the low nibble with the next two nibbles: every access pattern of the passes (lanes along any one of the
@@ -1107,7 +1110,7 @@ CHB_D void cta_fused_prologue(Ctx &ctx, const ChfSys &F, cd *sm) {
 // the CTA program
 // ------------------------------------------------------------------------------------------------
 template <int NSEG, int PMODE, class Ctx>
-CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, double *red, cd *sm) {
+CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, long long b_pf, double *red, cd *sm) {
     const double *vec_b = A.vec_in ? A.vec_in + b * F.nparams : (const double *)0;
     const double *kin_b = A.kin_src ? A.kin_src + b * F.nparams : (const double *)0;
     const double *seg_in_b = A.seg_in ? A.seg_in + b * F.segsz : (const double *)0;
@@ -1124,9 +1127,9 @@ CHB_D void cta_fused(Ctx &ctx, const ChfSys &F, const ChfArgs &A, long long b, d
             cd *buf = sm + L.smem_off;
             if (F.ver >= 2) {
                 if (!(F.dbg & 1)) chf_load_pass_r(grp, F, L, vec_b, buf, red, A.kin_from == 1, stash);
-                if (F.pf_stride > 0 && b + F.pf_stride < A.nstates && !(F.dbg & 512))
+                if (F.pf_stride > 0 && b_pf < A.nstates && !(F.dbg & 512))
                     grp.one([&]() {
-                        chf_prefetch_l2(A.vec_in + (b + F.pf_stride) * F.nparams, L.mom_off - L.nco_in, 4LL * L.npr,
+                        chf_prefetch_l2(A.vec_in + b_pf * F.nparams, L.mom_off - L.nco_in, 4LL * L.npr,
                                         A.vec_in + A.nstates * F.nparams);
                     });
                 if (!(F.dbg & 2)) chf_fft_spec_to_time(grp, buf, L, true, twsm, F.dbg & 256);

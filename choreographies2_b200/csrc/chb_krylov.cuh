@@ -31,6 +31,7 @@ struct ChkGivens {
     long long *kdone;
     unsigned char *done;
     int m;
+    int *live_list, *live_count;  // optional: the states still running after this step are appended (any order) for the next one
 };
 
 // one thread per state: previous rotations on the new column, the new rotation, R / g update, stopping test
@@ -58,7 +59,25 @@ CHK_HD void chk_givens_update(const ChkGivens &G, long long a, int j, double *hc
     g[j + 1] = -s * gj;
     g[j] = c * gj;
     G.kdone[a] = j + 1;
-    if (fabs(g[j + 1]) <= G.target[a]) G.done[a] = 1;
+    if (fabs(g[j + 1]) <= G.target[a]) {
+        G.done[a] = 1;
+    } else if (G.live_list) {
+#ifdef __CUDA_ARCH__
+        G.live_list[atomicAdd(G.live_count, 1)] = (int)a;
+#else
+        G.live_list[(*G.live_count)++] = (int)a;
+#endif
+    }
+}
+
+// y = R[:k,:k]^-1 g[:k] for one state (a zero pivot is replaced by 1, like the array-level code)
+CHK_HD void chk_back_subst(const double *R, const double *g, int m, int k, double *y) {
+    for (int j = k - 1; j >= 0; --j) {
+        double acc = g[j];
+        for (int i = j + 1; i < k; ++i) acc -= R[(size_t)j * m + i] * y[i];
+        const double d = R[(size_t)j * m + j];
+        y[j] = acc / (d != 0.0 ? d : 1.0);
+    }
 }
 
 #ifndef CHB_HOSTSIM
@@ -216,7 +235,41 @@ k_arnoldi_smem(long long rows, long long n, int j, int ldh, double *V, const dou
         if (G.R) chk_givens_update(G, a, j, sh);
     }
 }
+
+__global__ void __launch_bounds__(256)
+k_gmres_solution(long long rows, long long n, int m, const double *V, const double *R, const double *g, const long long *kdone,
+                 double scale, double *sol) {
+    __shared__ double y[64];
+    const long long a = blockIdx.x;
+    int k = (int)kdone[a];
+    k = k < 0 ? 0 : (k > m ? m : k);
+    if (threadIdx.x == 0) chk_back_subst(R + (size_t)a * (m + 1) * m, g + (size_t)a * (m + 1), m, k, y);
+    __syncthreads();
+    const size_t vs = (size_t)rows * (size_t)n;
+    const double *va = V + (size_t)a * n;
+    for (long long e = threadIdx.x; e < n; e += 256) {
+        double s = 0.0;
+#pragma unroll 4
+        for (int j = 0; j < k; ++j) s = fma(y[j], va[(size_t)j * vs + e], s);
+        sol[(size_t)a * n + e] = scale * s;
+    }
+}
 #else
+static void chk_solution_host(long long rows, long long n, int m, const double *V, const double *R, const double *g,
+                              const long long *kdone, double scale, double *sol) {
+    const size_t vs = (size_t)rows * (size_t)n;
+    for (long long a = 0; a < rows; ++a) {
+        double y[64];
+        int k = (int)kdone[a];
+        k = k < 0 ? 0 : (k > m ? m : k);
+        chk_back_subst(R + (size_t)a * (m + 1) * m, g + (size_t)a * (m + 1), m, k, y);
+        for (long long e = 0; e < n; ++e) {
+            double s = 0.0;
+            for (int j = 0; j < k; ++j) s += y[j] * V[(size_t)j * vs + (size_t)a * n + e];
+            sol[(size_t)a * n + e] = scale * s;
+        }
+    }
+}
 // host emulation (tests/hostsim): the same arithmetic, one state after the other
 static void chk_arnoldi_host(long long rows, long long n, int j, int ldh, double *V, const double *w,
                              const unsigned char *skip, double *h, ChkGivens G) {

@@ -323,10 +323,78 @@ class NBodySystB200:
             C.c_void_p(sk.ctypes.data) if sk is not None else None, C.c_void_p(h.ctypes.data), None))
         return True
 
-    def gmres_step(self, V, j: int, w, done, R, g, cs, target, kdone) -> bool:
+    def _direct_ok(self, a) -> bool:
+        """True when the library can address ``a`` directly: CUDA tensors, or NumPy arrays with the host emulation build."""
+        return _is_torch(a) or str(getattr(self._lib, "_name", "")).endswith("libchb_hostsim.so")
+
+    def _ptr_stream(self, like):
+        if _is_torch(like):
+            import torch
+            return (lambda t: C.c_void_p(t.data_ptr()) if t is not None else None), \
+                C.c_void_p(torch.cuda.current_stream(like.device).cuda_stream)
+        return (lambda t: C.c_void_p(t.ctypes.data) if t is not None else None), None
+
+    def _ws_direct(self, batch, like):
+        if _is_torch(like):
+            ws = self._workspace(batch, like)
+            return C.c_void_p(ws.data_ptr()), ws.numel()
+        need = C.c_size_t()
+        L.check(self._lib, self._lib.chb_workspace_bytes(self._plan, batch, C.byref(need)))
+        if getattr(self, "_ws_np", None) is None or self._ws_np.size < need.value:
+            self._ws_np = np.empty(int(need.value), dtype=np.uint8)
+        return C.c_void_p(self._ws_np.ctypes.data), self._ws_np.size
+
+    def hess_masked(self, segmpos, dparams, skip, out) -> bool:
+        """``segmpos_dparams_to_action_hess`` into ``out`` for the states whose ``skip`` flag (bool ``[batch]``) is clear
+        (``chb_segmpos_dparams_to_action_hess_masked_dev``); rows of flagged states may be left untouched.  2-D inputs.
+        Returns False when the library cannot address the arrays."""
+        if not self._direct_ok(segmpos):
+            return False
+        b = int(dparams.shape[0])
+        if tuple(segmpos.shape) != (b,) + self.segmpos_shape or tuple(dparams.shape) != (b, self.nparams) \
+                or tuple(out.shape) != (b, self.nparams) or tuple(skip.shape) != (b,):
+            raise ValueError("hess_masked: inconsistent shapes")
+        ptr, stream = self._ptr_stream(dparams)
+        wsp, wsn = self._ws_direct(b, dparams)
+        L.check(self._lib, self._lib.chb_segmpos_dparams_to_action_hess_masked_dev(
+            self._plan, b, ptr(segmpos), ptr(dparams), ptr(skip), ptr(out), wsp, wsn, stream))
+        return True
+
+    def hess_listed(self, segmpos, dparams, live_list, live_count, out) -> bool:
+        """``segmpos_dparams_to_action_hess`` into ``out`` for the states ``live_list[: live_count[0]]`` (int32 arrays in the
+        library's memory, e.g. written by ``gmres_step``): ``chb_segmpos_dparams_to_action_hess_listed_dev``."""
+        if not self._direct_ok(segmpos):
+            return False
+        b = int(dparams.shape[0])
+        if tuple(segmpos.shape) != (b,) + self.segmpos_shape or tuple(dparams.shape) != (b, self.nparams) \
+                or tuple(out.shape) != (b, self.nparams) or int(live_list.shape[0]) < b:
+            raise ValueError("hess_listed: inconsistent shapes")
+        ptr, stream = self._ptr_stream(dparams)
+        wsp, wsn = self._ws_direct(b, dparams)
+        L.check(self._lib, self._lib.chb_segmpos_dparams_to_action_hess_listed_dev(
+            self._plan, b, ptr(segmpos), ptr(dparams), ptr(live_list), ptr(live_count), ptr(out), wsp, wsn, stream))
+        return True
+
+    def gmres_solution(self, V, R, g, kdone, scale: float, out) -> bool:
+        """``out[b] = scale * sum_(j < kdone[b]) y_j V[j, b]`` with ``y`` from the back substitution on the state's triangle
+        of ``R`` (``chb_gmres_solution_dev``).  Returns False when the library cannot address the arrays."""
+        if not self._direct_ok(V):
+            return False
+        m, batch, n = int(V.shape[0]) - 1, int(V.shape[1]), int(V.shape[2])
+        if tuple(R.shape) != (batch, m + 1, m) or tuple(g.shape) != (batch, m + 1) or tuple(kdone.shape) != (batch,) \
+                or tuple(out.shape) != (batch, n):
+            raise ValueError("gmres_solution: inconsistent shapes")
+        ptr, stream = self._ptr_stream(V)
+        L.check(self._lib, self._lib.chb_gmres_solution_dev(self._plan, batch, n, m, ptr(V), ptr(R), ptr(g), ptr(kdone),
+                                                            float(scale), ptr(out), stream))
+        return True
+
+    def gmres_step(self, V, j: int, w, done, R, g, cs, target, kdone, live_list_next=None, live_count_next=None) -> bool:
         """One whole inner iteration of the batched GMRES (``chb_gmres_step_dev``): Arnoldi step + Givens rotations + R / g /
         kdone / done updates, all in place, one launch.  Shapes: ``V [m+1, batch, n]``, ``w [batch, n]``, ``done [batch]``
         bool, ``R [batch, m+1, m]``, ``g [batch, m+1]``, ``cs [batch, m, 2]``, ``target [batch]``, ``kdone [batch]`` int64.
+        ``live_list_next`` (int32 ``[batch]``) / ``live_count_next`` (int32 ``[1]``, zero on entry): the states still running
+        after this step are appended, for ``hess_listed`` of the next step.
         Returns False when the library cannot address the arrays (see ``arnoldi_step``)."""
         torch_in = _is_torch(V)
         if not torch_in and not str(getattr(self._lib, "_name", "")).endswith("libchb_hostsim.so"):
@@ -361,7 +429,9 @@ class NBodySystB200:
             ptr = lambda t: C.c_void_p(t.ctypes.data)
             stream = None
         L.check(self._lib, self._lib.chb_gmres_step_dev(self._plan, batch, n, int(j), m, ptr(V), ptr(w), ptr(done), ptr(R),
-                                                        ptr(g), ptr(cs), ptr(target), ptr(kdone), stream))
+                                                        ptr(g), ptr(cs), ptr(target), ptr(kdone),
+                                                        ptr(live_list_next) if live_list_next is not None else None,
+                                                        ptr(live_count_next) if live_count_next is not None else None, stream))
         return True
 
     def TestHashSame(self, Hash_a, Hash_b, rtol: float = 1e-5, detect_multiples: bool = True) -> bool:

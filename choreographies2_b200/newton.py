@@ -35,9 +35,9 @@ class _XP:
 
     def zeros(self, shape, dtype="f8"):
         if self.torch:
-            dt = {"f8": self.t.float64, "i8": self.t.int64, "b": self.t.bool}[dtype]
+            dt = {"f8": self.t.float64, "i8": self.t.int64, "i4": self.t.int32, "b": self.t.bool}[dtype]
             return self.t.zeros(shape, dtype=dt, device=self.dev)
-        return np.zeros(shape, dtype={"f8": np.float64, "i8": np.int64, "b": bool}[dtype])
+        return np.zeros(shape, dtype={"f8": np.float64, "i8": np.int64, "i4": np.int32, "b": bool}[dtype])
 
     def empty(self, shape):
         return self.t.empty(shape, dtype=self.t.float64, device=self.dev) if self.torch else np.empty(shape)
@@ -194,6 +194,62 @@ def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20, arnoldi=None, s
     return sol, kdone, nmv
 
 
+class _Buffers:
+    """Flat scratch arrays of the library path, reused across the Newton iterations (the active set only shrinks)."""
+
+    def __init__(self, xp: _XP):
+        self.xp, self.flat = xp, {}
+
+    def arange(self, n):
+        a = self.flat.get("arange")
+        if a is None or a.shape[0] < n:
+            a = self.flat["arange"] = self.xp.t.arange(n, dtype=self.xp.t.int32, device=self.xp.dev) if self.xp.torch \
+                else np.arange(n, dtype=np.int32)
+        return a[:n]
+
+    def get(self, name, shape):
+        size = 1
+        for d in shape:
+            size *= int(d)
+        buf = self.flat.get(name)
+        if buf is None or buf.shape[0] < size:
+            buf = self.flat[name] = self.xp.empty((size,))
+        return buf[:size].reshape(shape)
+
+
+def gmres_batched_lib(xp: _XP, nbs, seg, rhs, rtol, restart: int, bufs: _Buffers, check_every: int = 4):
+    """``gmres_batched`` with every array-sized step inside the library: per inner iteration one Hessian-vector launch over the
+    list of running states (``hess_listed``: no gather / scatter of the active rows, the persistent CTAs share the listed states
+    evenly) and one ``gmres_step`` launch (Arnoldi + Givens + stopping test + the list for the next iteration); one
+    ``gmres_solution`` launch at the end.  The host looks at
+    the stop flags only every ``check_every`` iterations (a device synchronisation).  Returns (solution, inner iterations)."""
+    A, n = int(rhs.shape[0]), int(rhs.shape[1])
+    m = int(restart)
+    V = bufs.get("V", (m + 1, A, n))
+    w = bufs.get("w", (A, n))
+    beta = xp.norm(rhs)
+    V[0] = rhs / xp.where(beta > 0, beta, beta + 1.0)[:, None]
+    R = xp.zeros((A, m + 1, m))
+    g = xp.zeros((A, m + 1))
+    g[:, 0] = beta
+    cs = xp.zeros((A, m, 2))
+    target = xp.zeros((A,)) + rtol * beta
+    done = ~(beta > 0)
+    kdone = xp.zeros((A,), "i8")
+    lists = xp.zeros((2, A), "i4")
+    counts = xp.zeros((m + 1,), "i4")
+    lists[0] += bufs.arange(A)  # states with a zero right-hand side included: their matvec is 0 and the step skips them
+    counts[0] += A
+    for j in range(m):
+        if j > 0 and j % check_every == 0 and bool(done.all()):
+            break
+        nbs.hess_listed(seg, V[j], lists[j & 1], counts[j:j + 1], w)
+        nbs.gmres_step(V, j, w, done, R, g, cs, target, kdone, lists[(j + 1) & 1], counts[j + 1:j + 2])
+    sol = xp.empty((A, n))
+    nbs.gmres_solution(V, R, g, kdone, 1.0, sol)
+    return sol, kdone
+
+
 def _take(xp: _XP, a, idx):
     return a if idx is None else a[idx]
 
@@ -217,7 +273,12 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search) 
     # CHB_NO_GMRES_STEP=1: the library's Arnoldi step but the Givens / stopping logic at array level
     arnoldi = None if os.environ.get("CHB_NO_ARNOLDI", "0") not in ("", "0") else getattr(nbs, "arnoldi_step", None)
     step = None if arnoldi is None or os.environ.get("CHB_NO_GMRES_STEP", "0") not in ("", "0") else getattr(nbs, "gmres_step", None)
+    # everything in the library (masked matvec + whole GMRES iteration + solution kernels) when it can address the arrays
+    lib_gmres = step is not None and hasattr(nbs, "hess_masked") and nbs._direct_ok(x0) \
+        and os.environ.get("CHB_NO_GMRES_LIB", "0") in ("", "0")
+    bufs = _Buffers(xp)
     n_grad = n_hess = 0
+    n_hess_lazy = []  # per-cycle device sums, read once at the end
 
     def func(idx, xs):
         nonlocal n_grad
@@ -250,7 +311,13 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search) 
             return nbs.segmpos_dparams_to_action_hess(seg if idx is None else seg[idx], v)
 
         tol = xp.minimum(etaa, etaa * Fna)  # nonlin.py:113
-        sol, _, _ = gmres_batched(xp, matvec, Fa, tol, restart, arnoldi, step)
+        if lib_gmres:
+            sol, kd = gmres_batched_lib(xp, nbs, seg if seg.is_contiguous() else seg.contiguous(), Fa if allact else Fa.contiguous(),
+                                        tol, restart, bufs) if xp.torch else \
+                gmres_batched_lib(xp, nbs, np.ascontiguousarray(seg), np.ascontiguousarray(Fa), tol, restart, bufs)
+            n_hess_lazy.append(kd.sum())
+        else:
+            sol, _, _ = gmres_batched(xp, matvec, Fa, tol, restart, arnoldi, step)
         dx = -sol
         # ---- line search on phi(s) = |F(x + s dx)|^2, scalar_search_armijo(phi, phi0, -phi0, amin=smin) per state ----
         phi0 = Fna * Fna
@@ -335,5 +402,6 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search) 
         conv = (status == 0) & (xp.maxabs(Fx) <= f_tol)
         status = xp.where(conv, status * 0 + 1, status)
     status = xp.where(status == 0, status * 0 + 2, status)
+    n_hess += sum(int(v) for v in n_hess_lazy)
     return NewtonResult(x=x, status=xp.to_numpy(status), nit=xp.to_numpy(nit), fnorm=xp.to_numpy(xp.maxabs(Fx)),
                         n_grad_evals=n_grad, n_hess_evals=n_hess)

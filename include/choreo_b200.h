@@ -175,10 +175,16 @@ int chb_arnoldi_step_dev(chb_plan *plan, int64_t batch, int64_t n, int j, int ld
  * iteration of scipy.sparse.linalg.gmres does: previous Givens rotations on the new Hessenberg column, the new rotation,
  * column j of R, the rotated right-hand side g, the iteration count and the stopping test.
  *   done   [batch] bytes     in: states to skip; out: additionally set where |g[j+1]| <= target
- *   R      [batch][m+1][m]   g [batch][m+1]   cs [batch][m][2] (c, s of rotation k)   target [batch]   kdone [batch] int64 */
+ *   R      [batch][m+1][m]   g [batch][m+1]   cs [batch][m][2] (c, s of rotation k)   target [batch]   kdone [batch] int64
+ *   live_list_next [batch] / live_count_next [1] (both or neither NULL): the states still running after this step are
+ *   appended to the list (any order; *live_count_next must be 0 on entry) for chb_..._hess_listed_dev of the next step */
 int chb_gmres_step_dev(chb_plan *plan, int64_t batch, int64_t n, int j, int m, double *V, const double *w,
                        unsigned char *done, double *R, double *g, double *cs, const double *target, int64_t *kdone,
-                       void *stream);
+                       int *live_list_next, int *live_count_next, void *stream);
+/* End of a GMRES cycle, all states in one launch: back substitution on each state's kdone x kdone triangle of R and
+ * sol[b] = scale * sum_(j < kdone[b]) y_j V[j][b]  (scipy.sparse.linalg.gmres: solve_triangular + x += V^T y). */
+int chb_gmres_solution_dev(chb_plan *plan, int64_t batch, int64_t n, int m, const double *V, const double *R,
+                           const double *g, const int64_t *kdone, double scale, double *sol, void *stream);
 /* segm_pos_to_pot_nrg_grad, cdef :6472-6533 ; grad_segmpos is overwritten (reference accumulates into a zeroed buffer) */
 int chb_segmpos_to_pot_nrg_grad_dev(chb_plan *plan, int64_t batch, const double *segmpos, double globalmul,
                                     double *grad_segmpos, void *workspace, size_t workspace_bytes, void *stream);
@@ -209,6 +215,16 @@ int chb_segmpos_params_to_action_grad_dev(chb_plan *plan, int64_t batch, const d
 int chb_segmpos_dparams_to_action_hess_dev(chb_plan *plan, int64_t batch, const double *segmpos,
                                            const double *dparams, double *hess, void *workspace,
                                            size_t workspace_bytes, void *stream);
+/* The same operator inside the batched GMRES: skip [batch] bytes, states with a non-zero byte (their GMRES has stopped) MAY
+ * be left out -- their rows of hess are then not written (the fused kernels skip them, the staged kernels compute them). */
+int chb_segmpos_dparams_to_action_hess_masked_dev(chb_plan *plan, int64_t batch, const double *segmpos,
+                                                  const double *dparams, const unsigned char *skip, double *hess,
+                                                  void *workspace, size_t workspace_bytes, void *stream);
+/* ... and with the states to process given as a list in device memory, live_list[0 .. *live_count) (each state at most
+ * once, any order): the persistent CTAs share the listed states evenly.  Rows of states not listed are not written. */
+int chb_segmpos_dparams_to_action_hess_listed_dev(chb_plan *plan, int64_t batch, const double *segmpos,
+                                                  const double *dparams, const int *live_list, const int *live_count,
+                                                  double *hess, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---- host-pointer operators: H2D copy + operator + D2H copy, synchronous ------------------------ */
 /* which: one of the CHB_OP_* codes; unused pointers may be NULL.  in0/in1 -> out0/out1:

@@ -91,3 +91,122 @@ def test_arnoldi_step_gpu(n, j, with_skip):
     dev = torch.device("cuda:0")
     _check(nbs, lambda a: torch.as_tensor(np.ascontiguousarray(a), device=dev), lambda t: t.cpu().numpy(),
            7, n, j, 20, 5 + n, with_skip)
+
+
+def _masked_case(nbs, B, seed, forced):
+    rng = np.random.default_rng(seed)
+    x, dx = rng.random((B, nbs.nparams)), rng.random((B, nbs.nparams))
+    skip = rng.random(B) < 0.4
+    for b, v in forced.items():
+        skip[b] = v
+    return x, dx, skip
+
+
+@pytest.mark.parametrize("name,nint,B,ver", [("3C", 96, 9, 3), ("3B", 4096, 300, 4)])
+def test_hess_masked_hostsim(name, nint, B, ver):
+    """The masked Hessian-vector operator of the GMRES loop: flagged states are left out by the fused kernels (their rows of the
+    output keep what was there), the other rows equal the plain operator bit for bit.  The version-4 case has more states than
+    the emulated grid has CTAs (148): CTA 0 starts on a flagged state, CTA 5 owns only flagged states, CTA 7 a flagged state
+    between two live ones."""
+    from hostsim import build_hostsim
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", f"{name}.npz"))
+    nbs = NBodySystB200(T, nint, _lib_handle=build_hostsim.load())
+    assert nbs.fused_version == ver
+    forced = {0: True, 1: False}
+    if B > 296:
+        forced.update({5: True, 153: True, 7: False, 155: True, 148: False, 296: False, 2: False, 150: False, 298: True})
+    x, dx, skip = _masked_case(nbs, B, 3, forced)
+    live = np.nonzero(~skip)[0]
+    seg = np.zeros((B,) + nbs.segmpos_shape)
+    seg[live] = nbs.params_to_segmpos(x[live])
+    out = np.full((B, nbs.nparams), -7.25)
+    assert nbs.hess_masked(seg, dx, skip, out)
+    ref = nbs.segmpos_dparams_to_action_hess(seg[live], dx[live])
+    assert np.array_equal(out[live], ref)
+    assert np.all(out[skip] == -7.25)
+    # the same states given as a list (any order), longer than the emulated grid in the version-4 case
+    lst = np.zeros(B, dtype=np.int32)
+    lst[:live.size] = np.random.default_rng(0).permutation(live)
+    out2 = np.full((B, nbs.nparams), -7.25)
+    assert nbs.hess_listed(seg, dx, lst, np.array([live.size], dtype=np.int32), out2)
+    assert np.array_equal(out2, out)
+    out2[:] = 1.5
+    assert nbs.hess_listed(seg, dx, lst, np.array([0], dtype=np.int32), out2) and np.all(out2 == 1.5)
+
+
+def test_gmres_solution_hostsim():
+    from hostsim import build_hostsim
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nbs = NBodySystB200(T, 96, _lib_handle=build_hostsim.load())
+    rng = np.random.default_rng(2)
+    A, n, m = 6, 130, 20
+    V = rng.standard_normal((m + 1, A, n))
+    R = np.triu(rng.standard_normal((A, m + 1, m))) + 3 * np.eye(m + 1, m)
+    g = rng.standard_normal((A, m + 1))
+    kdone = np.array([0, 1, 5, 20, 13, 2])
+    R[4, 3, 3] = 0.0  # zero pivot: replaced by 1
+    out = np.empty((A, n))
+    assert nbs.gmres_solution(V, R, g, kdone, -1.0, out)
+    for a in range(A):
+        k = kdone[a]
+        Rk = R[a, :k, :k].copy()
+        for i in range(k):
+            if Rk[i, i] == 0:
+                Rk[i, i] = 1.0
+        y = np.linalg.solve(Rk, g[a, :k]) if k else np.zeros(0)
+        assert np.abs(out[a] + y @ V[:k, a]).max() < 1e-9 * max(1.0, np.abs(y).max(initial=0.0))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,nint,B,ver", [("3C", 3072, 700, 3), ("3B", 4096, 1000, 4)])
+def test_hess_masked_gpu(name, nint, B, ver):
+    import torch
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", f"{name}.npz"))
+    nbs = NBodySystB200(T, nint)
+    assert nbs.fused_version == ver
+    x, dx, skip = _masked_case(nbs, B, 4, {0: True, 1: False, B - 1: True})
+    dev = torch.device("cuda:0")
+    xd, dxd, sk = torch.as_tensor(x, device=dev), torch.as_tensor(dx, device=dev), torch.as_tensor(skip, device=dev)
+    seg = nbs.params_to_segmpos(xd)
+    out = torch.full((B, nbs.nparams), -7.25, dtype=torch.float64, device=dev)
+    assert nbs.hess_masked(seg, dxd, sk, out)
+    ref = nbs.segmpos_dparams_to_action_hess(seg, dxd)
+    torch.cuda.synchronize()
+    assert torch.equal(out[~sk], ref[~sk])
+    assert bool((out[sk] == -7.25).all())
+    live = torch.nonzero(~sk).flatten()
+    lst = torch.zeros(B, dtype=torch.int32, device=dev)
+    lst[:live.numel()] = live[torch.randperm(live.numel(), device=dev)].to(torch.int32)
+    out2 = torch.full((B, nbs.nparams), -7.25, dtype=torch.float64, device=dev)
+    assert nbs.hess_listed(seg, dxd, lst, torch.tensor([live.numel()], dtype=torch.int32, device=dev), out2)
+    torch.cuda.synchronize()
+    assert torch.equal(out2, out)
+    assert nbs.hess_listed(seg, dxd, lst, torch.zeros(1, dtype=torch.int32, device=dev), out2)
+    torch.cuda.synchronize()
+    assert torch.equal(out2, out)
+    # all states flagged: nothing is written, nothing hangs
+    out.fill_(1.5)
+    assert nbs.hess_masked(seg, dxd, torch.ones(B, dtype=torch.bool, device=dev), out)
+    torch.cuda.synchronize()
+    assert bool((out == 1.5).all())
+
+
+@pytest.mark.gpu
+def test_gmres_solution_gpu():
+    import torch
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nbs = NBodySystB200(T, 96)
+    rng = np.random.default_rng(2)
+    A, n, m = 9, 6142, 20
+    V = rng.standard_normal((m + 1, A, n))
+    R = np.triu(rng.standard_normal((A, m + 1, m))) + 3 * np.eye(m + 1, m)
+    g = rng.standard_normal((A, m + 1))
+    kdone = np.array([0, 1, 5, 20, 13, 2, 7, 19, 3])
+    dev = torch.device("cuda:0")
+    out = torch.empty((A, n), dtype=torch.float64, device=dev)
+    assert nbs.gmres_solution(*(torch.as_tensor(a, device=dev) for a in (V, R, g, kdone)), 1.0, out)
+    got = out.cpu().numpy()
+    for a in range(A):
+        k = kdone[a]
+        y = np.linalg.solve(R[a, :k, :k], g[a, :k]) if k else np.zeros(0)
+        assert np.abs(got[a] - y @ V[:k, a]).max() < 1e-9 * max(1.0, np.abs(y).max(initial=0.0))
