@@ -1375,7 +1375,8 @@ CHB_KERNEL void CHF_BOUNDS k_fused(ChfSys F, ChfArgs A) {
 }
 
 // version 4 of the fused kernel (chb_fused4.cuh): persistent CTAs, rows moved by bulk asynchronous copies
-template <int NSEG, int PMODE>
+// SEL: 0 = every state of the batch, grid stride; 1 = the states selected by A.skip / A.live_list (GMRES matvec)
+template <int NSEG, int PMODE, int SEL = 0>
 CHB_KERNEL void CHF_BOUNDS k_fused4(ChfSys F, ChfArgs A) {
     CHB_CTX_DECL;
 #ifndef CHB_HOSTSIM
@@ -1422,27 +1423,34 @@ CHB_KERNEL void CHF_BOUNDS k_fused4(ChfSys F, ChfArgs A) {
     cd *sm = (cd *)(CHB_SMEM + CHF_RED_BYTES);
     // the states of this CTA: grid stride over the batch (the ones flagged in A.skip left out) or over A.live_list; the next
     // state is known one state ahead: its rows are requested while the current one drains
-    const long long nlive = A.live_list ? (long long)*A.live_count : 0;
-    auto settle = [&](long long k) {  // first position >= k (same CTA) that is not flagged
-        if (!A.live_list)
-            while (A.skip && k < A.nstates && A.skip[k]) k += CHB_GRID_DIM;
-        return k;
-    };
-    auto state_at = [&](long long k) {  // position -> state (nstates: none left)
-        if (A.live_list) return k < nlive ? (long long)A.live_list[k] : A.nstates;
-        return k < A.nstates ? k : A.nstates;
-    };
-    long long k = settle(CHB_BLOCK_ID);
-    const long long b_first = state_at(k);
-    cta_fused4_first_loads(ctx, F, A, b_first, sm);
-    cta_fused4_prologue(ctx, F, sm);
     unsigned parity = 0;
     double *red_alt = (double *)(sm + F.tw4_off + 256);  // second buffer of partial sums, behind the twiddle tables
-    for (long long b = b_first; b < A.nstates; parity ^= 1u) {
-        k = settle(k + CHB_GRID_DIM);
-        const long long bn = state_at(k);
-        cta_fused4<NSEG, PMODE>(ctx, F, A, b, bn, parity, parity ? red_alt : red, sm);
-        b = bn;
+    if (SEL == 0) {
+        cta_fused4_first_loads(ctx, F, A, CHB_BLOCK_ID, sm);
+        cta_fused4_prologue(ctx, F, sm);
+        for (long long b = CHB_BLOCK_ID; b < A.nstates; b += CHB_GRID_DIM, parity ^= 1u)
+            cta_fused4<NSEG, PMODE>(ctx, F, A, b, b + CHB_GRID_DIM, parity, parity ? red_alt : red, sm);
+    } else {
+        // (32-bit positions, the list length re-read from memory: the loop state stays out of the register budget of the passes)
+        auto settle = [&](int k) {  // first position >= k (same CTA) that is not flagged
+            if (!A.live_list)
+                while (A.skip && k < (int)A.nstates && A.skip[k]) k += (int)CHB_GRID_DIM;
+            return k;
+        };
+        auto state_at = [&](int k) -> long long {  // position -> state (nstates: none left)
+            if (A.live_list) return k < *A.live_count ? (long long)A.live_list[k] : A.nstates;
+            return k < (int)A.nstates ? (long long)k : A.nstates;
+        };
+        int k = settle((int)CHB_BLOCK_ID);
+        const long long b_first = state_at(k);
+        cta_fused4_first_loads(ctx, F, A, b_first, sm);
+        cta_fused4_prologue(ctx, F, sm);
+        for (long long b = b_first; b < A.nstates; parity ^= 1u) {
+            k = settle(k + (int)CHB_GRID_DIM);
+            const long long bn = state_at(k);
+            cta_fused4<NSEG, PMODE>(ctx, F, A, b, bn, parity, parity ? red_alt : red, sm);
+            b = bn;
+        }
     }
 #ifndef CHB_HOSTSIM
     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the result rows of the last state have left shared memory
@@ -1594,16 +1602,19 @@ static int launch_fused(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A0, c
         }
         if (p->fsys.nseg == 3) {
             if (pmode == 1) CHB_LAUNCH(p, (k_fused4<3, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
+            else if (A.skip || A.live_list) CHB_LAUNCH(p, (k_fused4<3, 2, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
             else CHB_LAUNCH(p, (k_fused4<3, 2>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
             return CHB_OK;
         }
         if (p->fsys.nseg == 2) {
             if (pmode == 1) CHB_LAUNCH(p, (k_fused4<2, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
+            else if (A.skip || A.live_list) CHB_LAUNCH(p, (k_fused4<2, 2, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
             else CHB_LAUNCH(p, (k_fused4<2, 2>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
             return CHB_OK;
         }
         if (p->fsys.nseg == 1) {
             if (pmode == 1) CHB_LAUNCH(p, (k_fused4<1, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
+            else if (A.skip || A.live_list) CHB_LAUNCH(p, (k_fused4<1, 2, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
             else CHB_LAUNCH(p, (k_fused4<1, 2>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
             return CHB_OK;
         }
