@@ -894,6 +894,11 @@ extern "C" int chb_plan_query(const chb_plan *p, int what, int64_t *v) {
         case CHB_Q_SEGM_SIZE: *v = p->sys.segm_size; break;
         case CHB_Q_SEGM_STORE: *v = p->sys.segm_store; break;
         case CHB_Q_SEGMPOS_SIZE: *v = p->sys.segsz; break;
+#ifdef CHB_HOSTSIM
+        case CHB_Q_HOST_POINTERS: *v = 1; break;
+#else
+        case CHB_Q_HOST_POINTERS: *v = 0; break;
+#endif
         case CHB_Q_FUSED: *v = (p->fused_enabled && p->fused_active) ? ((p->fused_enabled >= 4 && p->fused4_ok) ? 4 : std::min(p->fused_enabled, 3)) : 0; break;
         case CHB_Q_CHUNK: {
             int64_t c = p->chunk_user;

@@ -285,6 +285,11 @@ class NBodySystB200:
                 for e in self.Hash_exp]
         return np.stack(cols, axis=-1).reshape(a.shape[:-3] + (len(self.Hash_exp),))
 
+    def params_resize(self, params_buf_in, nint_fac: int = 1):
+        """_NBodySyst.pyx:2413-2465: the parameters of this ``nint`` level re-expressed at ``nint = 2 nint_min nint_fac``
+        (batched over leading dimensions)."""
+        return self.tables.params_resize(params_buf_in, self.nint, 2 * self.tables.nint_min * int(nint_fac))
+
     # ------------------------------------------------------------------ Krylov helper of the batched Newton driver
     def arnoldi_step(self, V, j: int, w, skip, h) -> bool:
         """One Arnoldi step of the batched GMRES for all states in one launch (``chb_arnoldi_step_dev``): orthogonalises
@@ -293,7 +298,7 @@ class NBodySystB200:
         when the arrays are not ones the library can address (NumPy arrays with the CUDA library): the caller then runs its
         own array-level Gram-Schmidt."""
         torch_in = _is_torch(V)
-        if not torch_in and not str(getattr(self._lib, "_name", "")).endswith("libchb_hostsim.so"):
+        if not self._direct_ok(V):
             return False
         batch, n = int(w.shape[0]), int(w.shape[1])
         if n * 8 > 200 * 1024 or j >= 62:
@@ -324,8 +329,9 @@ class NBodySystB200:
         return True
 
     def _direct_ok(self, a) -> bool:
-        """True when the library can address ``a`` directly: CUDA tensors, or NumPy arrays with the host emulation build."""
-        return _is_torch(a) or str(getattr(self._lib, "_name", "")).endswith("libchb_hostsim.so")
+        """True when the library can address ``a`` directly: CUDA tensors, or NumPy arrays with a build whose ``*_dev`` entry
+        points take host pointers (``CHB_Q_HOST_POINTERS``)."""
+        return _is_torch(a) or bool(self._q(L.Q_HOST_POINTERS))
 
     def _ptr_stream(self, like):
         if _is_torch(like):
@@ -397,7 +403,7 @@ class NBodySystB200:
         after this step are appended, for ``hess_listed`` of the next step.
         Returns False when the library cannot address the arrays (see ``arnoldi_step``)."""
         torch_in = _is_torch(V)
-        if not torch_in and not str(getattr(self._lib, "_name", "")).endswith("libchb_hostsim.so"):
+        if not self._direct_ok(V):
             return False
         batch, n = int(w.shape[0]), int(w.shape[1])
         m = int(R.shape[2])

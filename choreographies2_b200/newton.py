@@ -84,6 +84,9 @@ class _XP:
     def isfinite_rows(self, a):
         return self.t.isfinite(a).all(-1) if self.torch else np.isfinite(a).all(-1)
 
+    def from_numpy_index(self, idx):
+        return self.t.as_tensor(idx, device=self.dev) if self.torch else idx
+
     def to_numpy(self, a):
         return a.detach().cpu().numpy() if self.torch else np.asarray(a)
 
@@ -96,6 +99,8 @@ class NewtonResult:
     fnorm: np.ndarray      # [B] max-norm of the final gradient
     n_grad_evals: int      # U1 evaluations (states x calls)
     n_hess_evals: int      # U2 evaluations
+    best_x: Any = None     # [B, nparams] iterate with the smallest 2-norm of the gradient seen (track_best; nonlin.py:13-39)
+    best_fnorm: Any = None  # [B] that 2-norm (array of the carrier)
 
 
 def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20, arnoldi=None, step=None):
@@ -255,13 +260,17 @@ def _take(xp: _XP, a, idx):
 
 
 def newton_krylov_batched(nbs, x0, f_tol: float = 1e-10, maxiter: int = 50, restart: int = 20, smin: float = 1e-2,
-                          line_search: Optional[str] = "armijo") -> NewtonResult:
-    """See ``_newton_krylov_batched``; masked-out rows may divide by zero in the interpolation formulas: silenced."""
+                          line_search: Optional[str] = "armijo", tol_norm: str = "max", track_best: bool = False) -> NewtonResult:
+    """See ``_newton_krylov_batched``; masked-out rows may divide by zero in the interpolation formulas: silenced.
+    ``tol_norm``: "max" (nonlin_solve_pp's default ``tol_norm``) or "l2" (``np.linalg.norm``, what find.py:264 passes);
+    ``track_best``: also return, per state, the iterate with the smallest gradient 2-norm (``current_best``, find.py:204,252)."""
+    if tol_norm not in ("max", "l2"):
+        raise ValueError("tol_norm must be 'max' or 'l2'")
     with np.errstate(all="ignore"):
-        return _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search)
+        return _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search, tol_norm, track_best)
 
 
-def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search) -> NewtonResult:
+def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search, tol_norm="max", track_best=False) -> NewtonResult:
     """Solve ``nbs.params_to_action_grad(x) = 0`` for every row of ``x0`` ([B, nparams]; NumPy array or torch CUDA tensor).
 
     Termination like the reference's ``TerminationCondition(f_tol=...)`` with the max norm (``nonlin.py:77-78``): a state is
@@ -287,6 +296,9 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search) 
 
     Fx = func(None, x)
     Fnorm = xp.norm(Fx)
+    tnorm = (lambda F, F2: F2) if tol_norm == "l2" else (lambda F, F2: xp.maxabs(F))  # F2: the 2-norm, kept up to date
+    if track_best:
+        best_x, best_n = xp.copy(x), xp.where(Fnorm == Fnorm, Fnorm, Fnorm * 0 + 1e100)
     eta = xp.full((B,), 1e-3)
     gamma, eta_max, eta_threshold = 0.9, 0.9999, 0.1  # nonlin.py:101-105
     status = xp.zeros((B,), "i8")
@@ -294,7 +306,7 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search) 
     for _ in range(int(maxiter)):
         bad = ~xp.isfinite_rows(Fx)
         status = xp.where((status == 0) & bad, status * 0 + 3, status)
-        conv = (status == 0) & (xp.maxabs(Fx) <= f_tol)
+        conv = (status == 0) & (tnorm(Fx, Fnorm) <= f_tol)
         status = xp.where(conv, status * 0 + 1, status)
         act = xp.nonzero(status == 0)
         na = int(act.shape[0])
@@ -398,10 +410,15 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search) 
         else:
             x[act], Fx[act], Fnorm[act], eta[act] = xn, F_fin, Fn_new, eta_new
             nit[act] = nit[act] + 1
+        if track_best:  # current_best.update after every iteration (the callback of find.py:249-257)
+            better = Fnorm < best_n
+            best_x = xp.where(better[:, None], x, best_x)
+            best_n = xp.where(better, Fnorm, best_n)
     else:
-        conv = (status == 0) & (xp.maxabs(Fx) <= f_tol)
+        conv = (status == 0) & (tnorm(Fx, Fnorm) <= f_tol)
         status = xp.where(conv, status * 0 + 1, status)
     status = xp.where(status == 0, status * 0 + 2, status)
     n_hess += sum(int(v) for v in n_hess_lazy)
     return NewtonResult(x=x, status=xp.to_numpy(status), nit=xp.to_numpy(nit), fnorm=xp.to_numpy(xp.maxabs(Fx)),
-                        n_grad_evals=n_grad, n_hess_evals=n_hess)
+                        n_grad_evals=n_grad, n_hess_evals=n_hess,
+                        best_x=best_x if track_best else None, best_fnorm=best_n if track_best else None)

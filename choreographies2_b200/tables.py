@@ -173,6 +173,24 @@ class PlanTables:
     # ------------------------------------------------------------------ (de)serialisation
     _SCALARS = ("geodim", "nbody", "nloop", "nsegm", "nbin", "nint_min", "greater_nstore", "inter_law")
 
+    def params_resize(self, params, nint_in: int, nint_out: int):
+        """Batched restatement of ``NBodySyst.params_resize`` (_NBodySyst.pyx:2413-2465): per loop the leading (lowest
+        frequency) entries are copied, the new high-frequency entries are zero (refinement) or the old ones dropped
+        (coarsening).  ``params``: ``[..., nparams(nint_in)]`` NumPy array or torch tensor; returns ``[..., nparams(nint_out)]``."""
+        lin, lout = self.level(int(nint_in)), self.level(int(nint_out))
+        if params.shape[-1] != lin.nparams:
+            raise ValueError(f"params_resize: last dimension {params.shape[-1]}, expected nparams = {lin.nparams}")
+        shape = tuple(params.shape[:-1]) + (lout.nparams,)
+        if type(params).__module__.startswith("torch"):
+            import torch
+            out = torch.zeros(shape, dtype=params.dtype, device=params.device)
+        else:
+            out = np.zeros(shape, dtype=np.asarray(params).dtype)
+        for il in range(self.nloop):
+            n = int(min(lin.mom_off[il + 1] - lin.mom_off[il], lout.mom_off[il + 1] - lout.mom_off[il]))
+            out[..., int(lout.mom_off[il]):int(lout.mom_off[il]) + n] = params[..., int(lin.mom_off[il]):int(lin.mom_off[il]) + n]
+        return out
+
     def make_params_bounds(self, nint: int, coeff_ampl_o: float = 1e-1, k_infl: int = 1, k_max: int = 200,
                            coeff_ampl_min: float = 1e-16) -> Tuple[np.ndarray, np.ndarray]:
         """``NBodySyst.Make_params_bounds`` (_NBodySyst.pyx:2301-2327): amplitude envelope of ``Make_Init_bounds_coeffs``

@@ -116,7 +116,9 @@ enum chb_query {
     CHB_Q_CHUNK = 9,          /* states processed per internal launch group             */
     CHB_Q_LAUNCHES = 10,      /* kernels launched by this plan since creation (counter)  */
     CHB_Q_FUSED = 11,         /* 0: staged kernels; else the version of the fused single-kernel path that serves this level (3 or 4) */
-    CHB_Q_SEGMPOS_SIZE = 12   /* nsegm*segm_store*geodim                                 */
+    CHB_Q_SEGMPOS_SIZE = 12,  /* nsegm*segm_store*geodim                                 */
+    CHB_Q_HOST_POINTERS = 13  /* 1 when the *_dev entry points of this build address host memory (CPU emulation build of the
+                                 test suite), 0 for the CUDA library (device pointers only)                              */
 };
 
 int chb_abi_version(void);

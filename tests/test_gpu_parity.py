@@ -248,3 +248,35 @@ def test_batched_newton_on_gpu(chb):
     assert np.abs(xd - rh.x).max() < 1e-6  # |dx| ~ f_tol / smallest Hessian eigenvalue (translation-like soft modes)
     for i in range(x0.shape[0]):
         assert abs(nbs.params_to_action(xd[i]) - float(z[f"{name}/stored_action"])) < 1e-9
+
+
+@pytest.mark.gpu
+def test_find_batched_on_gpu(chb):
+    """Coarse-to-fine refinement driver (refine.py) on device tensors (library GMRES kernels, one plan per nint level) against
+    the same driver on NumPy arrays through the host-pointer operators (array-level GMRES): same outcome, level and orbit."""
+    import torch
+    from choreographies2_b200 import refine
+    T = chb.PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nint0 = 2 * T.nint_min * 16
+    x_min, x_max = T.make_params_bounds(nint0, 0.1, 3, 50, 1e-16)
+    starts = []
+    for seed in range(12):
+        np.random.seed(seed)
+        starts.append(x_min + (x_max - x_min) * np.random.random(x_min.shape[0]))
+    x0 = np.stack(starts)
+    kw = dict(gradtol=1e-9, maxiter=40, n_reconverge_it_max=2, Newt_err_norm_max=1e-8, Newt_err_norm_max_save=1e-5)
+    plans = {}
+
+    def make(nint):
+        plans[nint] = chb.NBodySystB200(T, nint)
+        return plans[nint]
+
+    rd = refine.find_batched(make, torch.from_numpy(x0).cuda(), nint0, **kw)
+    rh = refine.find_batched(lambda nint: plans[nint], x0, nint0, **kw)
+    good = np.isin(rh.outcome, (refine.FOUND, refine.APPROX))
+    assert good.sum() >= 2
+    assert np.array_equal(rd.outcome[good], rh.outcome[good]) and np.array_equal(rd.level[good], rh.level[good])
+    for i in np.nonzero(good)[0]:
+        nbs = plans[int(rh.nint[i])]
+        a_d, a_h = nbs.params_to_action(rd.params[i].cpu().numpy()), nbs.params_to_action(rh.params[i])
+        assert abs(a_d - a_h) < 1e-7 * abs(a_h)

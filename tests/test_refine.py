@@ -1,0 +1,135 @@
+"""Coarse-to-fine refinement (choreographies2_b200/refine.py, tables.params_resize) against the reference's own pieces:
+``NBodySyst.params_resize`` and a per-state replay of the outer loop of ``Find_Choreo`` (find.py:225-432) built from the
+UNMODIFIED reference functions (nonlin_solve_pp, current_best, params_resize, the nint_fac setter)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+from choreographies2_b200 import NBodySystB200, PlanTables
+from choreographies2_b200 import refine
+
+
+@pytest.fixture(scope="module")
+def sim():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from hostsim import build_hostsim
+    return build_hostsim.load()
+
+
+@pytest.mark.parametrize("name", ["3C", "3D", "3C5k", "5Dq", "3B"])
+def test_params_resize_roundtrip_and_band_limit(sim, name):
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", f"{name}.npz"))
+    nint = 2 * T.nint_min * 6
+    coarse = NBodySystB200(T, nint, _lib_handle=sim)
+    fine = NBodySystB200(T, 2 * nint, _lib_handle=sim)
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((3, coarse.nparams))
+    xf = coarse.params_resize(x, coarse.nint_fac * 2)
+    assert xf.shape == (3, fine.nparams)
+    assert np.array_equal(fine.params_resize(xf, coarse.nint_fac), x)  # refine then coarsen = identity
+    assert np.count_nonzero(xf) == np.count_nonzero(x)
+    # zero-padded spectrum: the fine path passes through the coarse samples (even points of every segment)
+    sc, sf = coarse.params_to_segmpos(x), fine.params_to_segmpos(xf)
+    n = coarse.segmpos_shape[1] if not T.greater_nstore else coarse.segmpos_shape[1] - 1
+    assert np.abs(sf[:, :, 0:2 * n:2, :] - sc[:, :, :n, :]).max() < 1e-12 * max(1.0, np.abs(sc).max())
+
+
+def test_params_resize_matches_reference():
+    from oracle import ref_loader
+    if not ref_loader.reference_available():
+        pytest.skip("oracle/_ref not built")
+    ref_loader.import_reference()
+    for name in ("3C", "3C5k", "3D"):
+        NBS = ref_loader.build_named(name)
+        T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", f"{name}.npz"))
+        NBS.nint_fac = 6
+        x = np.random.default_rng(1).standard_normal(NBS.nparams)
+        for fac in (12, 3, 6):
+            ref = np.asarray(NBS.params_resize(x, fac))
+            got = T.params_resize(x, NBS.nint, 2 * T.nint_min * fac)
+            assert got.shape == ref.shape and np.array_equal(got, ref), (name, fac)
+
+
+def _reference_find(NBS, x0, nint_fac0, gradtol, maxiter, n_reconverge_it_max, err_max, err_save, mul_c2f):
+    """find.py:225-432 for one state with one optimiser parameter set, no duplicate / escape checks."""
+    from choreo.scipy_plus.nonlin import nonlin_solve_pp, current_best
+    NBS.nint_fac = nint_fac0
+    best = current_best(x0.copy(), NBS.params_to_action_grad(x0))
+    lvl = 0
+    while True:
+        jac = NBS.GetKrylovJacobian(True, {"method": "gmres", "rdiff": None, "outer_k": 5, "inner_tol": 0., "inner_M": None})
+
+        def cb(x, f, f_norm):
+            best.update(x, f, f_norm)
+            return False
+        nonlin_solve_pp(F=NBS.params_to_action_grad, x0=np.copy(best.x), jacobian=jac, verbose=False, maxiter=maxiter,
+                        f_tol=gradtol, line_search="armijo", callback=cb, raise_exception=False, smin=1e-2,
+                        full_output=True, tol_norm=np.linalg.norm)
+        fac = NBS.nint_fac
+        x_fine = NBS.params_resize(best.x, 2 * fac)
+        NBS.nint_fac = 2 * fac
+        f_fine = NBS.params_to_action_grad(x_fine)
+        ff = np.linalg.norm(f_fine)
+        NBS.nint_fac = fac
+        precise, precise_save = ff < err_max, ff < err_save
+        can_refine = lvl < n_reconverge_it_max
+        needs_ref = (ff > mul_c2f * best.f_norm) and (ff > precise_save)
+        collision = (best.f_norm < 1e3 * err_max) and (ff > 1e6 * best.f_norm)
+        if precise and not needs_ref:
+            return refine.FOUND, lvl, best.f_norm, ff, best.x
+        if precise_save and (not can_refine or not needs_ref):
+            return refine.APPROX, lvl, best.f_norm, ff, best.x
+        if not can_refine or not needs_ref:
+            return refine.NOT_CONVERGED, lvl, best.f_norm, ff, best.x
+        if collision:
+            return refine.COLLISION, lvl, best.f_norm, ff, best.x
+        best = current_best(x_fine, f_fine)
+        NBS.nint_fac = 2 * fac
+        lvl += 1
+
+
+def test_find_batched_matches_reference_outer_loop(sim):
+    from oracle import ref_loader
+    if not ref_loader.reference_available():
+        pytest.skip("oracle/_ref not built")
+    ref_loader.import_reference()
+    NBS = ref_loader.build_named("3C")
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    fac0 = 8
+    nint0 = 2 * T.nint_min * fac0
+    NBS.nint_fac = fac0
+    x_min, x_max = map(np.asarray, NBS.Make_params_bounds(0.1, 3, 50, 1e-16))
+    starts = []
+    for seed in range(8):
+        np.random.seed(seed)
+        starts.append(x_min + (x_max - x_min) * np.random.random(NBS.nparams))
+    x0 = np.stack(starts)
+    kw = dict(gradtol=1e-9, maxiter=40, n_reconverge_it_max=2, Newt_err_norm_max=1e-8, Newt_err_norm_max_save=1e-5,
+              mul_coarse_to_fine=3.0)
+    levels = []
+
+    def make(nint):
+        levels.append(nint)
+        return NBodySystB200(T, nint, _lib_handle=sim)
+
+    res = refine.find_batched(make, x0, nint0, **kw)
+    assert levels == sorted(set(levels))  # one plan per level
+    nsame = 0
+    for i in range(x0.shape[0]):
+        out, lvl, fn, ff, xb = _reference_find(NBS, x0[i], fac0, kw["gradtol"], kw["maxiter"], kw["n_reconverge_it_max"],
+                                               kw["Newt_err_norm_max"], kw["Newt_err_norm_max_save"], kw["mul_coarse_to_fine"])
+        if out in (refine.FOUND, refine.APPROX):
+            # the reference found an orbit from this start: the batched driver must stop at the same level with the same orbit
+            assert res.outcome[i] == out and res.level[i] == lvl, (i, res.outcome[i], out, res.level[i], lvl)
+            assert res.nint[i] == nint0 * 2 ** lvl and res.params[i].shape == np.asarray(xb).shape
+            NBS.nint_fac = fac0 * 2 ** lvl
+            a_ref, a_got = NBS.params_to_action(np.asarray(xb)), NBS.params_to_action(np.ascontiguousarray(res.params[i]))
+            assert abs(a_ref - a_got) < 1e-7 * abs(a_ref)
+            nsame += 1
+        else:
+            assert res.outcome[i] not in (0,)
+    assert nsame >= 2
+    assert (res.outcome > 0).all() and res.n_hess_evals > 0
