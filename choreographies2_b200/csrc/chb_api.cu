@@ -1740,6 +1740,29 @@ static int arnoldi_launch(chb_plan *p, const char *name, int64_t batch, int64_t 
     chb_stream_t st = (chb_stream_t)stream;
 #ifndef CHB_HOSTSIM
     const long long ne = (n + CHK_THREADS - 1) / CHK_THREADS;
+    {
+        // rows through a shared-memory ring of bulk copies when they are 16-byte multiples and at least two fit
+        // (CHB_ARNOLDI_RING=0: register-prefetch kernel, for A/B measurements)
+        static const bool ring_on = [] { const char *e = getenv("CHB_ARNOLDI_RING"); return !(e && atoi(e) == 0); }();
+        const size_t rowbytes = sizeof(double) * (size_t)n;
+        const int ne_t = ne <= 4 ? 4 : ne <= 8 ? 8 : ne <= 12 ? 12 : 16;
+        const size_t stagebytes = sizeof(double) * CHK_THREADS * (size_t)ne_t;  // padded row, see k_arnoldi_ring
+        const size_t fit = ((size_t)216 * 1024) / stagebytes;
+        const int nstage = (int)std::min<size_t>(std::min<size_t>(CHK_RING_MAX, (size_t)j + 1), fit);
+        const bool aligned = (n % 2 == 0) && ((((uintptr_t)V) & 15) == 0);
+        if (ring_on && aligned && ne <= 16 && j >= 1 && nstage >= 2) {
+            const size_t smem = stagebytes * (size_t)nstage;
+            if (ne <= 4)
+                CHB_LAUNCH(p, k_arnoldi_ring<4>, batch, CHK_THREADS, smem, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G, nstage, (unsigned)rowbytes);
+            else if (ne <= 8)
+                CHB_LAUNCH(p, k_arnoldi_ring<8>, batch, CHK_THREADS, smem, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G, nstage, (unsigned)rowbytes);
+            else if (ne <= 12)
+                CHB_LAUNCH(p, k_arnoldi_ring<12>, batch, CHK_THREADS, smem, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G, nstage, (unsigned)rowbytes);
+            else
+                CHB_LAUNCH(p, k_arnoldi_ring<16>, batch, CHK_THREADS, smem, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G, nstage, (unsigned)rowbytes);
+            return CHB_OK;
+        }
+    }
     if (ne <= 4)
         CHB_LAUNCH(p, k_arnoldi_reg<4>, batch, CHK_THREADS, 0, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
     else if (ne <= 8)
@@ -1764,7 +1787,7 @@ static int arnoldi_launch(chb_plan *p, const char *name, int64_t batch, int64_t 
 extern "C" int chb_arnoldi_step_dev(chb_plan *p, int64_t batch, int64_t n, int j, int ldh, double *V, const double *w,
                                     const unsigned char *skip, double *h, void *stream) {
     CHB_REQUIRE(h && ldh >= j + 2, CHB_ERR_INVALID_ARGUMENT, "chb_arnoldi_step_dev: h missing or ldh < j + 2");
-    ChkGivens G = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, nullptr};
+    ChkGivens G = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, nullptr, 0};
     return arnoldi_launch(p, "chb_arnoldi_step_dev", batch, n, j, ldh, V, w, skip, h, G, stream);
 }
 // One whole inner iteration of the batched GMRES(m): the Arnoldi step above, then per state the Givens rotations on the new
@@ -1775,8 +1798,13 @@ extern "C" int chb_gmres_step_dev(chb_plan *p, int64_t batch, int64_t n, int j, 
                                   int64_t *kdone, int *live_list_next, int *live_count_next, void *stream) {
     CHB_REQUIRE(done && R && g && cs && target && kdone && j < m, CHB_ERR_INVALID_ARGUMENT,
                 "chb_gmres_step_dev: NULL array or j >= m");
-    ChkGivens G = {R, g, cs, target, (long long *)kdone, done, m, live_list_next, live_count_next};
-    return arnoldi_launch(p, "chb_gmres_step_dev", batch, n, j, 0, V, w, done, nullptr, G, stream);
+    static const bool split_on = [] { const char *e = getenv("CHB_GMRES_TAIL_SPLIT"); return !(e && atoi(e) == 0); }();
+    ChkGivens G = {R, g, cs, target, (long long *)kdone, done, m, live_list_next, live_count_next, split_on ? 1 : 0};
+    CHB_TRY(arnoldi_launch(p, "chb_gmres_step_dev", batch, n, j, 0, V, w, done, nullptr, G, stream));
+#ifndef CHB_HOSTSIM
+    if (G.split && batch > 0) CHB_LAUNCH(p, k_givens_tail, (batch + 127) / 128, 128, 0, (chb_stream_t)stream, (long long)batch, j, G);
+#endif
+    return CHB_OK;
 }
 
 extern "C" int chb_segmpos_to_pot_nrg_grad_dev(chb_plan *p, int64_t batch, const double *segmpos, double globalmul,

@@ -32,6 +32,8 @@ struct ChkGivens {
     unsigned char *done;
     int m;
     int *live_list, *live_count;  // optional: the states still running after this step are appended (any order) for the next one
+    int split;  // 1: the step kernel only stores the raw Hessenberg column into R[:, j]; k_givens_tail (one THREAD per state)
+                // does the update -- the serial per-state tail then runs for all states at once instead of once per CTA wave
 };
 
 // one thread per state: previous rotations on the new column, the new rotation, R / g update, stopping test
@@ -93,6 +95,30 @@ __device__ __forceinline__ double chk_block_sum(double v, double (*sred)[CHK_THR
     return s;
 }
 
+// two sums at once (independent dependency chains: the FP64 add / shuffle latencies overlap)
+__device__ __forceinline__ void chk_block_sum2(double &u, double &v, double (*sred2)[2 * (CHK_THREADS / 32)], int &ph) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        u += __shfl_xor_sync(0xffffffffu, u, o);
+        v += __shfl_xor_sync(0xffffffffu, v, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        sred2[ph][2 * (threadIdx.x >> 5)] = u;
+        sred2[ph][2 * (threadIdx.x >> 5) + 1] = v;
+    }
+    __syncthreads();
+    // lane l takes the partial sums of warp l % 16, four xor steps leave the total in every lane (same order everywhere)
+    const double2 uv = *reinterpret_cast<const double2 *>(&sred2[ph][2 * (threadIdx.x & (CHK_THREADS / 32 - 1))]);
+    u = uv.x;
+    v = uv.y;
+#pragma unroll
+    for (int o = CHK_THREADS / 64; o > 0; o >>= 1) {
+        u += __shfl_xor_sync(0xffffffffu, u, o);
+        v += __shfl_xor_sync(0xffffffffu, v, o);
+    }
+    ph ^= 1;
+}
+
 // n <= CHK_THREADS * NE: the candidate vector and two basis rows (current + prefetched next) live in registers
 template <int NE>
 __global__ void __launch_bounds__(CHK_THREADS, 1)
@@ -104,8 +130,9 @@ k_arnoldi_reg(long long rows, long long n, int j, int ldh, double *V, const doub
     const int tid = threadIdx.x;
     const size_t vs = (size_t)rows * (size_t)n;
     double *vout = V + (size_t)(j + 1) * vs + (size_t)a * n;
-    if (skip && skip[a]) {
-        for (long long e = tid; e < n; e += CHK_THREADS) vout[e] = 0.0;
+    if (skip && skip[a]) {  // (inside the library's GMRES nobody reads the vectors of a stopped state: no zero fill)
+        if (!G.R)
+            for (long long e = tid; e < n; e += CHK_THREADS) vout[e] = 0.0;
         if (h && tid <= j + 1) h[(size_t)a * ldh + tid] = 0.0;
         return;
     }
@@ -172,8 +199,204 @@ k_arnoldi_reg(long long rows, long long n, int j, int ldh, double *V, const doub
         sh[j + 1] = hn;
         if (h)
             for (int i = 0; i <= j + 1; ++i) h[(size_t)a * ldh + i] = sh[i];
-        if (G.R) chk_givens_update(G, a, j, sh);
+        if (G.R) {
+            if (G.split) {
+                double *Rc = G.R + (size_t)a * (G.m + 1) * G.m + j;
+                for (int i = 0; i <= j + 1; ++i) Rc[(size_t)i * G.m] = sh[i];
+            } else {
+                chk_givens_update(G, a, j, sh);
+            }
+        }
     }
+}
+
+// the same step with the basis rows streamed through a shared-memory ring by bulk asynchronous copies (one cp.async.bulk per
+// row, completion on an mbarrier per stage): up to CHK_RING_MAX rows in flight per SM instead of the one prefetched row of
+// k_arnoldi_reg, which is what the HBM latency x bandwidth product asks for with a single resident CTA.  Needs even n (16-byte
+// rows) and at least two rows of shared memory.
+#define CHK_RING_MAX 6
+__device__ __forceinline__ void chk_ring_issue(double *dst, const double *src, unsigned bytes, unsigned long long *bar) {
+    const unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     (unsigned)__cvta_generic_to_shared(dst)), "l"(src), "r"(bytes), "r"(b) : "memory");
+}
+// every lane polls (measured: one polling lane per warp + __syncwarp is 15 % slower at batch 8192)
+__device__ __forceinline__ void chk_ring_wait(unsigned long long *bar, unsigned parity) {
+    const unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "CHK_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra CHK_DONE;\n"
+        "bra CHK_WAIT;\n"
+        "CHK_DONE:\n"
+        "}\n" ::"r"(b), "r"(parity) : "memory");
+}
+
+template <int NE>
+__global__ void __launch_bounds__(CHK_THREADS, 1)
+k_arnoldi_ring(long long rows, long long n, int j, int ldh, double *V, const double *w, const unsigned char *skip, double *h,
+               ChkGivens G, int nstage, unsigned rowbytes) {
+    extern __shared__ __align__(128) unsigned char chk_ring[];
+    __shared__ double sred[2][CHK_THREADS / 32];
+    __shared__ __align__(16) double sred2[2][2 * (CHK_THREADS / 32)];
+    __shared__ double sh[64];
+    __shared__ __align__(8) unsigned long long bars[CHK_RING_MAX];
+    const long long a = blockIdx.x;
+    const int tid = threadIdx.x;
+    const size_t vs = (size_t)rows * (size_t)n;
+    double *vout = V + (size_t)(j + 1) * vs + (size_t)a * n;
+    if (skip && skip[a]) {  // (inside the library's GMRES nobody reads the vectors of a stopped state: no zero fill)
+        if (!G.R)
+            for (long long e = tid; e < n; e += CHK_THREADS) vout[e] = 0.0;
+        if (h && tid <= j + 1) h[(size_t)a * ldh + tid] = 0.0;
+        return;
+    }
+    if (tid < 64) sh[tid] = 0.0;
+    for (int s = 0; s < nstage; ++s)
+        for (long long e = n + tid; e < (long long)CHK_THREADS * NE; e += CHK_THREADS)
+            ((double *)chk_ring)[(size_t)s * (CHK_THREADS * NE) + e] = 0.0;  // the pad of every stage, once
+    if (tid == 0) {
+        for (int s = 0; s < nstage; ++s)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned)__cvta_generic_to_shared(&bars[s])) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const double *va = V + (size_t)a * n;  // row i of this state: va + i * vs
+    auto row_of = [&](int t) { return t == 0 ? j : t - 1; };  // basis order j, 0, 1, .., j-1
+    // a stage holds CHK_THREADS * NE doubles: the copies fill the first n, the rest is zeroed once (rows are read unpredicated)
+    auto stage = [&](int s) { return (double *)(chk_ring + (size_t)s * (sizeof(double) * CHK_THREADS * NE)); };
+    // consumer position in the ring: stage su, phase parity pu (kept incrementally: no integer division in the row loop);
+    // a consumed stage is refilled in place, and at the start of a pass the ring is empty with the producer at (su, pu) too
+    int su = 0;
+    unsigned pu = 0;
+    auto fill_ring = [&]() {  // thread 0: the first rows of a pass
+        int si = su;
+        for (int t = 0; t <= j && t < nstage; ++t) {
+            chk_ring_issue(stage(si), va + (size_t)row_of(t) * vs, rowbytes, &bars[si]);
+            if (++si == nstage) si = 0;
+        }
+    };
+    if (tid == 0) fill_ring();
+    int ph = 0, ph2 = 0;
+    double acc[NE], vc0[NE], vc1[NE];
+    const double *wr = w + (size_t)a * n;
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+        const long long e = tid + (long long)CHK_THREADS * k;
+        acc[k] = e < n ? wr[e] : 0.0;
+    }
+    double n0 = 0.0, hn = 0.0;
+    for (int pass = 0; pass < 2; ++pass) {
+        // rows are taken two at a time (one reduction barrier per pair, two independent dependency chains): inside a pair the
+        // second coefficient is computed before the first row is subtracted -- the rows are orthonormal, the difference is
+        // rounding, and the second pass below covers the rest
+        for (int t = 0; t <= j;) {
+            const bool first = pass == 0 && t == 0;           // v_j: the shift w - v_j and its norm come first, alone
+            const int nr = (first || t == j) ? 1 : 2;
+            const int s0 = su;
+            const unsigned par0 = pu;
+            if (++su == nstage) { su = 0; pu ^= 1u; }
+            const int s1 = su;
+            const unsigned par1 = pu;
+            if (nr == 2 && ++su == nstage) { su = 0; pu ^= 1u; }
+            chk_ring_wait(&bars[s0], par0);
+            const double *r0 = stage(s0);
+#pragma unroll
+            for (int k = 0; k < NE; ++k) vc0[k] = r0[tid + CHK_THREADS * k];
+            if (nr == 2) {
+                chk_ring_wait(&bars[s1], par1);
+                const double *r1 = stage(s1);
+#pragma unroll
+                for (int k = 0; k < NE; ++k) vc1[k] = r1[tid + CHK_THREADS * k];
+            } else {
+#pragma unroll
+                for (int k = 0; k < NE; ++k) vc1[k] = 0.0;
+            }
+            if (first) {
+                double pa = 0.0, pb = 0.0;
+#pragma unroll
+                for (int k = 0; k < NE; k += 2) {
+                    acc[k] -= vc0[k];
+                    pa = fma(acc[k], acc[k], pa);
+                    if (k + 1 < NE) {
+                        acc[k + 1] -= vc0[k + 1];
+                        pb = fma(acc[k + 1], acc[k + 1], pb);
+                    }
+                }
+                n0 = sqrt(chk_block_sum(pa + pb, sred, ph));
+            }
+            double p0a = 0.0, p0b = 0.0, p1a = 0.0, p1b = 0.0;
+#pragma unroll
+            for (int k = 0; k < NE; k += 2) {
+                p0a = fma(vc0[k], acc[k], p0a);
+                p1a = fma(vc1[k], acc[k], p1a);
+                if (k + 1 < NE) {
+                    p0b = fma(vc0[k + 1], acc[k + 1], p0b);
+                    p1b = fma(vc1[k + 1], acc[k + 1], p1b);
+                }
+            }
+            double h0 = p0a + p0b, h1 = p1a + p1b;
+            chk_block_sum2(h0, h1, sred2, ph2);  // its barrier: every thread has read the stage(s)
+            if (tid == 0) {
+                sh[row_of(t)] += h0;
+                if (t + nstage <= j) chk_ring_issue(stage(s0), va + (size_t)row_of(t + nstage) * vs, rowbytes, &bars[s0]);
+                if (nr == 2) {
+                    sh[row_of(t + 1)] += h1;
+                    if (t + 1 + nstage <= j)
+                        chk_ring_issue(stage(s1), va + (size_t)row_of(t + 1 + nstage) * vs, rowbytes, &bars[s1]);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < NE; ++k) acc[k] = fma(-h1, vc1[k], fma(-h0, vc0[k], acc[k]));
+            t += nr;
+        }
+        double pa = 0.0, pb = 0.0;
+#pragma unroll
+        for (int k = 0; k < NE; k += 2) {
+            pa = fma(acc[k], acc[k], pa);
+            if (k + 1 < NE) pb = fma(acc[k + 1], acc[k + 1], pb);
+        }
+        hn = sqrt(chk_block_sum(pa + pb, sred, ph));
+        if (pass == 0 && hn < 0.1 * n0) {  // second pass: stream the rows again (every stage is free)
+            if (tid == 0) fill_ring();
+            continue;
+        }
+        break;
+    }
+    const double inv = hn > 0.0 ? 1.0 / hn : 1.0;
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+        const long long e = tid + (long long)CHK_THREADS * k;
+        if (e < n) vout[e] = acc[k] * inv;
+    }
+    if (tid == 0) {
+        sh[j] += 1.0;
+        sh[j + 1] = hn;
+        if (h)
+            for (int i = 0; i <= j + 1; ++i) h[(size_t)a * ldh + i] = sh[i];
+        if (G.R) {
+            if (G.split) {
+                double *Rc = G.R + (size_t)a * (G.m + 1) * G.m + j;
+                for (int i = 0; i <= j + 1; ++i) Rc[(size_t)i * G.m] = sh[i];
+            } else {
+                chk_givens_update(G, a, j, sh);
+            }
+        }
+    }
+}
+
+// the per-state tail of the step for all states at once (see ChkGivens::split): one thread per state
+__global__ void __launch_bounds__(128)
+k_givens_tail(long long rows, int j, ChkGivens G) {
+    const long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= rows || G.done[a]) return;
+    double hcol[64];
+    const double *Rc = G.R + (size_t)a * (G.m + 1) * G.m + j;
+    for (int i = 0; i <= j + 1; ++i) hcol[i] = Rc[(size_t)i * G.m];
+    chk_givens_update(G, a, j, hcol);
 }
 
 // larger rows: the candidate vector lives in shared memory (8 n bytes), every basis row is streamed once from HBM for the dot
@@ -188,8 +411,9 @@ k_arnoldi_smem(long long rows, long long n, int j, int ldh, double *V, const dou
     const int tid = threadIdx.x;
     const size_t vs = (size_t)rows * (size_t)n;
     double *vout = V + (size_t)(j + 1) * vs + (size_t)a * n;
-    if (skip && skip[a]) {
-        for (long long e = tid; e < n; e += CHK_THREADS) vout[e] = 0.0;
+    if (skip && skip[a]) {  // (inside the library's GMRES nobody reads the vectors of a stopped state: no zero fill)
+        if (!G.R)
+            for (long long e = tid; e < n; e += CHK_THREADS) vout[e] = 0.0;
         if (h && tid <= j + 1) h[(size_t)a * ldh + tid] = 0.0;
         return;
     }
@@ -232,7 +456,14 @@ k_arnoldi_smem(long long rows, long long n, int j, int ldh, double *V, const dou
         sh[j + 1] = hn;
         if (h)
             for (int i = 0; i <= j + 1; ++i) h[(size_t)a * ldh + i] = sh[i];
-        if (G.R) chk_givens_update(G, a, j, sh);
+        if (G.R) {
+            if (G.split) {
+                double *Rc = G.R + (size_t)a * (G.m + 1) * G.m + j;
+                for (int i = 0; i <= j + 1; ++i) Rc[(size_t)i * G.m] = sh[i];
+            } else {
+                chk_givens_update(G, a, j, sh);
+            }
+        }
     }
 }
 
@@ -315,7 +546,7 @@ static void chk_arnoldi_host(long long rows, long long n, int j, int ldh, double
         hr[j + 1] = hn;
         if (h)
             for (int i = 0; i <= j + 1; ++i) h[(size_t)a * ldh + i] = hr[i];
-        if (G.R) chk_givens_update(G, a, j, hr);
+        if (G.R) chk_givens_update(G, a, j, hr);  // (the emulation always runs the tail in place)
     }
 }
 #endif

@@ -31,20 +31,21 @@ def _numpy_step(V, j, w, skip):
     return h, vnew
 
 
-def _case(A, n, j, m, seed, with_skip):
+def _case(A, n, j, m, seed, with_skip, noise=1e-2):
     rng = np.random.default_rng(seed)
     V = np.zeros((m + 1, A, n))
     for a in range(A):  # orthonormal v_0..v_j per state
         q, _ = np.linalg.qr(rng.standard_normal((n, j + 1)))
         V[:j + 1, a] = q.T
     # A v_j = v_j + small perturbation with components along the basis (what the action Hessian produces)
-    w = V[j] + 1e-2 * rng.standard_normal((A, n)) + 0.3 * V[0]
+    # (noise 1e-4: what is left after the first Gram-Schmidt pass is < 0.1 of the vector -> the second pass runs)
+    w = V[j] + noise * rng.standard_normal((A, n)) + 0.3 * V[0]
     skip = (rng.random(A) < 0.3) if with_skip else None
     return V, w, skip
 
 
-def _check(nbs, to_dev, from_dev, A, n, j, m, seed, with_skip):
-    V, w, skip = _case(A, n, j, m, seed, with_skip)
+def _check(nbs, to_dev, from_dev, A, n, j, m, seed, with_skip, noise=1e-2):
+    V, w, skip = _case(A, n, j, m, seed, with_skip, noise)
     h_ref, v_ref = _numpy_step(V, j, w, skip)
     Vd, wd, hd = to_dev(V), to_dev(w), to_dev(np.zeros((A, m + 1)))
     sd = to_dev(skip) if skip is not None else None
@@ -66,6 +67,7 @@ def test_arnoldi_step_hostsim(n, j, with_skip):
     T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
     nbs = NBodySystB200(T, 96, _lib_handle=build_hostsim.load())
     _check(nbs, lambda a: np.ascontiguousarray(a), lambda a: a, 5, n, j, 20, 11 + n, with_skip)
+    _check(nbs, lambda a: np.ascontiguousarray(a), lambda a: a, 3, n, j, 20, 12 + n, with_skip, noise=1e-4)
 
 
 def test_arnoldi_step_declines_host_arrays_on_cuda_library():
@@ -80,7 +82,7 @@ def test_arnoldi_step_declines_host_arrays_on_cuda_library():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("n,j,with_skip", [(37, 0, False), (2000, 5, True), (4100, 7, False), (6142, 19, True),
-                                           (8192, 3, True), (8193, 2, False), (24570, 4, True)])
+                                           (6142, 2, False), (8192, 3, True), (8193, 2, False), (24570, 4, True)])
 def test_arnoldi_step_gpu(n, j, with_skip):
     import torch
     T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
@@ -88,6 +90,8 @@ def test_arnoldi_step_gpu(n, j, with_skip):
     dev = torch.device("cuda:0")
     _check(nbs, lambda a: torch.as_tensor(np.ascontiguousarray(a), device=dev), lambda t: t.cpu().numpy(),
            7, n, j, 20, 5 + n, with_skip)
+    _check(nbs, lambda a: torch.as_tensor(np.ascontiguousarray(a), device=dev), lambda t: t.cpu().numpy(),
+           150, n, j, 20, 6 + n, with_skip, noise=1e-4)  # second Gram-Schmidt pass, more states than SMs
 
 
 def _masked_case(nbs, B, seed, forced):

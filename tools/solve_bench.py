@@ -42,6 +42,7 @@ def main():
     x0h = np.stack(starts)
     x0 = torch.from_numpy(x0h).cuda()
     newton_krylov_batched(nbs, x0[:8], f_tol=a.f_tol, maxiter=3)  # warm-up (plans, workspaces)
+    newton_krylov_batched(nbs, x0, f_tol=a.f_tol, maxiter=2)      # ... and the caching allocator at the full batch size
     torch.cuda.synchronize(); t0 = time.perf_counter()
     res = newton_krylov_batched(nbs, x0, f_tol=a.f_tol, maxiter=a.maxiter)
     torch.cuda.synchronize(); dt = time.perf_counter() - t0
