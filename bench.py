@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=0, help="states in the cpu_baseline sample (0 = auto)")
     ap.add_argument("--ref-sample", type=int, default=0, help="states per step of the reference arm (0 = auto)")
     ap.add_argument("--stages", action="store_true", help="also time the staged operators separately")
+    ap.add_argument("--no-newton", action="store_true", help="skip the Newton orbit solves/hour leg")
+    ap.add_argument("--newton-batch", type=int, default=8192, help="random starts per GPU in the solves/hour leg")
     return ap.parse_args()
 
 
@@ -370,6 +372,42 @@ def run_b200(args):
                       "3-slot stream pipeline of 48 MB slices (H2D, kernels, D2H overlapped)"}
         assert abs(float(a_h.sum()) - checksum) <= 1e-9 * abs(checksum)
 
+    # ---- second half of the metric: Newton orbit solves/hour ----------------------------------------------------------
+    # every rank solves its own shard of find.py-style random starts (seeded by global index) of the 3C system at nint 3072
+    # with the batched Newton-Krylov driver (GMRES(20) + Armijo, the reference's settings); no collective on the path
+    newton = None
+    if not args.no_newton:
+        try:
+            from choreographies2_b200.newton import newton_krylov_batched
+            Tn = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+            n_nint, Bn = 3072, int(args.newton_batch)
+            nbs_n = NBodySystB200(Tn, n_nint, device=dev.index)
+            x_min, x_max = Tn.make_params_bounds(n_nint, 0.1, 3, 50, 1e-16)
+            starts = np.empty((Bn, nbs_n.nparams))
+            for i in range(Bn):  # find.py:105-108,158: np.random.seed(seed); x = x_min + x_ptp * U[0, 1)
+                np.random.seed(rank * Bn + i)
+                starts[i] = x_min + (x_max - x_min) * np.random.random(nbs_n.nparams)
+            x0n = torch.from_numpy(starts).to(dev)
+            newton_krylov_batched(nbs_n, x0n, f_tol=1e-9, maxiter=2)  # warm-up: plan, workspaces, caching allocator
+            barrier()
+            l0 = nbs_n.kernel_launches
+            t0 = time.perf_counter()
+            res = newton_krylov_batched(nbs_n, x0n, f_tol=1e-9, maxiter=60)
+            torch.cuda.synchronize()
+            dtn = max_over_ranks(time.perf_counter() - t0)
+            newton = {"solves_per_hour": world * Bn / dtn * 3600.0, "seconds": dtn, "batch_per_gpu": Bn, "system": "3C",
+                      "nint": n_nint, "nparams": int(nbs_n.nparams),
+                      "settings": "f_tol 1e-9 (max norm), <= 60 Newton iterations, GMRES(20), Armijo smin 1e-2, "
+                                  "starts x_min + (x_max - x_min) U[0,1) from Make_params_bounds(0.1, 3, 50, 1e-16)",
+                      "rank0": {"converged": int((res.status == 1).sum()), "iteration_limit": int((res.status == 2).sum()),
+                                "non_finite": int((res.status == 3).sum()), "U1_evals": int(res.n_grad_evals),
+                                "U2_evals": int(res.n_hess_evals), "gpu_launches": int(nbs_n.kernel_launches - l0)},
+                      "note": "a solve = one run from one random start to termination; reference solver on one host core: "
+                              "profiles/r01_solves_*.json (about 1.0e5 solves/hour per process)"}
+            del nbs_n, x0n, res
+        except Exception as exc:  # the first half of the metric stands on its own
+            newton = {"error": f"{type(exc).__name__}: {exc}"}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(args, npar)
@@ -387,6 +425,8 @@ def run_b200(args):
         }
         if stages:
             line["stages"] = stages
+        if newton is not None:
+            line["newton"] = newton
         print(json.dumps(line))
     return 0
 
