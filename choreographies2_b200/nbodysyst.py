@@ -440,6 +440,87 @@ class NBodySystB200:
                                                         ptr(live_count_next) if live_count_next is not None else None, stream))
         return True
 
+    # ------------------------------------------------------------------ post-solve reductions (find.py:285-308, 376-380)
+    def _body_tables(self, like):
+        T = self.tables
+        if T.bodysegm is None:
+            raise ValueError("these tables carry no per-body symmetries (bodysegm / body_spacerot / body_timerev): "
+                             "re-extract them with extract_tables from a live NBodySyst")
+        mass = T.loopmass[T.bodyloop]
+        if _is_torch(like):
+            import torch
+            key = ("body", str(like.device))
+            if getattr(self, "_body_cache", None) is None or self._body_cache[0] != key:
+                self._body_cache = (key, tuple(torch.as_tensor(np.ascontiguousarray(a), device=like.device)
+                                               for a in (T.bodysegm, T.body_spacerot, T.body_timerev, mass)))
+            return self._body_cache[1]
+        return T.bodysegm, T.body_spacerot, T.body_timerev, mass
+
+    def ComputeCenterOfMass(self, segmpos):
+        """_NBodySyst.pyx:3968-4009, batched: mass-weighted mean position over all bodies and the whole period, from the stored
+        segments and the symmetry that carries each body onto them.  ``[..., nsegm, segm_store, geodim] -> [..., geodim]``."""
+        self._check(segmpos, self.segmpos_shape, "segmpos")
+        bodysegm, rot, trev, mass = self._body_tables(segmpos)
+        n = self.segm_size
+        s_fwd = segmpos[..., :, 0:n, :].sum(-2)                     # TimeRev > 0: samples 0 .. segm_size-1
+        if (self.tables.body_timerev < 0).any():
+            if self.segm_store <= n:
+                raise ValueError("ComputeCenterOfMass: a time-reversed body segment needs segm_store = segm_size + 1")
+            s_rev = s_fwd - segmpos[..., :, 0, :] + segmpos[..., :, n, :]   # TimeRev < 0: samples 1 .. segm_size
+        else:
+            s_rev = s_fwd
+        tot = None
+        for ib in range(self.tables.nbody):
+            for ii in range(self.tables.nint_min):
+                src = s_fwd if int(self.tables.body_timerev[ib, ii]) > 0 else s_rev
+                v = src[..., int(self.tables.bodysegm[ib, ii]), :] @ rot[ib, ii].T * float(self.tables.loopmass[self.tables.bodyloop[ib]])
+                tot = v if tot is None else tot + v
+        totmass = float(self.tables.loopmass[self.tables.bodyloop].sum()) * self.tables.nint_min
+        return tot / (n * totmass)
+
+    def DetectEscape(self, segmpos, fac: float = 2.):
+        """_NBodySyst.pyx:2125-2192, batched: per body the box spanned by the rotated min / max corners of its segments, an edge
+        between two bodies whose box centres are closer than ``fac`` times the sum of the box diagonals; escaped = that graph
+        is not connected.  Returns a bool (one state) or a NumPy bool array over the leading dimensions."""
+        batch, lead = self._check(segmpos, self.segmpos_shape, "segmpos")
+        bodysegm, rot, trev, mass = self._body_tables(segmpos)
+        torch_in = _is_torch(segmpos)
+        lo_s = segmpos.amin(-2) if torch_in else segmpos.min(-2)    # [..., nsegm, G]
+        hi_s = segmpos.amax(-2) if torch_in else segmpos.max(-2)
+        nb = self.tables.nbody
+        mids, sizes = [], []
+        for ib in range(nb):
+            pts = []
+            for ii in range(self.tables.nint_min):
+                k = int(self.tables.bodysegm[ib, ii])
+                pts.append(lo_s[..., k, :] @ rot[ib, ii].T)
+                pts.append(hi_s[..., k, :] @ rot[ib, ii].T)
+            if torch_in:
+                import torch
+                P = torch.stack(pts, -2)
+                lo, hi = P.amin(-2), P.amax(-2)
+                sizes.append(((hi - lo) ** 2).sum(-1).sqrt())
+            else:
+                P = np.stack(pts, -2)
+                lo, hi = P.min(-2), P.max(-2)
+                sizes.append(np.sqrt(((hi - lo) ** 2).sum(-1)))
+            mids.append((hi + lo) / 2)
+        if torch_in:
+            import torch
+            M, S = torch.stack(mids, -2), torch.stack(sizes, -1)    # [..., nb, G], [..., nb]
+            D = ((M[..., :, None, :] - M[..., None, :, :]) ** 2).sum(-1).sqrt()
+            adj = (D < fac * (S[..., :, None] + S[..., None, :])).cpu().numpy()
+        else:
+            M, S = np.stack(mids, -2), np.stack(sizes, -1)
+            D = np.sqrt(((M[..., :, None, :] - M[..., None, :, :]) ** 2).sum(-1))
+            adj = D < fac * (S[..., :, None] + S[..., None, :])
+        reach = adj | np.eye(nb, dtype=bool)
+        for _ in range(max(1, int(np.ceil(np.log2(max(nb, 2)))))):  # transitive closure by repeated squaring
+            r = reach.astype(np.int32)
+            reach = (r @ r) > 0
+        escaped = ~reach[..., 0, :].all(-1)
+        return bool(escaped) if escaped.ndim == 0 else escaped
+
     def TestHashSame(self, Hash_a, Hash_b, rtol: float = 1e-5, detect_multiples: bool = True) -> bool:
         """_NBodySyst.pyx:2036-2067.  For a homogeneous law (gravity / power law: Homo_exp = n) two orbits that differ by a
         rescaling have hashes whose ratios follow a power law; otherwise the hashes must agree entry by entry."""

@@ -17,7 +17,7 @@ from __future__ import annotations
 import dataclasses
 import io
 import os
-from typing import Any, Dict, List, Tuple
+from typing import Optional, Any, Dict, List, Tuple
 
 import numpy as np
 
@@ -93,6 +93,12 @@ class PlanTables:
     bin_spacerot: np.ndarray  # [nbin, G, G]
     bin_spacerot_isid: np.ndarray
     bin_prodchargesum: np.ndarray
+    # per (body, interval of the period): which stored segment the body runs on and the symmetry that maps it there
+    # (``_bodysegm`` and ``intersegm_to_all[ib][iint]``) -- only the post-solve reductions (centre of mass, escape test) use
+    # them; optional so that older table files keep loading
+    bodysegm: Optional[np.ndarray] = None       # [nbody, nint_min]
+    body_spacerot: Optional[np.ndarray] = None  # [nbody, nint_min, G, G]
+    body_timerev: Optional[np.ndarray] = None   # [nbody, nint_min]
 
     # ------------------------------------------------------------------ helpers
     def __post_init__(self) -> None:
@@ -111,6 +117,10 @@ class PlanTables:
         self.alg_spacerot = self.alg_spacerot.reshape(self.nloop, G, G)
         self.inter_spacerot = self.inter_spacerot.reshape(self.nsegm, G, G)
         self.bin_spacerot = self.bin_spacerot.reshape(self.nbin, G, G)
+        if self.bodysegm is not None:
+            self.bodysegm = c(self.bodysegm, dtype=_INT).reshape(self.nbody, self.nint_min)
+            self.body_timerev = c(self.body_timerev, dtype=_INT).reshape(self.nbody, self.nint_min)
+            self.body_spacerot = c(self.body_spacerot, dtype=_F64).reshape(self.nbody, self.nint_min, G, G)
 
     def segm_loop(self) -> np.ndarray:
         """Loop index of every generating segment (BodyLoop[gensegm_to_body], _NBodySyst.pyx:5774-5776)."""
@@ -220,6 +230,8 @@ class PlanTables:
         out: Dict[str, np.ndarray] = {}
         for f in dataclasses.fields(self):
             v = getattr(self, f.name)
+            if v is None:
+                continue
             out[f.name] = np.asarray(int(v)) if f.name in self._SCALARS else np.asarray(v)
         return out
 
@@ -227,6 +239,8 @@ class PlanTables:
     def from_dict(cls, d: Dict[str, Any], prefix: str = "") -> "PlanTables":
         kw = {}
         for f in dataclasses.fields(cls):
+            if f.default is None and (prefix + f.name) not in d:
+                continue
             v = d[prefix + f.name]
             if f.name in cls._SCALARS:
                 v = int(np.asarray(v))
@@ -319,6 +333,11 @@ def extract_tables(NBS) -> PlanTables:
         params_basis=cat(basis_list, _C128), params_basis_shifts=shifts(basis_list),
         alg_iint=np.asarray(NBS.ALG_Iint), alg_timerev=np.asarray(NBS.ALG_TimeRev), alg_spacerot=alg_rot,
         bodyloop=np.asarray(NBS.bodyloop),
+        bodysegm=np.asarray(NBS.bodysegm, dtype=_INT),
+        body_spacerot=np.array([[np.asarray(NBS.intersegm_to_all[ib][ii].SpaceRot) for ii in range(nint_min)]
+                                for ib in range(int(NBS.nbody))]),
+        body_timerev=np.array([[int(NBS.intersegm_to_all[ib][ii].TimeRev) for ii in range(nint_min)]
+                               for ib in range(int(NBS.nbody))], dtype=_INT),
         gensegm_to_body=gensegm_to_body, gensegm_to_iintrel=np.asarray(NBS.gensegm_to_iintrel),
         inter_timerev=inter_tr, inter_spacerot=inter_rot, inter_spacerot_isid=inter_isid,
         bin_source=np.asarray(NBS.BinSourceSegm), bin_target=np.asarray(NBS.BinTargetSegm),
