@@ -7,9 +7,10 @@ per state -- with the reference's own tests -- whether it is a solution, an appr
 collision, or has to be re-converged at the finer level.  States that continue are compacted and solved together at the next
 level; every level has its own plan (``NBodySystB200``), built once and cached.
 
-Not restated here (host-side bookkeeping of the reference that does not touch the numerics): the duplicate search against the
-store folder, escape detection, descriptors / images written per solution, the list of optimiser parameter sets (this driver
-runs the single-set case, ``n_optim_param = 1``).
+Escape detection (find.py:290-297) and the re-centering of saved solutions on their centre of mass (find.py:376-380) are
+included.  Not restated here (host-side bookkeeping of the reference that does not touch the numerics): the duplicate search
+against the store folder (``segmpos_to_hash`` + ``TestHashSame`` are the pieces), descriptors / images written per solution,
+the list of optimiser parameter sets (this driver runs the single-set case, ``n_optim_param = 1``).
 """
 from __future__ import annotations
 
@@ -21,10 +22,11 @@ import numpy as np
 from .newton import _XP, newton_krylov_batched
 
 # per-state outcome codes
-FOUND, APPROX, NOT_CONVERGED, COLLISION, TOO_BIG_ON_ENTRY = 1, 2, 3, 4, 5
+FOUND, APPROX, NOT_CONVERGED, COLLISION, TOO_BIG_ON_ENTRY, ESCAPED = 1, 2, 3, 4, 5, 6
 OUTCOME = {FOUND: "found solution", APPROX: "found approximate solution",
            NOT_CONVERGED: "could not converge within prescribed optimizer and refinement parameters",
-           COLLISION: "likely narrowing in on a collision solution", TOO_BIG_ON_ENTRY: "norm on entry too big"}
+           COLLISION: "likely narrowing in on a collision solution", TOO_BIG_ON_ENTRY: "norm on entry too big",
+           ESCAPED: "one loop escaped"}
 
 
 @dataclass
@@ -43,7 +45,8 @@ class RefineResult:
 def find_batched(make_nbs: Callable[[int], Any], x0, nint0: int, *, gradtol: float = 1e-11, maxiter: int = 50,
                  n_reconverge_it_max: int = 4, Newt_err_norm_max: float = 1e-10, Newt_err_norm_max_save: float = 1e-7,
                  mul_coarse_to_fine: float = 3.0, max_norm_on_entry: float = 1e20, linesearch_smin: float = 1e-2,
-                 line_search: Optional[str] = "armijo", restart: int = 20) -> RefineResult:
+                 line_search: Optional[str] = "armijo", restart: int = 20, Check_Escape: bool = True,
+                 recenter: bool = True) -> RefineResult:
     """``make_nbs(nint)`` returns the evaluator of one level (called once per level); ``x0`` ``[B, nparams(nint0)]`` NumPy
     array or torch CUDA tensor.  Keyword names and defaults follow the reference's ``Find_Choreo`` arguments."""
     xp = _XP(x0)
@@ -102,6 +105,10 @@ def find_batched(make_nbs: Callable[[int], Any], x0, nint0: int, *, gradtol: flo
         collision = (fn < 1e3 * Newt_err_norm_max) & (ff > 1e6 * fn)
         out = np.zeros(ids.size, dtype=np.int64)
         go = np.ones(ids.size, dtype=bool)
+        body_tables = getattr(nbs.tables, "bodysegm", None) is not None
+        if Check_Escape and body_tables:  # find.py:290-297: an escaped loop ends the attempt before anything else is looked at
+            esc = np.asarray(nbs.DetectEscape(nbs.params_to_segmpos(best_x))).reshape(-1)
+            out[esc], go = ESCAPED, go & ~esc
         hit = go & precise & ~needs_ref
         out[hit], go = FOUND, go & ~hit
         hit = go & precise_save & (~needs_ref | (not can_refine))
@@ -114,6 +121,12 @@ def find_batched(make_nbs: Callable[[int], Any], x0, nint0: int, *, gradtol: flo
         sid = ids[stop]
         outcome[sid], level[sid], nint_out[sid] = out[stop], lvl, nint
         f_norm[sid], f_fine_norm[sid] = fn[stop], ff[stop]
+        saved = np.nonzero(stop & ((out == FOUND) | (out == APPROX)))[0]
+        if recenter and body_tables and saved.size > 0:  # find.py:376-380: saved solutions are centred on their centre of mass
+            sel = xp.from_numpy_index(saved)
+            seg = nbs.params_to_segmpos(best_x[sel])
+            seg = seg - nbs.ComputeCenterOfMass(seg)[:, None, None, :]
+            best_x[sel] = nbs.segmpos_to_params(seg)
         for k in np.nonzero(stop)[0]:
             params[ids[k]] = best_x[int(k)]
         # re-converge the others at the finer level, starting from the resized best iterate (find.py:426-432)

@@ -74,14 +74,19 @@ def _reference_find(NBS, x0, nint_fac0, gradtol, maxiter, n_reconverge_it_max, e
         f_fine = NBS.params_to_action_grad(x_fine)
         ff = np.linalg.norm(f_fine)
         NBS.nint_fac = fac
+        segmpos = NBS.params_to_segmpos(best.x)
+        if NBS.DetectEscape(segmpos):
+            return refine.ESCAPED, lvl, best.f_norm, ff, best.x
         precise, precise_save = ff < err_max, ff < err_save
         can_refine = lvl < n_reconverge_it_max
         needs_ref = (ff > mul_c2f * best.f_norm) and (ff > precise_save)
         collision = (best.f_norm < 1e3 * err_max) and (ff > 1e6 * best.f_norm)
-        if precise and not needs_ref:
-            return refine.FOUND, lvl, best.f_norm, ff, best.x
-        if precise_save and (not can_refine or not needs_ref):
-            return refine.APPROX, lvl, best.f_norm, ff, best.x
+        if (precise and not needs_ref) or (precise_save and (not can_refine or not needs_ref)):
+            xo = NBS.ComputeCenterOfMass(segmpos)  # find.py:376-380
+            for idim in range(NBS.geodim):
+                segmpos[:, :, idim] -= xo[idim]
+            xs = NBS.segmpos_to_params(segmpos)
+            return (refine.FOUND if (precise and not needs_ref) else refine.APPROX), lvl, best.f_norm, ff, xs
         if not can_refine or not needs_ref:
             return refine.NOT_CONVERGED, lvl, best.f_norm, ff, best.x
         if collision:
@@ -128,7 +133,11 @@ def test_find_batched_matches_reference_outer_loop(sim):
             NBS.nint_fac = fac0 * 2 ** lvl
             a_ref, a_got = NBS.params_to_action(np.asarray(xb)), NBS.params_to_action(np.ascontiguousarray(res.params[i]))
             assert abs(a_ref - a_got) < 1e-7 * abs(a_ref)
+            com = NBS.ComputeCenterOfMass(NBS.params_to_segmpos(np.ascontiguousarray(res.params[i])))
+            assert np.abs(com).max() < 1e-12  # saved solutions are centred
             nsame += 1
+        elif out == refine.ESCAPED:
+            assert res.outcome[i] == refine.ESCAPED and res.level[i] == lvl
         else:
             assert res.outcome[i] not in (0,)
     assert nsame >= 2
