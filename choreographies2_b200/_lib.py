@@ -72,6 +72,7 @@ SYMBOLS = {
     "chb_segmpos_to_pot_nrg_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),
     "chb_segmpos_to_hash_dev": (C.c_int, _dev_op + [_vp, C.c_double, _vp, _vp, _sz, _vp]),
     "chb_arnoldi_step_dev": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
+    "chb_row_stats_dev": (C.c_int, [_vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp]),
     "chb_gmres_solution_dev": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp]),
     "chb_segmpos_dparams_to_action_hess_masked_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "chb_gmres_step_dev": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

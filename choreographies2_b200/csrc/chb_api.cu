@@ -1469,7 +1469,7 @@ CHB_KERNEL void CHF_BOUNDS k_fused4(ChfSys F, ChfArgs A) {
 #ifndef CHB_HOSTSIM
 #define CHB_LAUNCH(p, kern, grid, block, smem, stream, ...)                                                  \
     do {                                                                                                     \
-        if ((smem) > 48 * 1024) {                                                                            \
+        if ((smem) > 32 * 1024) { /* static shared memory counts towards the 48 KB default limit too */    \
             CHB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); \
         }                                                                                                    \
         kern<<<(unsigned)(grid), (unsigned)(block), (smem), (stream)>>>(__VA_ARGS__);                       \
@@ -1961,6 +1961,24 @@ extern "C" int chb_segmpos_dparams_to_action_hess_listed_dev(chb_plan *p, int64_
                                                              double *hess, void *ws, size_t ws_bytes, void *stream) {
     CHB_REQUIRE(live_list && live_count, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_dparams_to_action_hess_listed_dev: NULL list");
     return hess_common(p, batch, segmpos, dparams, nullptr, live_list, live_count, hess, ws, ws_bytes, stream);
+}
+
+// per-row sum of squares and max |.| of a [batch][n] array in one pass (norms of the Newton driver)
+extern "C" int chb_row_stats_dev(chb_plan *p, int64_t batch, int64_t n, const double *a, double *sumsq, double *maxabs,
+                                 void *stream) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_row_stats_dev: NULL plan");
+    CHB_REQUIRE(batch >= 0 && n >= 1, CHB_ERR_INVALID_ARGUMENT, "chb_row_stats_dev: need batch >= 0, n >= 1");
+    if (batch == 0) return CHB_OK;
+    CHB_REQUIRE(a && sumsq, CHB_ERR_INVALID_ARGUMENT, "chb_row_stats_dev: NULL array");
+    CHB_SET_DEVICE();
+#ifndef CHB_HOSTSIM
+    CHB_LAUNCH(p, k_row_stats, batch, 256, 0, (chb_stream_t)stream, (long long)n, a, sumsq, maxabs);
+#else
+    (void)stream;
+    chk_row_stats_host(batch, n, a, sumsq, maxabs);
+    p->launches++;
+#endif
+    return CHB_OK;
 }
 
 // End of a GMRES cycle for every state: back substitution on the state's own kdone x kdone triangle of R, then

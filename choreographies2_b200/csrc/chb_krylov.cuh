@@ -388,6 +388,48 @@ k_arnoldi_ring(long long rows, long long n, int j, int ldh, double *V, const dou
     }
 }
 
+// per-row sum of squares and max |.| in one pass (the norms of the Newton driver: 2-norm of the gradient for the forcing terms
+// and the line search, max norm for the termination test; a non-finite entry makes the sum non-finite).  One CTA per row,
+// fixed reduction order: a row's result does not depend on the batch it is in.
+__global__ void __launch_bounds__(256)
+k_row_stats(long long n, const double *a, double *sumsq, double *maxabs) {
+    __shared__ double s1[8], s2[8];
+    const double *r = a + (size_t)blockIdx.x * n;
+    double p0 = 0.0, p1 = 0.0, m = 0.0;
+    long long e = threadIdx.x;
+    for (; e + 256 < n; e += 512) {
+        const double x = r[e], y = r[e + 256];
+        p0 = fma(x, x, p0);
+        p1 = fma(y, y, p1);
+        m = fmax(m, fmax(fabs(x), fabs(y)));
+    }
+    if (e < n) {
+        const double x = r[e];
+        p0 = fma(x, x, p0);
+        m = fmax(m, fabs(x));
+    }
+    double p = p0 + p1;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        p += __shfl_xor_sync(0xffffffffu, p, o);
+        m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        s1[threadIdx.x >> 5] = p;
+        s2[threadIdx.x >> 5] = m;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double ps = 0.0, ms = 0.0;
+        for (int k = 0; k < 8; ++k) {
+            ps += s1[k];
+            ms = fmax(ms, s2[k]);
+        }
+        sumsq[blockIdx.x] = ps;
+        if (maxabs) maxabs[blockIdx.x] = ms;
+    }
+}
+
 // the per-state tail of the step for all states at once (see ChkGivens::split): one thread per state
 __global__ void __launch_bounds__(128)
 k_givens_tail(long long rows, int j, ChkGivens G) {
@@ -499,6 +541,18 @@ static void chk_solution_host(long long rows, long long n, int m, const double *
             for (int j = 0; j < k; ++j) s += y[j] * V[(size_t)j * vs + (size_t)a * n + e];
             sol[(size_t)a * n + e] = scale * s;
         }
+    }
+}
+static void chk_row_stats_host(long long rows, long long n, const double *a, double *sumsq, double *maxabs) {
+    for (long long b = 0; b < rows; ++b) {
+        double p = 0.0, m = 0.0;
+        for (long long e = 0; e < n; ++e) {
+            const double x = a[(size_t)b * n + e];
+            p += x * x;
+            m = std::fmax(m, std::fabs(x));
+        }
+        sumsq[b] = p;
+        if (maxabs) maxabs[b] = m;
     }
 }
 // host emulation (tests/hostsim): the same arithmetic, one state after the other

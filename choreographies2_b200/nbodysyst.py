@@ -381,6 +381,24 @@ class NBodySystB200:
             self._plan, b, ptr(segmpos), ptr(dparams), ptr(live_list), ptr(live_count), ptr(out), wsp, wsn, stream))
         return True
 
+    def row_stats(self, a):
+        """(sum of squares, max |.|) of every row of ``a`` ``[batch, n]`` in one pass (``chb_row_stats_dev``), or None when
+        the library cannot address the array."""
+        if not self._direct_ok(a):
+            return None
+        b, n = int(a.shape[0]), int(a.shape[1])
+        ptr, stream = self._ptr_stream(a)
+        if _is_torch(a):
+            import torch
+            a = a.contiguous()
+            ss = torch.empty((b,), dtype=torch.float64, device=a.device)
+            mx = torch.empty((b,), dtype=torch.float64, device=a.device)
+        else:
+            a = np.ascontiguousarray(a, dtype=np.float64)
+            ss, mx = np.empty((b,)), np.empty((b,))
+        L.check(self._lib, self._lib.chb_row_stats_dev(self._plan, b, n, ptr(a), ptr(ss), ptr(mx), stream))
+        return ss, mx
+
     def gmres_solution(self, V, R, g, kdone, scale: float, out) -> bool:
         """``out[b] = scale * sum_(j < kdone[b]) y_j V[j, b]`` with ``y`` from the back substitution on the state's triangle
         of ``R`` (``chb_gmres_solution_dev``).  Returns False when the library cannot address the arrays."""

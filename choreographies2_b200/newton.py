@@ -81,6 +81,12 @@ class _XP:
     def any(self, m) -> bool:
         return bool(m.any())
 
+    def isfinite(self, a):
+        return self.t.isfinite(a) if self.torch else np.isfinite(a)
+
+    def axpy(self, x, alpha, d):  # x + alpha[:, None] * d in one pass
+        return self.t.addcmul(x, alpha[:, None], d) if self.torch else x + alpha[:, None] * d
+
     def isfinite_rows(self, a):
         return self.t.isfinite(a).all(-1) if self.torch else np.isfinite(a).all(-1)
 
@@ -294,9 +300,21 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search, 
         n_grad += int(xs.shape[0])
         return nbs.params_to_action_grad(xs)
 
+    row_stats = getattr(nbs, "row_stats", None) if lib_gmres else None
+
+    def stats(F):
+        """(sum of squares, max |.|) per row; a row with a non-finite entry has a non-finite sum (so does a row whose squares
+        overflow: such a state is reported as non-finite, status 3)."""
+        r = row_stats(F) if row_stats is not None else None
+        if r is None:
+            ss = xp.dot(F, F)
+            return xp.where(xp.isfinite_rows(F), ss, ss * 0 + float("inf")), xp.maxabs(F)
+        return r
+
     Fx = func(None, x)
-    Fnorm = xp.norm(Fx)
-    tnorm = (lambda F, F2: F2) if tol_norm == "l2" else (lambda F, F2: xp.maxabs(F))  # F2: the 2-norm, kept up to date
+    ss0, Fmax = stats(Fx)
+    Fnorm = xp.sqrt(ss0)
+    tnorm = (lambda: Fnorm) if tol_norm == "l2" else (lambda: Fmax)  # both norms of Fx are kept up to date
     if track_best:
         best_x, best_n = xp.copy(x), xp.where(Fnorm == Fnorm, Fnorm, Fnorm * 0 + 1e100)
     eta = xp.full((B,), 1e-3)
@@ -304,9 +322,9 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search, 
     status = xp.zeros((B,), "i8")
     nit = xp.zeros((B,), "i8")
     for _ in range(int(maxiter)):
-        bad = ~xp.isfinite_rows(Fx)
+        bad = ~xp.isfinite(Fnorm)
         status = xp.where((status == 0) & bad, status * 0 + 3, status)
-        conv = (status == 0) & (tnorm(Fx, Fnorm) <= f_tol)
+        conv = (status == 0) & (tnorm() <= f_tol)
         status = xp.where(conv, status * 0 + 1, status)
         act = xp.nonzero(status == 0)
         na = int(act.shape[0])
@@ -335,7 +353,7 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search, 
         phi0 = Fna * Fna
         if line_search is None:
             s_fin = xp.full((na,), smin)
-            F_fin = func(None, xa + s_fin[:, None] * dx)
+            F_fin = func(None, xp.axpy(xa, s_fin, dx))
         else:
             c1 = 1e-4
             s_fin = xp.full((na,), smin)
@@ -363,9 +381,9 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search, 
                     alpha = (-cb + xp.sqrt(xp.abs(cb * cb + 3.0 * ca * phi0))) / (3.0 * ca)
                 sub_all = int(ids.shape[0]) == na
                 al = alpha if sub_all else alpha[ids]
-                Ft = func(None, (xa if sub_all else xa[ids]) + al[:, None] * (dx if sub_all else dx[ids]))
-                fin = xp.isfinite_rows(Ft)
-                pt = xp.where(fin, xp.dot(Ft, Ft), al * 0 + float("inf"))  # _safe_norm_pp
+                Ft = func(None, xp.axpy(xa if sub_all else xa[ids], al, dx if sub_all else dx[ids]))
+                sst, _ = stats(Ft)
+                pt = xp.where(xp.isfinite(sst), sst, al * 0 + float("inf"))  # _safe_norm_pp
                 ph0 = phi0 if sub_all else phi0[ids]
                 ok = pt <= ph0 - c1 * al * ph0
                 if sub_all:
@@ -396,29 +414,30 @@ def _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search, 
                     search = search & (a1 > smin)  # while alpha1 > amin (the failed ones fall back to s = smin)
             miss = xp.nonzero(~have)
             if int(miss.shape[0]) > 0:
-                F_fin[miss] = func(None, xa[miss] + s_fin[miss][:, None] * dx[miss])
-        xn = xa + s_fin[:, None] * dx
-        Fn_new = xp.norm(F_fin)
+                F_fin[miss] = func(None, xp.axpy(xa[miss], s_fin[miss], dx[miss]))
+        xn = xp.axpy(xa, s_fin, dx)
+        ssn, Fmax_new = stats(F_fin)
+        Fn_new = xp.sqrt(ssn)
         # forcing terms (nonlin.py:146-151)
         eta_A = gamma * (Fn_new / Fna) ** 2
         low = gamma * etaa * etaa < eta_threshold
         eta_new = xp.where(low, xp.minimum(eta_A * 0 + eta_max, eta_A),
                            xp.minimum(eta_A * 0 + eta_max, xp.maximum(eta_A, gamma * etaa * etaa)))
         if allact:
-            x, Fx, Fnorm, eta = xn, F_fin, Fn_new, eta_new
+            x, Fx, Fnorm, Fmax, eta = xn, F_fin, Fn_new, Fmax_new, eta_new
             nit = nit + 1
         else:
-            x[act], Fx[act], Fnorm[act], eta[act] = xn, F_fin, Fn_new, eta_new
+            x[act], Fx[act], Fnorm[act], Fmax[act], eta[act] = xn, F_fin, Fn_new, Fmax_new, eta_new
             nit[act] = nit[act] + 1
         if track_best:  # current_best.update after every iteration (the callback of find.py:249-257)
             better = Fnorm < best_n
             best_x = xp.where(better[:, None], x, best_x)
             best_n = xp.where(better, Fnorm, best_n)
     else:
-        conv = (status == 0) & (tnorm(Fx, Fnorm) <= f_tol)
+        conv = (status == 0) & (tnorm() <= f_tol)
         status = xp.where(conv, status * 0 + 1, status)
     status = xp.where(status == 0, status * 0 + 2, status)
     n_hess += sum(int(v) for v in n_hess_lazy)
-    return NewtonResult(x=x, status=xp.to_numpy(status), nit=xp.to_numpy(nit), fnorm=xp.to_numpy(xp.maxabs(Fx)),
+    return NewtonResult(x=x, status=xp.to_numpy(status), nit=xp.to_numpy(nit), fnorm=xp.to_numpy(Fmax),
                         n_grad_evals=n_grad, n_hess_evals=n_hess,
                         best_x=best_x if track_best else None, best_fnorm=best_n if track_best else None)

@@ -183,6 +183,10 @@ int chb_arnoldi_step_dev(chb_plan *plan, int64_t batch, int64_t n, int j, int ld
 int chb_gmres_step_dev(chb_plan *plan, int64_t batch, int64_t n, int j, int m, double *V, const double *w,
                        unsigned char *done, double *R, double *g, double *cs, const double *target, int64_t *kdone,
                        int *live_list_next, int *live_count_next, void *stream);
+/* Norms of the Newton driver in one pass over a [batch][n] array: sumsq[b] = sum_e a[b][e]^2 (non-finite when the row has a
+ * non-finite entry), maxabs[b] = max_e |a[b][e]| (may be NULL).  nonlin_solve_pp uses the 2-norm for the forcing terms and the
+ * line search (nonlin.py:98,146; _safe_norm_pp) and tol_norm for the termination test (:77-78). */
+int chb_row_stats_dev(chb_plan *plan, int64_t batch, int64_t n, const double *a, double *sumsq, double *maxabs, void *stream);
 /* End of a GMRES cycle, all states in one launch: back substitution on each state's kdone x kdone triangle of R and
  * sol[b] = scale * sum_(j < kdone[b]) y_j V[j][b]  (scipy.sparse.linalg.gmres: solve_triangular + x += V^T y). */
 int chb_gmres_solution_dev(chb_plan *plan, int64_t batch, int64_t n, int m, const double *V, const double *R,

@@ -82,7 +82,7 @@ def test_arnoldi_step_declines_host_arrays_on_cuda_library():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("n,j,with_skip", [(37, 0, False), (2000, 5, True), (4100, 7, False), (6142, 19, True),
-                                           (6142, 2, False), (8192, 3, True), (8193, 2, False), (24570, 4, True)])
+                                           (6142, 2, False), (1534, 2, False), (8192, 3, True), (8193, 2, False), (24570, 4, True)])
 def test_arnoldi_step_gpu(n, j, with_skip):
     import torch
     T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
@@ -211,3 +211,41 @@ def test_gmres_solution_gpu():
         k = kdone[a]
         y = np.linalg.solve(R[a, :k, :k], g[a, :k]) if k else np.zeros(0)
         assert np.abs(got[a] - y @ V[:k, a]).max() < 1e-9 * max(1.0, np.abs(y).max(initial=0.0))
+
+
+def _row_stats_case():
+    rng = np.random.default_rng(9)
+    a = rng.standard_normal((7, 1531)) * np.logspace(-3, 3, 7)[:, None]
+    a[2, 17] = np.nan
+    a[4, 1530] = np.inf
+    a[5, :] = 0.0
+    return a
+
+
+def _check_row_stats(ss, mx, a):
+    ok = [0, 1, 3, 5, 6]
+    assert np.allclose(ss[ok], (a[ok] ** 2).sum(-1), rtol=1e-13, atol=0)
+    assert np.array_equal(mx[ok], np.abs(a[ok]).max(-1))
+    assert not np.isfinite(ss[2]) and not np.isfinite(ss[4])
+
+
+def test_row_stats_hostsim():
+    from hostsim import build_hostsim
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nbs = NBodySystB200(T, 96, _lib_handle=build_hostsim.load())
+    a = _row_stats_case()
+    ss, mx = nbs.row_stats(a)
+    _check_row_stats(ss, mx, a)
+
+
+@pytest.mark.gpu
+def test_row_stats_gpu():
+    import torch
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nbs = NBodySystB200(T, 96)
+    a = _row_stats_case()
+    ss, mx = nbs.row_stats(torch.from_numpy(a).cuda())
+    _check_row_stats(ss.cpu().numpy(), mx.cpu().numpy(), a)
+    # a row's result does not depend on the batch it is in
+    ss1, mx1 = nbs.row_stats(torch.from_numpy(a[3:4]).cuda())
+    assert ss1.item() == ss[3].item() and mx1.item() == mx[3].item()
