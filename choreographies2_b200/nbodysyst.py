@@ -539,6 +539,39 @@ class NBodySystB200:
         escaped = ~reach[..., 0, :].all(-1)
         return bool(escaped) if escaped.ndim == 0 else escaped
 
+    def segm_to_path_stats(self, segmpos, segmvel):
+        """_NBodySyst.pyx:3903-3943 (cdef :7420-7529), batched: length of every loop (trapezoid rule on ``|v|`` when the
+        segments store their end point, plain sum otherwise) and the minimum distance of every binary interaction over the
+        stored samples.  ``segmvel`` has the shape of ``segmpos``.  Returns ``(loop_len [..., nloop], bin_dx_min [..., nbin])``."""
+        self._check(segmpos, self.segmpos_shape, "segmpos")
+        self._check(segmvel, self.segmpos_shape, "segmvel")
+        T, n = self.tables, self.segm_size
+        torch_in = _is_torch(segmpos)
+        speed = (segmvel * segmvel).sum(-1).sqrt() if torch_in else np.sqrt((segmvel * segmvel).sum(-1))   # [..., nsegm, store]
+        if self.segm_store == n:
+            val = speed.sum(-1)
+        else:
+            val = speed[..., 1:n].sum(-1) + 0.5 * (speed[..., 0] + speed[..., n])
+        segm_len = val * (T.nint_min / n)
+        seg_loop = T.bodyloop[T.gensegm_to_body]
+        loops = [segm_len[..., np.nonzero(seg_loop == il)[0].tolist()].sum(-1) / T.nint_min for il in range(T.nloop)]
+        mins = []
+        for ib in range(T.nbin):
+            src = segmpos[..., int(T.bin_source[ib]), :, :]
+            if not T.bin_spacerot_isid[ib]:
+                R = T.bin_spacerot[ib].T
+                if torch_in:
+                    import torch
+                    R = torch.as_tensor(np.ascontiguousarray(R), device=segmpos.device)
+                src = src @ R
+            d = src - segmpos[..., int(T.bin_target[ib]), :, :]
+            d2 = (d * d).sum(-1)
+            mins.append((d2.amin(-1) if torch_in else d2.min(-1)))
+        if torch_in:
+            import torch
+            return torch.stack(loops, -1), torch.stack(mins, -1).sqrt()
+        return np.stack(loops, -1), np.sqrt(np.stack(mins, -1))
+
     def TestHashSame(self, Hash_a, Hash_b, rtol: float = 1e-5, detect_multiples: bool = True) -> bool:
         """_NBodySyst.pyx:2036-2067.  For a homogeneous law (gravity / power law: Homo_exp = n) two orbits that differ by a
         rescaling have hashes whose ratios follow a power law; otherwise the hashes must agree entry by entry."""

@@ -52,6 +52,28 @@ def test_center_of_mass_and_escape_match_reference(sim, name):
         assert bool(nbs.DetectEscape(seg[0], fac)) == bool(NBS.DetectEscape(np.ascontiguousarray(seg[0]), fac))
 
 
+@pytest.mark.parametrize("name", ["3C", "3D", "3B", "5Dq"])
+def test_path_stats_match_reference(sim, name):
+    from oracle import ref_loader
+    if not ref_loader.reference_available():
+        pytest.skip("oracle/_ref not built")
+    ref_loader.import_reference()
+    NBS = ref_loader.build_named(name)
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", f"{name}.npz"))
+    nint = 2 * T.nint_min * 8
+    NBS.nint = nint
+    nbs = NBodySystB200(T, nint, _lib_handle=sim)
+    x = _states(nbs, 4, 7)
+    seg = nbs.params_to_segmpos(x)
+    vel = np.stack([np.asarray(NBS.params_to_segmvel(x[b].copy())) for b in range(4)])
+    loop_len, dx_min = nbs.segm_to_path_stats(seg, vel)
+    assert loop_len.shape == (4, T.nloop) and dx_min.shape == (4, T.nbin)
+    for b in range(4):
+        rl, rd = NBS.segm_to_path_stats(np.ascontiguousarray(seg[b]), np.ascontiguousarray(vel[b]))
+        assert np.abs(loop_len[b] - np.asarray(rl)).max() < 1e-12 * max(1.0, np.abs(rl).max())
+        assert np.abs(dx_min[b] - np.asarray(rd)).max() < 1e-12 * max(1.0, np.abs(rd).max())
+
+
 def test_center_of_mass_follows_translation(sim):
     T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3B.npz"))
     nbs = NBodySystB200(T, 32, _lib_handle=sim)
