@@ -137,3 +137,21 @@ def find_batched(make_nbs: Callable[[int], Any], x0, nint0: int, *, gradtol: flo
         lvl += 1
     return RefineResult(outcome=outcome, level=level, nint=nint_out, f_norm=f_norm, f_fine_norm=f_fine_norm, params=params,
                         newton_iterations=nit_tot, n_grad_evals=n_grad, n_hess_evals=n_hess)
+
+
+def group_duplicates(nbs, hashes, rtol: float = 1e-5, detect_multiples: bool = True) -> np.ndarray:
+    """Duplicate filter of the search loop over a batch (``Check_Duplicates``, find.py:905-935, minus the store folder): orbit
+    ``b`` joins the first earlier orbit whose hash passes ``TestHashSame`` (_NBodySyst.pyx:2036-2067), else it starts a new
+    group.  ``hashes``: ``[B, nexp]`` from ``nbs.segmpos_to_hash`` (NumPy array or device tensor).  Returns the group
+    representative (index of the first member) of every orbit, ``[B]``."""
+    H = hashes.detach().cpu().numpy() if type(hashes).__module__.startswith("torch") else np.asarray(hashes)
+    rep = np.arange(H.shape[0])
+    firsts: List[int] = []
+    for b in range(H.shape[0]):
+        for f in firsts:
+            if nbs.TestHashSame(H[f], H[b], rtol, detect_multiples):
+                rep[b] = f
+                break
+        else:
+            firsts.append(b)
+    return rep

@@ -142,3 +142,20 @@ def test_find_batched_matches_reference_outer_loop(sim):
             assert res.outcome[i] not in (0,)
     assert nsame >= 2
     assert (res.outcome > 0).all() and res.n_hess_evals > 0
+
+
+def test_group_duplicates(sim):
+    """Hash-based duplicate filter over a batch: the same orbit re-sampled (time shift = other Fourier phases), rescaled
+    (homogeneous law: detect_multiples) and a different orbit."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "sols.npz"))
+    name = "3C-Figure_eight"
+    pre = f"{name}/T/"
+    T = PlanTables.from_dict({k[len(pre):]: z[k] for k in z.files if k.startswith(pre)})
+    nbs = NBodySystB200(T, int(z[f"{name}/nint"]), _lib_handle=sim)
+    xs = z[f"{name}/params"]
+    seg = nbs.params_to_segmpos(xs)
+    other = nbs.params_to_segmpos(xs * np.linspace(1.0, 0.2, xs.size))   # another path
+    batch = np.stack([seg, other, seg * 1.7, seg, other * 0.5])
+    H = nbs.segmpos_to_hash(batch)
+    assert refine.group_duplicates(nbs, H).tolist() == [0, 1, 0, 0, 1]
+    assert refine.group_duplicates(nbs, H, detect_multiples=False).tolist() == [0, 1, 2, 0, 4]
