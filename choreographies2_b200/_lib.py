@@ -71,6 +71,9 @@ SYMBOLS = {
     "chb_params_to_kin_nrg_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),
     "chb_segmpos_to_pot_nrg_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),
     "chb_segmpos_to_hash_dev": (C.c_int, _dev_op + [_vp, C.c_double, _vp, _vp, _sz, _vp]),
+    "chb_compute_forces_dev": (C.c_int, [_vp, _i64, _vp, _vp, _vp]),
+    "chb_compute_grad_forces_dev": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "chb_compute_forces_host": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),
     "chb_arnoldi_step_dev": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "chb_row_stats_dev": (C.c_int, [_vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp]),
     "chb_gmres_solution_dev": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp]),

@@ -25,6 +25,7 @@
 #endif
 #include "chb_fused.cuh"
 #include "chb_fused4.cuh"
+#include "chb_ode.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // errors
@@ -2005,6 +2006,91 @@ extern "C" int chb_gmres_solution_dev(chb_plan *p, int64_t batch, int64_t n, int
 // ------------------------------------------------------------------------------------------------
 // memory helpers + host-pointer operators
 // ------------------------------------------------------------------------------------------------
+// ODE right-hand sides (chb_ode.cuh): forces and tangent forces of the reduced system at nvec phase-space points.
+// dpos == NULL: forces [nvec][nsegm*G]; else grad forces [nvec][nsegm*G][ndof].
+static int ode_launch(chb_plan *p, const char *name, int64_t nvec, int64_t ndof, const double *pos, const double *dpos,
+                      double *out, void *stream) {
+    (void)name;
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_compute_forces_dev / chb_compute_grad_forces_dev: NULL plan");
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_compute_forces_dev / chb_compute_grad_forces_dev: call chb_plan_set_nint first");
+    CHB_REQUIRE(nvec >= 0 && ndof >= 0, CHB_ERR_INVALID_ARGUMENT,
+                "chb_compute_forces_dev / chb_compute_grad_forces_dev: negative size");
+    const bool grad = dpos != nullptr;
+    const long long ncol = grad ? (long long)nvec * ndof : (long long)nvec;
+    if (ncol == 0) return CHB_OK;
+    CHB_REQUIRE(pos && out, CHB_ERR_INVALID_ARGUMENT, "chb_compute_forces_dev / chb_compute_grad_forces_dev: NULL array");
+    CHB_SET_DEVICE();
+    chb_stream_t st = (chb_stream_t)stream;
+    const ChbSys &S = p->sys;
+#ifndef CHB_HOSTSIM
+    // columns per CTA: the largest of 128 / 64 / 32 whose two [entry][column] tiles fit in shared memory, three CTAs per SM
+    // when the tiles are small; vectors too long for that go straight to global memory
+    const int vs = S.nsegm * S.G;
+    int T = 128;
+    auto tile_bytes = [&](int t) { return (size_t)2 * vs * (t + 1) * sizeof(double); };
+    while (T > 32 && tile_bytes(T) > p->smem_limit - 1024) T >>= 1;
+    static const bool no_tiles = [] { const char *e = getenv("CHB_ODE_NOSMEM"); return e && atoi(e) != 0; }();  // tests
+    const bool smem = !no_tiles && tile_bytes(T) <= p->smem_limit - 1024;
+    const size_t sb = smem ? tile_bytes(T) : 0;
+    const long long ntile = (ncol + T - 1) / T;
+    const int per_sm = smem ? (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)(200 * 1024) / (sb + 1024))) : 8;
+    const long long grid = std::min<long long>(ntile, (long long)p->num_sms * per_sm);
+    if (grad) {
+        if (smem) CHB_LAUNCH(p, (k_ode_forces<true, true>), grid, T, sb, st, S, ncol, (long long)ndof, pos, dpos, out);
+        else CHB_LAUNCH(p, (k_ode_forces<true, false>), grid, T, sb, st, S, ncol, (long long)ndof, pos, dpos, out);
+    } else {
+        if (smem) CHB_LAUNCH(p, (k_ode_forces<false, true>), grid, T, sb, st, S, ncol, 1LL, pos, dpos, out);
+        else CHB_LAUNCH(p, (k_ode_forces<false, false>), grid, T, sb, st, S, ncol, 1LL, pos, dpos, out);
+    }
+#else
+    (void)st;
+    if (grad) ode_forces_host<true>(S, ncol, ndof, pos, dpos, out);
+    else ode_forces_host<false>(S, ncol, 1, pos, dpos, out);
+    p->launches++;
+#endif
+    return CHB_OK;
+}
+extern "C" int chb_compute_forces_dev(chb_plan *p, int64_t nvec, const double *pos, double *forces, void *stream) {
+    return ode_launch(p, "chb_compute_forces_dev", nvec, 1, pos, nullptr, forces, stream);
+}
+extern "C" int chb_compute_grad_forces_dev(chb_plan *p, int64_t nvec, int64_t grad_ndof, const double *pos, const double *dpos,
+                                           double *grad_forces, void *stream) {
+    CHB_REQUIRE(nvec * grad_ndof == 0 || dpos, CHB_ERR_INVALID_ARGUMENT, "chb_compute_grad_forces_dev: NULL dpos");
+    if (nvec * grad_ndof == 0) return CHB_OK;
+    return ode_launch(p, "chb_compute_grad_forces_dev", nvec, grad_ndof, pos, dpos, grad_forces, stream);
+}
+// Host-pointer forms: the arrays travel to the plan's device and back inside the call (dpos / grad_forces NULL: forces only).
+extern "C" int chb_compute_forces_host(chb_plan *p, int64_t nvec, int64_t grad_ndof, const double *pos, const double *dpos,
+                                       double *forces, double *grad_forces) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_compute_forces_host: NULL plan");
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_compute_forces_host: call chb_plan_set_nint first");
+    CHB_REQUIRE(nvec >= 0 && grad_ndof >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_compute_forces_host: negative size");
+    CHB_REQUIRE((dpos == nullptr) == (grad_forces == nullptr), CHB_ERR_INVALID_ARGUMENT,
+                "chb_compute_forces_host: dpos and grad_forces go together");
+    if (nvec == 0) return CHB_OK;
+    CHB_REQUIRE(pos && (forces || grad_forces), CHB_ERR_INVALID_ARGUMENT, "chb_compute_forces_host: NULL array");
+    const size_t vs = (size_t)p->sys.nsegm * p->sys.G;
+    const size_t nb_pos = sizeof(double) * vs * (size_t)nvec, nb_grad = dpos ? nb_pos * (size_t)grad_ndof : 0;
+    void *d_pos = nullptr, *d_out = nullptr, *d_dpos = nullptr, *d_gout = nullptr;
+    int rc = dev_alloc(p, nb_pos, &d_pos);
+    if (!rc) rc = dev_alloc(p, nb_pos, &d_out);
+    if (!rc && nb_grad) rc = dev_alloc(p, nb_grad, &d_dpos);
+    if (!rc && nb_grad) rc = dev_alloc(p, nb_grad, &d_gout);
+    if (!rc) rc = dev_upload(d_pos, pos, nb_pos);
+    if (!rc && nb_grad) rc = dev_upload(d_dpos, dpos, nb_grad);
+    if (!rc && forces) rc = chb_compute_forces_dev(p, nvec, (const double *)d_pos, (double *)d_out, nullptr);
+    if (!rc && nb_grad)
+        rc = chb_compute_grad_forces_dev(p, nvec, grad_ndof, (const double *)d_pos, (const double *)d_dpos, (double *)d_gout, nullptr);
+    if (!rc && forces) rc = chb_memcpy_d2h(p, forces, d_out, nb_pos, nullptr);
+    if (!rc && nb_grad) rc = chb_memcpy_d2h(p, grad_forces, d_gout, nb_grad, nullptr);
+    if (!rc) rc = chb_stream_synchronize(p, nullptr);
+    if (d_pos) dev_free(d_pos);
+    if (d_out) dev_free(d_out);
+    if (d_dpos) dev_free(d_dpos);
+    if (d_gout) dev_free(d_gout);
+    return rc;
+}
+
 extern "C" int chb_malloc_device(chb_plan *p, size_t bytes, void **out) {
     CHB_REQUIRE(p && out, CHB_ERR_INVALID_ARGUMENT, "chb_malloc_device: NULL argument");
     return dev_alloc(p, bytes, out);

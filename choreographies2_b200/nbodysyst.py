@@ -285,6 +285,63 @@ class NBodySystB200:
                 for e in self.Hash_exp]
         return np.stack(cols, axis=-1).reshape(a.shape[:-3] + (len(self.Hash_exp),))
 
+    # ------------------------------------------------------------------ ODE right-hand sides
+    def _forces(self, pos_flat, dpos_flat=None):
+        vs = self.nsegm * self.geodim
+        if _is_torch(pos_flat):
+            import torch
+            x, nvec, _ = self._tprep(pos_flat, (vs,), "pos_flat")
+            stream = C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)
+            vp = lambda a: C.c_void_p(a.data_ptr())  # noqa: E731
+            if dpos_flat is None:
+                out = torch.empty_like(x)
+                L.check(self._lib, self._lib.chb_compute_forces_dev(self._plan, nvec, vp(x), vp(out), stream))
+                return out
+            if not _is_torch(dpos_flat) or dpos_flat.dim() < 2 or dpos_flat.shape[-2] != vs:
+                raise ValueError(f"dpos_flat: expected a tensor of shape [..., {vs}, grad_ndof]")
+            ndof = int(dpos_flat.shape[-1])
+            d, nd, _ = self._tprep(dpos_flat, (vs, ndof), "dpos_flat")
+            if nd != nvec:
+                raise ValueError("pos_flat and dpos_flat hold different numbers of vectors")
+            out = torch.empty_like(d)
+            L.check(self._lib, self._lib.chb_compute_grad_forces_dev(self._plan, nvec, ndof, vp(x), vp(d), vp(out), stream))
+            return out
+        x = np.ascontiguousarray(pos_flat, dtype=np.float64)
+        nvec, _ = self._check(x, (vs,), "pos_flat")
+        vp = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None  # noqa: E731
+        if dpos_flat is None:
+            out = np.empty_like(x)
+            L.check(self._lib, self._lib.chb_compute_forces_host(self._plan, nvec, 0, vp(x), None, vp(out), None))
+            return out
+        d = np.ascontiguousarray(dpos_flat, dtype=np.float64)
+        if d.ndim < 2 or d.shape[-2] != vs:
+            raise ValueError(f"dpos_flat: expected an array of shape [..., {vs}, grad_ndof]")
+        ndof = int(d.shape[-1])
+        nd, _ = self._check(d, (vs, ndof), "dpos_flat")
+        if nd != nvec:
+            raise ValueError("pos_flat and dpos_flat hold different numbers of vectors")
+        out = np.empty_like(d)
+        L.check(self._lib, self._lib.chb_compute_forces_host(self._plan, nvec, ndof, vp(x), vp(d), None, vp(out)))
+        return out
+
+    def Compute_forces(self, t, pos_flat):
+        """_NBodySyst.pyx:4154-4171 (cdef 7531-7638): forces on the segments at one phase-space point, ``[nsegm*geodim]``
+        (``t`` is unused, as in the reference: the system is autonomous)."""
+        return self._forces(pos_flat)
+
+    def Compute_forces_vectorized(self, t, pos_flat):
+        """_NBodySyst.pyx:4228-4246: ``pos_flat`` is ``[nvec, nsegm*geodim]`` (any leading shape here); one thread per
+        vector on the device (``chb_compute_forces_dev``)."""
+        return self._forces(pos_flat)
+
+    def Compute_grad_forces(self, t, pos_flat, dpos_flat):
+        """_NBodySyst.pyx:4173-4191 (cdef 7641-7790): tangent forces, ``dpos_flat`` and the result ``[nsegm*geodim, grad_ndof]``."""
+        return self._forces(pos_flat, dpos_flat)
+
+    def Compute_grad_forces_vectorized(self, t, pos_flat, dpos_flat):
+        """_NBodySyst.pyx:4249-4268: ``[nvec, nsegm*geodim]`` positions, ``[nvec, nsegm*geodim, grad_ndof]`` tangents."""
+        return self._forces(pos_flat, dpos_flat)
+
     def params_resize(self, params_buf_in, nint_fac: int = 1):
         """_NBodySyst.pyx:2413-2465: the parameters of this ``nint`` level re-expressed at ``nint = 2 nint_min nint_fac``
         (batched over leading dimensions)."""

@@ -267,6 +267,19 @@ enum chb_op {
 int chb_run_host(chb_plan *plan, int op, int64_t batch, const double *in0, const double *in1, double scalar,
                  double *out0, double *out1);
 
+/* ---- ODE right-hand sides of the reduced system, batched over nvec phase-space points (one time sample each) ------------
+ * Compute_forces / Compute_forces_vectorized (choreo/cython/_NBodySyst.pyx:4154-4171, 4228-4246; cdef 7531-7638):
+ *   pos, forces [nvec][nsegm*geodim].
+ * Compute_grad_forces / Compute_grad_forces_vectorized (:4173-4191, 4249-4268; cdef 7641-7790):
+ *   dpos, grad_forces [nvec][nsegm*geodim][grad_ndof].
+ * Every vector is evaluated from its own positions (the per-vector definition of the reference). */
+int chb_compute_forces_dev(chb_plan *plan, int64_t nvec, const double *pos, double *forces, void *stream);
+int chb_compute_grad_forces_dev(chb_plan *plan, int64_t nvec, int64_t grad_ndof, const double *pos, const double *dpos,
+                                double *grad_forces, void *stream);
+/* host-pointer form of both (forces and / or grad_forces; dpos and grad_forces are given together or both NULL) */
+int chb_compute_forces_host(chb_plan *plan, int64_t nvec, int64_t grad_ndof, const double *pos, const double *dpos,
+                            double *forces, double *grad_forces);
+
 /* ---- memory helpers so a NumPy-only caller needs no CUDA binding ---------------------------------- */
 int chb_malloc_device(chb_plan *plan, size_t bytes, void **ptr_out);
 int chb_free_device(chb_plan *plan, void *ptr);
