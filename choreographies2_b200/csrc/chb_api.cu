@@ -2026,6 +2026,27 @@ static int ode_launch(chb_plan *p, const char *name, int64_t nvec, int64_t ndof,
     // columns per CTA: the largest of 128 / 64 / 32 whose two [entry][column] tiles fit in shared memory, three CTAs per SM
     // when the tiles are small; vectors too long for that go straight to global memory
     const int vs = S.nsegm * S.G;
+    {
+        // dense gather variants: identity rotations everywhere (S.pair_w), planar, enough segments to fill warps
+        static const bool dense_on = [] { const char *e = getenv("CHB_ODE_DENSE"); return !(e && atoi(e) == 0); }();
+        if (dense_on && S.pair_w && S.G == 2 && S.nsegm >= 8 && S.nsegm <= 256) {
+            if (!grad) {
+                const int nv_tile = std::max(1, 256 / S.nsegm), thr = nv_tile * S.nsegm;
+                const long long ntile = (nvec + nv_tile - 1) / nv_tile;
+                const long long grid = std::min<long long>(ntile, (long long)p->num_sms * (2048 / ((thr + 31) / 32 * 32)));
+                CHB_LAUNCH(p, k_ode_forces_dense<2>, grid, thr, sizeof(double) * nv_tile * vs, st, S, (long long)nvec, pos, out);
+                return CHB_OK;
+            }
+            if (ndof >= 16) {
+                const long long nitem = (long long)nvec * ((ndof + CHB_ODE_KC - 1) / CHB_ODE_KC);
+                const size_t sb = sizeof(double) * (size_t)vs * (CHB_ODE_KC + 1);
+                const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)(200 * 1024) / (sb + 1024)));
+                const long long grid = std::min<long long>(nitem, (long long)p->num_sms * per_sm);
+                CHB_LAUNCH(p, k_ode_grad_forces_dense<2>, grid, 256, sb, st, S, (long long)nvec, (long long)ndof, pos, dpos, out);
+                return CHB_OK;
+            }
+        }
+    }
     int T = 128;
     auto tile_bytes = [&](int t) { return (size_t)2 * vs * (t + 1) * sizeof(double); };
     while (T > 32 && tile_bytes(T) > p->smem_limit - 1024) T >>= 1;
@@ -2033,7 +2054,7 @@ static int ode_launch(chb_plan *p, const char *name, int64_t nvec, int64_t ndof,
     const bool smem = !no_tiles && tile_bytes(T) <= p->smem_limit - 1024;
     const size_t sb = smem ? tile_bytes(T) : 0;
     const long long ntile = (ncol + T - 1) / T;
-    const int per_sm = smem ? (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)(200 * 1024) / (sb + 1024))) : 8;
+    const int per_sm = smem ? (int)std::max<size_t>(1, std::min<size_t>(16, (size_t)(200 * 1024) / (sb + 1024))) : 8;
     const long long grid = std::min<long long>(ntile, (long long)p->num_sms * per_sm);
     if (grad) {
         if (smem) CHB_LAUNCH(p, (k_ode_forces<true, true>), grid, T, sb, st, S, ncol, (long long)ndof, pos, dpos, out);

@@ -35,6 +35,7 @@ for name in (sys.argv[1:] or ["3C", "3B", "5Dq", "20B", "64C"]):
     out = {"system": name, "nsegm": int(T.nsegm), "nbin": int(T.nbin), "vs": vs}
     s = timed(lambda: nbs.Compute_forces_vectorized(None, pos))
     out["forces"] = {"nvec": nvec, "ms": s * 1e3, "Mvec_per_s": nvec / s / 1e6, "GBs": 16 * vs * nvec / s / 1e9,
+                     "Gpairs_per_s": int(T.nbin) * nvec / s / 1e9,
                      "frac_hbm": 16 * vs * nvec / s / 1e9 / peak}
     ndof = 2 * vs
     nv2 = max(64, (1 << 27) // (vs * ndof))
@@ -43,5 +44,6 @@ for name in (sys.argv[1:] or ["3C", "3B", "5Dq", "20B", "64C"]):
     s = timed(lambda: nbs.Compute_grad_forces_vectorized(None, pos2, dpos))
     by = (16 * ndof + 8) * vs * nv2
     out["grad_forces"] = {"nvec": nv2, "ndof": ndof, "ms": s * 1e3, "Mvec_per_s": nv2 / s / 1e6, "GBs": by / s / 1e9,
+                          "Gpair_columns_per_s": int(T.nbin) * nv2 * ndof / s / 1e9,
                           "frac_hbm": by / s / 1e9 / peak}
     print(json.dumps(out))
