@@ -87,16 +87,34 @@ __global__ void k_ode_forces(ChbSys S, long long ncol, long long ndof, const dou
         if (SMEM) {
             if (!GRAD) {
                 // the tile is one contiguous block of nc*vs doubles: coalesced read, transposed into [e][column]
+                // (loads batched in registers: the shared-memory stores would otherwise order them one latency apart)
                 const double *src = pos + c0 * vs;
-                for (int idx = tid; idx < nc * vs; idx += T) {
-                    const int cl = idx / vs, e = idx - cl * vs;
-                    in_s[e * TP + cl] = src[idx];
+                const int n = nc * vs;
+                for (int base = tid; base < n; base += 8 * T) {
+                    double r[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) r[u] = base + u * T < n ? __ldg(src + base + u * T) : 0.0;
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int idx = base + u * T;
+                        if (idx < n) {
+                            const int cl = idx / vs, e = idx - cl * vs;
+                            in_s[e * TP + cl] = r[u];
+                        }
+                    }
                 }
             } else if (tid < nc) {
                 // consecutive columns of one vector are consecutive in memory for every entry
                 const long long k = c - v * ndof;
                 const double *src = din + v * vs * ndof + k;
-                for (int e = 0; e < vs; ++e) in_s[e * TP + tid] = src[(long long)e * ndof];
+                for (int e0 = 0; e0 < vs; e0 += 8) {
+                    double r[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) r[u] = e0 + u < vs ? __ldg(src + (long long)(e0 + u) * ndof) : 0.0;
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (e0 + u < vs) in_s[(e0 + u) * TP + tid] = r[u];
+                }
             }
             __syncthreads();
             if (tid < nc) {
