@@ -25,6 +25,7 @@
 #endif
 #include "chb_fused.cuh"
 #include "chb_fused4.cuh"
+#include "chb_fused5.cuh"
 #include "chb_ode.cuh"
 
 // ------------------------------------------------------------------------------------------------
@@ -103,6 +104,8 @@ struct chb_plan {
     ChfSys fsys;            // fused path (valid when fused_active)
     int fused_threads = 0;
     size_t fused_smem = 0;
+    int fused5_active = 0;  // the level is served by the general fused kernel (chb_fused5.cuh) instead of versions 3 / 4
+    Ch5Sys f5;              // passed by value (constant bank) to k_fused5
 };
 
 // ---- memory shims --------------------------------------------------------------------------------
@@ -589,6 +592,161 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
     return 1;
 }
 
+
+// ---- general fused path planning (chb_fused5.cuh) ----------------------------------------------------
+// returns 1 when k_fused5 can serve this level (and fills p->f5), 0 when not, <0 on error
+static int fused5_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_size, int segm_store) {
+    const HostTables &T = p->T;
+    static_assert(sizeof(Ch5Sys) + sizeof(ChfArgs) <= 32000, "kernel parameter space (CUDA >= 12.1: 32764 bytes)");
+    if (T.G != 2 || T.nloop > CHF_MAX_LOOPS || T.nsegm > CH5_MAX_SEGS || T.nsegm < 1) return 0;
+    Ch5Sys &F = p->f5;
+    memset(&F, 0, sizeof(F));
+    F.nloop = T.nloop;
+    F.nseg = T.nsegm;
+    F.segm_size = segm_size;
+    F.segm_store = segm_store;
+    F.law_kind = T.law;
+    for (int i = 0; i < 4; ++i) F.law[i] = T.law_params[i];
+    F.nparams = p->sys.nparams;
+    F.segsz = p->sys.segsz;
+    long long smem_cd = 0;
+    int maxN = 0;
+    std::map<int, int> first_loop_of_N;
+    for (int il = 0; il < T.nloop; ++il) {
+        const ChbLoop &L = loops[il];
+        Ch5Loop &FL = F.loops[il];
+        if (L.nnz < 1 || L.nnz > CH5_MAX_NNZ || L.nppl > CHB_MAX_NPPL) return 0;
+        FL.kind = L.shortcut;
+        FL.n_sub_fft = L.n_sub_fft;
+        FL.nnz = L.nnz;
+        FL.nppl = L.nppl;
+        FL.C = L.C;
+        FL.has_k0 = L.has_k0;
+        if (L.shortcut == CHB_RFFT) {
+            if (L.nnz != 1 || L.nppl != 4 || L.n_sub_fft != 1 || !L.has_k0) return 0;
+            FL.Cp = 1;
+        } else {
+            if (L.C < 2 || (L.C & 1) || L.C > CH5_MAX_C) return 0;
+            FL.Cp = L.C / 2;
+        }
+        ChfLoop &f = FL.f;
+        f.N = 2 * L.npr;
+        f.npr = L.npr;
+        std::vector<int> fac;
+        if (!chf_factorize(f.N, fac)) return 0;
+        f.nfac = (int)fac.size();
+        for (int i = 0; i < f.nfac; ++i) f.fac[i] = fac[i];
+        f.swm = (f.N % 16 == 0) ? 15 : 0;
+        f.mom_off = L.mom_off;
+        f.nco_in = L.nco_in;
+        f.ncm = L.ncm;
+        f.co0 = (L.shortcut == CHB_RFFT && L.co_in[0]) ? L.co_prefix[0] : -1;
+        f.co2 = (L.shortcut == CHB_RFFT && L.co_in[2]) ? L.co_prefix[2] : -1;
+        f.loopmul = L.loopmul;
+        FL.seq_stride = f.N;
+        f.smem_off = (int)smem_cd;
+        smem_cd += (long long)FL.Cp * f.N + 16;  // + the Adjust_after_last_gen row, keeps the next loop 256-byte aligned
+        maxN = std::max(maxN, f.N);
+        for (int j = 0; j < L.nppl; ++j) { FL.co_in[j] = L.co_in[j]; FL.co_prefix[j] = L.co_prefix[j]; }
+        FL.tw_trivial = 1;
+        for (int ik = 0; ik < L.nnz; ++ik) {
+            FL.nnz_k[ik] = L.nnz_k[ik];
+            FL.wmir[ik] = L.wmir[ik];
+            if (L.nnz_k[ik] != 0) FL.tw_trivial = 0;
+        }
+        for (int g = 0; g < 2; ++g)
+            for (int c = 0; c < L.C; ++c) { FL.bre[g][c] = L.bre[g][c]; FL.bim[g][c] = L.bim[g][c]; }
+        FL.gen_tw = L.gen_tw;
+        FL.has_alg = L.has_alg;
+        FL.alg_src = L.alg_src;
+        for (int i = 0; i < 4; ++i) FL.alg_rot[i] = L.alg_rot[i];
+        // rows produced by the transform and their coverage: every slot of segm_size rows holds exactly one segment
+        const int main_rows = (L.n_sub_fft == 2) ? L.npr : 2 * L.npr;
+        FL.nrows = (L.n_sub_fft == 2) ? L.npr + 1 : 2 * L.npr;
+        if (main_rows % segm_size != 0) return 0;
+        if (segm_store != segm_size && L.n_sub_fft == 1 && !L.has_alg) return 0;
+        std::vector<int> cover(main_rows / segm_size, 0);
+        for (int s = 0; s < T.nsegm; ++s)
+            if ((int)T.bodyloop[T.seg_body[s]] == il) {
+                if (T.seg_iintrel[s] >= (int64_t)cover.size()) return 0;
+                cover[T.seg_iintrel[s]]++;
+            }
+        for (int c : cover)
+            if (c != 1) return 0;
+    }
+    for (int s = 0; s < T.nsegm; ++s) {
+        ChfSeg &sg = F.segs[s];
+        sg.loop = (int)T.bodyloop[T.seg_body[s]];
+        sg.row0 = (int)T.seg_iintrel[s] * segm_size;
+        sg.timerev = (int)T.seg_timerev[s];
+        sg.isid = T.seg_isid[s] ? 1 : 0;
+        for (int i = 0; i < 4; ++i) sg.rot[i] = T.seg_rot[(size_t)s * 4 + i];
+    }
+    for (int b = 0; b < T.nbin; ++b) {
+        ChfPair &P = F.pairs[T.bin_src[b] * CH5_MAX_SEGS + T.bin_tgt[b]];
+        if (P.on) return 0;  // two interactions on the same ordered segment pair: generic path
+        P.on = 1;
+        P.isid = T.bin_isid[b] ? 1 : 0;
+        P.fac = T.bin_fac[b];
+        for (int i = 0; i < 4; ++i) P.rot[i] = T.bin_rot[(size_t)b * 4 + i];
+    }
+    int Tg = ((maxN / 32 + 31) / 32) * 32;
+    const int cap = (CHF_MAX_THREADS / T.nloop) / 32 * 32;
+    if (cap < 32) return 0;
+    Tg = std::max(32, std::min(Tg, cap));
+    F.T = Tg;
+    p->fused_threads = Tg * T.nloop;
+    p->fused_smem = CHF_RED_BYTES + (size_t)smem_cd * sizeof(cd);
+    if (p->fused_smem > p->smem_limit) return 0;
+    {
+        const size_t per_cta = p->fused_smem + 1024;
+        int occ = (int)std::min<size_t>((size_t)(228 * 1024) / per_cta, (size_t)(2048 / p->fused_threads));
+        occ = std::max(1, std::min(occ, 32));
+        p->fused_resident = occ * p->num_sms;
+    }
+    // FFT tables (global memory), shared between loops of equal length
+    for (int il = 0; il < T.nloop; ++il) {
+        ChfLoop &f = F.loops[il].f;
+        auto it = first_loop_of_N.find(f.N);
+        if (it != first_loop_of_N.end()) {
+            const ChfLoop &g = F.loops[it->second].f;
+            f.rev = g.rev;
+            for (int i = 0; i < f.nfac; ++i) { f.tw[i] = g.tw[i]; f.tw_len[i] = g.tw_len[i]; f.tw_soff[i] = -1; }
+            continue;
+        }
+        first_loop_of_N[f.N] = il;
+        const int N = f.N;
+        std::vector<int> rev(N);
+        for (int k = 0; k < N; ++k) {
+            int kk = k, pos = 0, Lcur = N;
+            for (int i = 0; i < f.nfac; ++i) {
+                const int r = f.fac[i], t = kk % r;
+                kk /= r;
+                Lcur /= r;
+                pos += t * Lcur;
+            }
+            rev[k] = pos;
+        }
+        if (level_upload(p, rev, &f.rev)) return -1;
+        int Lcur = N;
+        for (int i = 0; i < f.nfac; ++i) {
+            const int r = f.fac[i], Lp = Lcur / r, nb = chf_nbase(r);
+            std::vector<cd> tw((size_t)std::max(1, Lp * nb));
+            for (int j = 0; j < Lp; ++j)
+                for (int e = 0; e < nb; ++e) {
+                    double c, sn;
+                    exact_root((long long)j * (1LL << e), Lcur, &c, &sn);
+                    tw[(size_t)e * Lp + j] = mk(c, sn);
+                }
+            if (level_upload(p, tw, &f.tw[i])) return -1;
+            f.tw_len[i] = Lp > 1 ? Lp * nb : 0;
+            f.tw_soff[i] = -1;
+            Lcur = Lp;
+        }
+    }
+    return 1;
+}
+
 extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
     CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_nint: NULL plan");
     HostTables &T = p->T;
@@ -875,6 +1033,14 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
         int rcf = fused_setup(p, loops, segm_size);
         if (rcf < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: fused setup failed"); }
         p->fused_active = rcf;
+        p->fused5_active = 0;
+        if (!rcf) {  // layouts versions 3 / 4 refuse: the general fused kernel
+            int rc5 = fused5_setup(p, loops, segm_size, segm_store);
+            if (rc5 < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: fused setup failed"); }
+            if (getenv("CHB_FUSED5") && atoi(getenv("CHB_FUSED5")) == 0) rc5 = 0;  // A/B knob
+            p->fused5_active = rc5;
+            p->fused_active = rc5;
+        }
         p->ready = true;
     }
     return CHB_OK;
@@ -900,7 +1066,11 @@ extern "C" int chb_plan_query(const chb_plan *p, int what, int64_t *v) {
 #else
         case CHB_Q_HOST_POINTERS: *v = 0; break;
 #endif
-        case CHB_Q_FUSED: *v = (p->fused_enabled && p->fused_active) ? ((p->fused_enabled >= 4 && p->fused4_ok) ? 4 : std::min(p->fused_enabled, 3)) : 0; break;
+        case CHB_Q_FUSED:
+            *v = (p->fused_enabled && p->fused_active)
+                     ? (p->fused5_active ? 5 : ((p->fused_enabled >= 4 && p->fused4_ok) ? 4 : std::min(p->fused_enabled, 3)))
+                     : 0;
+            break;
         case CHB_Q_CHUNK: {
             int64_t c = p->chunk_user;
             if (c <= 0) {
@@ -1467,6 +1637,27 @@ CHB_KERNEL void CHF_BOUNDS k_fused4(ChfSys F, ChfArgs A) {
 #endif
 }
 
+
+// general fused kernel (chb_fused5.cuh): persistent CTAs, one state at a time per CTA, any mix of RFFT / GENERAL loops
+#ifndef CHB_HOSTSIM
+#define CH5_SYS_PARAM const __grid_constant__ Ch5Sys F
+#else
+#define CH5_SYS_PARAM const Ch5Sys &F
+#endif
+template <int NSEG, int PMODE>
+CHB_KERNEL void CHF_BOUNDS k_fused5(CH5_SYS_PARAM, ChfArgs A) {
+    CHB_CTX_DECL;
+    double *red = (double *)CHB_SMEM;
+    cd *bnd = (cd *)(CHB_SMEM + sizeof(double) * CHF_MAX_THREADS);  // 1 KB behind the partial sums
+    cd *sm = (cd *)(CHB_SMEM + CHF_RED_BYTES);
+    const long long nwork = A.live_list ? (long long)*A.live_count : A.nstates;
+    for (long long k = CHB_BLOCK_ID; k < nwork; k += CHB_GRID_DIM) {
+        const long long b = A.live_list ? (long long)A.live_list[k] : k;
+        if (A.skip && A.skip[b]) continue;  // CTA-uniform
+        cta_fused5<NSEG, PMODE>(ctx, F, A, b, red, sm, bnd);
+    }
+}
+
 #ifndef CHB_HOSTSIM
 #define CHB_LAUNCH(p, kern, grid, block, smem, stream, ...)                                                  \
     do {                                                                                                     \
@@ -1584,8 +1775,35 @@ static int launch_fused_n(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A, 
     }
     return CHB_OK;
 }
+
+template <int NSEG>
+static int launch_fused5_n(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A, chb_stream_t st) {
+    switch (pmode) {
+        case 0: CHB_LAUNCH(p, (k_fused5<NSEG, 0>), nb, p->fused_threads, p->fused_smem, st, p->f5, A); break;
+        case 1: CHB_LAUNCH(p, (k_fused5<NSEG, 1>), nb, p->fused_threads, p->fused_smem, st, p->f5, A); break;
+        case 2: CHB_LAUNCH(p, (k_fused5<NSEG, 2>), nb, p->fused_threads, p->fused_smem, st, p->f5, A); break;
+        default: CHB_LAUNCH(p, (k_fused5<NSEG, 3>), nb, p->fused_threads, p->fused_smem, st, p->f5, A); break;
+    }
+    return CHB_OK;
+}
+static int launch_fused5(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A0, chb_stream_t st) {
+    ChfArgs A = A0;
+    A.nstates = nb;
+    nb = std::min<int64_t>(nb, (int64_t)p->fused_resident);  // persistent grid = one resident wave
+    switch (p->f5.nseg) {
+        case 1: return launch_fused5_n<1>(p, pmode, nb, A, st);
+        case 2: return launch_fused5_n<2>(p, pmode, nb, A, st);
+        case 3: return launch_fused5_n<3>(p, pmode, nb, A, st);
+        case 4: return launch_fused5_n<4>(p, pmode, nb, A, st);
+        case 5: return launch_fused5_n<5>(p, pmode, nb, A, st);
+        case 6: return launch_fused5_n<6>(p, pmode, nb, A, st);
+        case 7: return launch_fused5_n<7>(p, pmode, nb, A, st);
+        default: return launch_fused5_n<8>(p, pmode, nb, A, st);
+    }
+}
 // pmode: 0 energy, 1 energy + gradient, 2 Hessian-vector, 3 segment positions only
 static int launch_fused(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A0, chb_stream_t st) {
+    if (p->fused5_active) return launch_fused5(p, pmode, nb, A0, st);
     ChfArgs A = A0;
     A.nstates = nb;
     p->fsys.ver = p->fused_enabled;

@@ -18,7 +18,9 @@ OUT = os.path.join(HERE, "libchb_hostsim.so")
 def build(force=False):
     deps = [SRC, os.path.join(os.path.dirname(SRC), "chb_core.cuh"), os.path.join(os.path.dirname(SRC), "chb_fused.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_fused4.cuh"),
+            os.path.join(os.path.dirname(SRC), "chb_fused5.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_krylov.cuh"),
+            os.path.join(os.path.dirname(SRC), "chb_ode.cuh"),
             os.path.join(ROOT, "include", "choreo_b200.h")]
     if force or not os.path.isfile(OUT) or any(os.path.getmtime(d) > os.path.getmtime(OUT) for d in deps):
         subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DCHB_HOSTSIM", "-x", "c++", SRC, "-o", OUT],
