@@ -15,17 +15,18 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libchoreo_b200.so")
 
 CHB_OK = 0
+ABI_VERSION = 2  # CHB_ABI_VERSION of include/choreo_b200.h
 STATUS_NAMES = {
     1: "CHB_ERR_INVALID_ARGUMENT", 2: "CHB_ERR_INVALID_NINT", 3: "CHB_ERR_UNSUPPORTED", 4: "CHB_ERR_CUDA",
     5: "CHB_ERR_NO_DEVICE", 6: "CHB_ERR_WORKSPACE", 7: "CHB_ERR_NOT_READY",
 }
 # enum chb_query
 Q_NINT, Q_NPARAMS, Q_SEGM_SIZE, Q_SEGM_STORE, Q_NSEGM, Q_GEODIM, Q_NLOOP, Q_NBIN, Q_DEVICE, Q_CHUNK, Q_LAUNCHES, \
-    Q_FUSED, Q_SEGMPOS_SIZE, Q_HOST_POINTERS = range(14)
+    Q_FUSED, Q_SEGMPOS_SIZE, Q_HOST_POINTERS, Q_NPARAMS_INCL_O = range(15)
 # enum chb_op
 (OP_PARAMS_TO_SEGMPOS, OP_SEGMPOS_TO_PARAMS, OP_SEGMPOS_TO_PARAMS_T, OP_ACTION, OP_ACTION_GRAD, OP_ACTION_HESS,
  OP_SEGMPOS_ACTION, OP_SEGMPOS_ACTION_GRAD, OP_SEGMPOS_ACTION_HESS, OP_KIN, OP_POT, OP_POT_GRAD, OP_POT_HESS,
- OP_HASH) = range(14)
+ OP_HASH, OP_PARAMS_TO_SEGMVEL) = range(15)
 
 _p64 = C.POINTER(C.c_int64)
 _p32 = C.POINTER(C.c_int32)
@@ -46,6 +47,7 @@ class chb_tables(C.Structure):
         ("inter_spacerot", _pd), ("inter_spacerot_isid", _p32),
         ("bin_source", _p64), ("bin_target", _p64), ("bin_spacerot", _pd), ("bin_spacerot_isid", _p32),
         ("bin_prodchargesum", _pd),
+        ("bodysegm", _p64), ("body_spacerot", _pd), ("body_timerev", _p64),  # ABI 2, optional (NULL)
     ]
 
 
@@ -88,6 +90,13 @@ SYMBOLS = {
     "chb_segmpos_params_to_action_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _sz, _vp]),
     "chb_segmpos_params_to_action_grad_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "chb_segmpos_dparams_to_action_hess_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _sz, _vp]),
+    "chb_params_to_segmvel_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),
+    "chb_params_changevar_dev": (C.c_int, _dev_op + [_vp, C.c_int, C.c_int, _vp, _vp]),
+    "chb_segmpos_to_hash_multi_dev": (C.c_int, _dev_op + [_vp, C.c_int, _vp, _vp, _vp]),
+    "chb_center_of_mass_dev": (C.c_int, _dev_op + [_vp, _vp, _vp]),
+    "chb_detect_escape_dev": (C.c_int, _dev_op + [_vp, C.c_double, _vp, _vp]),
+    "chb_path_stats_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _vp]),
+    "chb_compute_velocities_dev": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "chb_run_host": (C.c_int, [_vp, C.c_int, _i64, _vp, _vp, C.c_double, _vp, _vp]),
     "chb_malloc_device": (C.c_int, [_vp, _sz, C.POINTER(_vp)]),
     "chb_free_device": (C.c_int, [_vp, _vp]),
@@ -124,7 +133,7 @@ def load() -> C.CDLL:
                 f"{LIB_PATH} is missing: build it with `python -m choreographies2_b200.build` "
                 "(nvcc, sm_100a). There is no CPU fallback for this path.")
         _lib = bind(C.CDLL(LIB_PATH))
-        if _lib.chb_abi_version() != 1:
+        if _lib.chb_abi_version() != ABI_VERSION:
             raise ChoreoB200Error("libchoreo_b200.so ABI version mismatch")
     return _lib
 
@@ -184,4 +193,8 @@ def tables_struct(T) -> "tuple[chb_tables, list]":
     s.bin_spacerot = ptr(T.bin_spacerot, f64, C.c_double)
     s.bin_spacerot_isid = ptr(T.bin_spacerot_isid, i32, C.c_int32)
     s.bin_prodchargesum = ptr(T.bin_prodchargesum, f64, C.c_double)
+    if getattr(T, "bodysegm", None) is not None:
+        s.bodysegm = ptr(T.bodysegm, i64, C.c_int64)
+        s.body_spacerot = ptr(T.body_spacerot, f64, C.c_double)
+        s.body_timerev = ptr(T.body_timerev, i64, C.c_int64)
     return s, keep

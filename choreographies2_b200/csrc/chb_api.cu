@@ -27,6 +27,7 @@
 #include "chb_fused4.cuh"
 #include "chb_fused5.cuh"
 #include "chb_ode.cuh"
+#include "chb_post.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // errors
@@ -64,6 +65,10 @@ struct HostTables {
         alg_timerev, bodyloop, seg_body, seg_iintrel, seg_timerev, bin_src, bin_tgt;
     std::vector<int32_t> shortcut, co_in, seg_isid, bin_isid;
     std::vector<double> loopmass, basis, alg_rot, seg_rot, bin_rot, bin_fac;
+    // ABI 2 (optional): per (body, interval) tables of the post-solve reductions
+    std::vector<int64_t> bodysegm, body_timerev;
+    std::vector<double> body_rot;
+    int vel = 0;  // velocity plan: basis * i, rotations * TimeRev, every loop GENERAL_SYM, changevar_mom_vel scaling
 };
 
 struct chb_plan {
@@ -104,6 +109,10 @@ struct chb_plan {
     ChfSys fsys;            // fused path (valid when fused_active)
     int fused_threads = 0;
     size_t fused_smem = 0;
+    chb_plan *vel_plan = nullptr;  // sibling plan of params_to_segmvel (same nint level), owned by this plan
+    ChbBodyTab body;               // device copies of the body tables (valid when body.nbody > 0)
+    const long long *d_pos_off = nullptr;  // [nloop + 1] offsets of the loops in position-parameter space (params_changevar)
+    long long nparams_incl_o = 0;
     int fused5_active = 0;  // the level is served by the general fused kernel (chb_fused5.cuh) instead of versions 3 / 4
     Ch5Sys f5;              // passed by value (constant bank) to k_fused5
 };
@@ -247,6 +256,12 @@ extern "C" int chb_plan_create(const chb_tables *t, int device, chb_plan **out) 
     copy_in(T.bin_rot, t->bin_spacerot, (size_t)T.nbin * G * G);
     copy_in(T.bin_isid, t->bin_spacerot_isid, T.nbin);
     copy_in(T.bin_fac, t->bin_prodchargesum, T.nbin);
+    if (t->bodysegm && t->body_spacerot && t->body_timerev) {
+        const size_t nbi = (size_t)T.nbody * T.nint_min;
+        copy_in(T.bodysegm, t->bodysegm, nbi);
+        copy_in(T.body_timerev, t->body_timerev, nbi);
+        copy_in(T.body_rot, t->body_spacerot, nbi * G * G);
+    }
     // consistency checks (the reference would hit undefined behaviour instead, asserts compiled out: setup.py:237-239)
     std::string err;
     for (int il = 0; il < nl && err.empty(); ++il) {
@@ -280,6 +295,10 @@ extern "C" int chb_plan_create(const chb_tables *t, int device, chb_plan **out) 
         if (T.bin_src[b] < 0 || T.bin_src[b] >= T.nsegm || T.bin_tgt[b] < 0 || T.bin_tgt[b] >= T.nsegm)
             err = "BinSourceSegm/BinTargetSegm out of range";
     }
+    for (size_t k = 0; k < T.bodysegm.size() && err.empty(); ++k) {
+        if (T.bodysegm[k] < 0 || T.bodysegm[k] >= T.nsegm) err = "bodysegm out of range";
+        else if (T.body_timerev[k] != 1 && T.body_timerev[k] != -1) err = "body TimeRev must be +-1";
+    }
     if (!err.empty()) {
         delete p;
         return chb_fail(CHB_ERR_INVALID_ARGUMENT, "chb_plan_create: " + err);
@@ -302,6 +321,8 @@ extern "C" int chb_plan_create(const chb_tables *t, int device, chb_plan **out) 
 
 extern "C" int chb_plan_destroy(chb_plan *p) {
     if (!p) return CHB_OK;
+    if (p->vel_plan) chb_plan_destroy(p->vel_plan);
+    p->vel_plan = nullptr;
     free_level(p);
     if (p->stage_dev) dev_free(p->stage_dev);
 #ifndef CHB_HOSTSIM
@@ -593,6 +614,21 @@ static int fused_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_
 }
 
 
+// factors of N for the general fused kernel, LARGEST radix first: the table of a DIF stage has (L / r) * nbase(r) entries, so
+// the long first stages get the big radices and the tables of all stages fit in shared memory up to N of about 10^4
+static bool ch5_factorize(int N, std::vector<int> &fac) {
+    fac.clear();
+    int m = N, e2 = 0;
+    while (m % 2 == 0) { m /= 2; ++e2; }
+    for (; e2 >= 4; e2 -= 4) fac.push_back(16);
+    if (e2 == 3) fac.push_back(8);
+    if (e2 == 2) fac.push_back(4);
+    if (e2 == 1) fac.push_back(2);
+    for (int q : {7, 5, 3})
+        while (m % q == 0) { fac.push_back(q); m /= q; }
+    return m == 1 && !fac.empty() && (int)fac.size() <= CHF_MAX_FAC;
+}
+
 // ---- general fused path planning (chb_fused5.cuh) ----------------------------------------------------
 // returns 1 when k_fused5 can serve this level (and fills p->f5), 0 when not, <0 on error
 static int fused5_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_size, int segm_store) {
@@ -633,7 +669,7 @@ static int fused5_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm
         f.N = 2 * L.npr;
         f.npr = L.npr;
         std::vector<int> fac;
-        if (!chf_factorize(f.N, fac)) return 0;
+        if (!ch5_factorize(f.N, fac)) return 0;
         f.nfac = (int)fac.size();
         for (int i = 0; i < f.nfac; ++i) f.fac[i] = fac[i];
         f.swm = (f.N % 16 == 0) ? 15 : 0;
@@ -744,6 +780,31 @@ static int fused5_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm
             Lcur = Lp;
         }
     }
+    {   // shared-memory copies of the stage tables, smallest first, while they fit behind the loop buffers
+        struct Item { int il, s, len; };
+        std::vector<Item> items;
+        for (auto &kv : first_loop_of_N) {
+            const ChfLoop &f = F.loops[kv.second].f;
+            for (int i = 0; i < f.nfac; ++i)
+                if (f.tw_len[i] > 0) items.push_back({kv.second, i, f.tw_len[i]});
+        }
+        std::sort(items.begin(), items.end(), [](const Item &a, const Item &b) { return a.len < b.len; });
+        size_t room = p->smem_limit > p->fused_smem + 1024 ? (p->smem_limit - p->fused_smem - 1024) / sizeof(cd) : 0;
+        int off = 0;
+        for (const Item &it : items) {
+            if ((size_t)it.len > room) break;
+            F.loops[it.il].f.tw_soff[it.s] = off;
+            off += it.len;
+            room -= it.len;
+        }
+        for (int il = 0; il < T.nloop; ++il) {  // loops of equal length share the tables
+            const int src = first_loop_of_N[F.loops[il].f.N];
+            for (int i = 0; i < F.loops[il].f.nfac; ++i) F.loops[il].f.tw_soff[i] = F.loops[src].f.tw_soff[i];
+        }
+        F.tw_smem_off = (int)smem_cd;
+        F.tw_smem_len = off;
+        p->fused_smem += (size_t)off * sizeof(cd);
+    }
     return 1;
 }
 
@@ -784,6 +845,9 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
         L.stride = L.npr + 1;
         L.mom_off = mom_off;
         L.loopmul = 1.0 / sqrt((double)T.loopnb[il] * T.loopmass[il] * 4.0 * M_PI * M_PI);
+        L.vel = T.vel;
+        L.velmul = 1.0 / sqrt((double)T.loopnb[il] * T.loopmass[il]);
+        L.invmass = 1.0 / T.loopmass[il];
         int ncor = 0;
         for (int j = 0; j < L.nppl; ++j) {
             int keep = 1;
@@ -935,6 +999,7 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
                 B.tgt = (int)T.bin_tgt[b];
                 B.isid = T.bin_isid[b] ? 1 : 0;
                 B.fac = T.bin_fac[b];
+                B.pad = b;  // position of the interaction in the caller's order (chb_path_stats_dev)
                 for (int i = 0; i < G * G; ++i) B.rot[i] = T.bin_rot[(size_t)b * G * G + i];
                 bins.push_back(B);
             }
@@ -962,6 +1027,32 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
     if (!rc) rc = level_upload(p, round_off, &S.round_off);
     if (rc) { free_level(p); return rc; }
     p->h_loops = loops;
+    {   // position-parameter offsets (params_changevar) and the body tables of the post-solve reductions
+        std::vector<long long> pos_off(nl + 1, 0);
+        for (int il = 0; il < nl; ++il) pos_off[il + 1] = pos_off[il] + (long long)loops[il].npr * loops[il].C;
+        p->nparams_incl_o = 2 * pos_off[nl];
+        rc = level_upload(p, pos_off, &p->d_pos_off);
+        memset(&p->body, 0, sizeof(p->body));
+        if (!rc && !T.bodysegm.empty()) {
+            const size_t nbi = (size_t)T.nbody * T.nint_min;
+            std::vector<int> bs(nbi), tr(nbi);
+            std::vector<double> mass(T.nbody);
+            double tot = 0.0;
+            for (size_t k = 0; k < nbi; ++k) { bs[k] = (int)T.bodysegm[k]; tr[k] = (int)T.body_timerev[k]; }
+            for (int ib = 0; ib < T.nbody; ++ib) {
+                mass[ib] = T.loopmass[T.bodyloop[ib]];
+                tot += mass[ib] * T.nint_min;
+            }
+            rc = level_upload(p, bs, &p->body.bodysegm);
+            if (!rc) rc = level_upload(p, tr, &p->body.timerev);
+            if (!rc) rc = level_upload(p, T.body_rot, &p->body.rot);
+            if (!rc) rc = level_upload(p, mass, &p->body.bodymass);
+            p->body.nbody = T.nbody;
+            p->body.nint_min = T.nint_min;
+            p->body.totmass = tot;
+        }
+        if (rc) { free_level(p); return rc; }
+    }
 
     // ---- launch geometry ----
     // transform kernels: FFT buffer in shared memory when it fits, else in the per-state global scratch
@@ -1032,9 +1123,10 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
     {
         int rcf = fused_setup(p, loops, segm_size);
         if (rcf < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: fused setup failed"); }
+        if (T.vel) rcf = 0;  // velocity plans run the staged kernels (their scaling is not in the fused load passes)
         p->fused_active = rcf;
         p->fused5_active = 0;
-        if (!rcf) {  // layouts versions 3 / 4 refuse: the general fused kernel
+        if (!rcf && !T.vel) {  // layouts versions 3 / 4 refuse: the general fused kernel
             int rc5 = fused5_setup(p, loops, segm_size, segm_store);
             if (rc5 < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: fused setup failed"); }
             if (getenv("CHB_FUSED5") && atoi(getenv("CHB_FUSED5")) == 0) rc5 = 0;  // A/B knob
@@ -1043,6 +1135,44 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
         }
         p->ready = true;
     }
+    if (p->vel_plan) {  // the sibling plan follows the level
+        int rcv = chb_plan_set_nint(p->vel_plan, nint);
+        if (rcv) return rcv;
+    }
+    return CHB_OK;
+}
+
+// velocity plan of params_to_segmvel (:6050-6118): the position plan with basis * i (:852-854), every loop on the GENERAL_SYM path
+// (the velocity basis is never the identity, :1451-1466), segment and Adjust_after_last_gen rotations multiplied by their TimeRev
+// (TimeDerivative, _ActionSym.pyx:268-291) and the scaling of changevar_mom_vel (:4830-4914)
+static int ensure_vel_plan(chb_plan *p) {
+    if (p->vel_plan) return CHB_OK;
+    chb_plan *v = new chb_plan();
+    v->device = p->device;
+    v->T = p->T;
+    HostTables &T = v->T;
+    T.vel = 1;
+    const int G = T.G;
+    for (size_t j = 0; j + 1 < T.basis.size(); j += 2) {
+        const double re = T.basis[j], im = T.basis[j + 1];
+        T.basis[j] = -im;
+        T.basis[j + 1] = re;
+    }
+    for (int il = 0; il < T.nloop; ++il) {
+        T.shortcut[il] = CHB_GENERAL_SYM;
+        for (int i = 0; i < G * G; ++i) T.alg_rot[(size_t)il * G * G + i] *= (double)T.alg_timerev[il];
+    }
+    for (int s = 0; s < T.nsegm; ++s) {
+        for (int i = 0; i < G * G; ++i) T.seg_rot[(size_t)s * G * G + i] *= (double)T.seg_timerev[s];
+        if (T.seg_timerev[s] < 0) T.seg_isid[s] = 0;
+    }
+    v->smem_limit = p->smem_limit;
+    v->num_sms = p->num_sms;
+    v->chunk_user = p->chunk_user;
+    memset(&v->sys, 0, sizeof(v->sys));
+    int rc = chb_plan_set_nint(v, p->nint);
+    if (rc) { chb_plan_destroy(v); return rc; }
+    p->vel_plan = v;
     return CHB_OK;
 }
 
@@ -1061,6 +1191,7 @@ extern "C" int chb_plan_query(const chb_plan *p, int what, int64_t *v) {
         case CHB_Q_SEGM_SIZE: *v = p->sys.segm_size; break;
         case CHB_Q_SEGM_STORE: *v = p->sys.segm_store; break;
         case CHB_Q_SEGMPOS_SIZE: *v = p->sys.segsz; break;
+        case CHB_Q_NPARAMS_INCL_O: *v = p->nparams_incl_o; break;
 #ifdef CHB_HOSTSIM
         case CHB_Q_HOST_POINTERS: *v = 1; break;
 #else
@@ -1146,6 +1277,8 @@ extern "C" int chb_workspace_bytes(const chb_plan *p, int64_t batch, size_t *out
     CHB_REQUIRE(p && out && batch >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_workspace_bytes: bad argument");
     CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_workspace_bytes: call chb_plan_set_nint first");
     *out = ws_bytes_for(p, plan_chunk(p, batch)) + 256;
+    if (p->vel_plan && p->vel_plan->ready)  // chb_params_to_segmvel_dev runs on the sibling plan with the same workspace
+        *out = std::max(*out, ws_bytes_for(p->vel_plan, plan_chunk(p->vel_plan, batch)) + 256);
     return CHB_OK;
 }
 
@@ -1650,6 +1783,7 @@ CHB_KERNEL void CHF_BOUNDS k_fused5(CH5_SYS_PARAM, ChfArgs A) {
     double *red = (double *)CHB_SMEM;
     cd *bnd = (cd *)(CHB_SMEM + sizeof(double) * CHF_MAX_THREADS);  // 1 KB behind the partial sums
     cd *sm = (cd *)(CHB_SMEM + CHF_RED_BYTES);
+    cta_fused5_prologue(ctx, F, sm);
     const long long nwork = A.live_list ? (long long)*A.live_count : A.nstates;
     for (long long k = CHB_BLOCK_ID; k < nwork; k += CHB_GRID_DIM) {
         const long long b = A.live_list ? (long long)A.live_list[k] : k;
@@ -2221,6 +2355,145 @@ extern "C" int chb_gmres_solution_dev(chb_plan *p, int64_t batch, int64_t n, int
     return CHB_OK;
 }
 
+
+// ---- post-solve reductions and small diagonal operators (chb_post.cuh), one CTA per state --------------------------
+CHB_KERNEL void k_hash_multi(ChbSys S, ChbHashExp H, const double *seg, double *hash) {
+    CHB_CTX_DECL;
+    const long long b = CHB_BLOCK_ID;
+    cta_hash_multi(ctx, S, H, seg + b * S.segsz, hash + b * H.n, (double *)CHB_SMEM);
+}
+CHB_KERNEL void k_center_of_mass(ChbSys S, ChbBodyTab T, const double *seg, double *com) {
+    CHB_CTX_DECL;
+    const long long b = CHB_BLOCK_ID;
+    double *part = (double *)CHB_SMEM;
+    cta_center_of_mass(ctx, S, T, seg + b * S.segsz, com + b * S.G, part, part + (size_t)2 * CHB_MAX_G * CHB_NTHREADS);
+}
+CHB_KERNEL void k_detect_escape(ChbSys S, ChbBodyTab T, const double *seg, double fac, int *flag) {
+    CHB_CTX_DECL;
+    const long long b = CHB_BLOCK_ID;
+    double *part = (double *)CHB_SMEM;
+    double *mm = part + (size_t)2 * CHB_MAX_G * CHB_NTHREADS;
+    double *box = mm + (size_t)2 * CHB_MAX_G * S.nsegm;
+    cta_detect_escape(ctx, S, T, seg + b * S.segsz, fac, flag + b, part, mm, box);
+}
+CHB_KERNEL void k_path_stats(ChbSys S, int nint_min, const double *seg, const double *vel, double *loop_len, double *bin_min) {
+    CHB_CTX_DECL;
+    const long long b = CHB_BLOCK_ID;
+    double *part = (double *)CHB_SMEM;
+    cta_path_stats(ctx, S, nint_min, seg + b * S.segsz, vel + b * S.segsz, loop_len + b * S.nloop, bin_min + b * S.nbin, part,
+                   part + CHB_NTHREADS);
+}
+CHB_KERNEL void k_changevar(ChbSys S, const long long *pos_off, int mode, long long n_in, long long n_out, const double *in,
+                            double *out) {
+    CHB_CTX_DECL;
+    const long long b = CHB_BLOCK_ID;
+    cta_changevar(ctx, S, pos_off, mode, in + b * n_in, out + b * n_out);
+}
+// out[v][s*G + d][j] = mom[v][s*G + d][j] / segment mass  (Compute_velocities_vectorized / Compute_grad_velocities_vectorized)
+CHB_KERNEL void k_scale_segm(ChbSys S, long long total, long long inner, const double *mom, double *out) {
+#ifndef CHB_HOSTSIM
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+#else
+    for (long long e = sim_block_id * sim_nthreads; e < total && e < (sim_block_id + 1) * sim_nthreads; ++e) {
+#endif
+        const int s = (int)(((e / inner) / S.G) % S.nsegm);
+        const ChbLoop &L = S.loops[S.segs[s].loop];
+        out[e] = mom[e] * L.invmass;
+    }
+}
+
+#define CHB_POST_PROLOGUE(name)                                                                   \
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, name ": NULL plan");                                 \
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, name ": call chb_plan_set_nint first");              \
+    CHB_REQUIRE(batch >= 0, CHB_ERR_INVALID_ARGUMENT, name ": negative batch");                   \
+    if (batch == 0) return CHB_OK;                                                                \
+    const ChbSys &S = p->sys;                                                                     \
+    chb_stream_t st = (chb_stream_t)stream;                                                       \
+    (void)S; (void)st;                                                                            \
+    CHB_SET_DEVICE();
+
+extern "C" int chb_params_to_segmvel_dev(chb_plan *p, int64_t batch, const double *params, double *segmvel, void *ws,
+                                         size_t ws_bytes, void *stream) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_segmvel_dev: NULL plan");
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_params_to_segmvel_dev: call chb_plan_set_nint first");
+    CHB_TRY(ensure_vel_plan(p));  // before the empty-batch return: a call with batch 0 makes chb_workspace_bytes cover this operator
+    return chb_params_to_segmpos_dev(p->vel_plan, batch, params, segmvel, ws, ws_bytes, stream);
+}
+
+extern "C" int chb_params_changevar_dev(chb_plan *p, int64_t batch, const double *in, int inv, int transpose, double *out,
+                                        void *stream) {
+    CHB_POST_PROLOGUE("chb_params_changevar_dev");
+    CHB_REQUIRE(in && out, CHB_ERR_INVALID_ARGUMENT, "chb_params_changevar_dev: NULL array");
+    const int mode = (inv ? 1 : 0) + (transpose ? 2 : 0);
+    const bool to_pos = (mode == 0 || mode == 3);
+    const long long n_in = to_pos ? S.nparams : p->nparams_incl_o, n_out = to_pos ? p->nparams_incl_o : S.nparams;
+    CHB_LAUNCH(p, k_changevar, batch, 256, 0, st, S, p->d_pos_off, mode, n_in, n_out, in, out);
+    return CHB_OK;
+}
+
+extern "C" int chb_segmpos_to_hash_multi_dev(chb_plan *p, int64_t batch, const double *segmpos, int nexp, const double *exponents,
+                                             double *hash, void *stream) {
+    CHB_POST_PROLOGUE("chb_segmpos_to_hash_multi_dev");
+    CHB_REQUIRE(segmpos && exponents && hash, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_to_hash_multi_dev: NULL array");
+    CHB_REQUIRE(nexp >= 1 && nexp <= CHB_MAX_HASH, CHB_ERR_UNSUPPORTED, "chb_segmpos_to_hash_multi_dev: 1 <= nexp <= 16");
+    ChbHashExp H;
+    H.n = nexp;
+    for (int e = 0; e < CHB_MAX_HASH; ++e) H.e[e] = e < nexp ? exponents[e] : 0.0;
+    CHB_LAUNCH(p, k_hash_multi, batch, CHB_POST_THREADS, sizeof(double) * CHB_MAX_HASH * CHB_POST_THREADS, st, S, H, segmpos, hash);
+    return CHB_OK;
+}
+
+extern "C" int chb_center_of_mass_dev(chb_plan *p, int64_t batch, const double *segmpos, double *com, void *stream) {
+    CHB_POST_PROLOGUE("chb_center_of_mass_dev");
+    CHB_REQUIRE(segmpos && com, CHB_ERR_INVALID_ARGUMENT, "chb_center_of_mass_dev: NULL array");
+    CHB_REQUIRE(p->body.nbody > 0, CHB_ERR_UNSUPPORTED, "chb_center_of_mass_dev: the plan was created without the body tables (bodysegm, body_spacerot, body_timerev)");
+    for (size_t k = 0; k < p->T.body_timerev.size(); ++k)
+        CHB_REQUIRE(p->T.body_timerev[k] > 0 || S.segm_store > S.segm_size, CHB_ERR_INVALID_ARGUMENT,
+                    "chb_center_of_mass_dev: a time-reversed body segment needs segm_store = segm_size + 1");
+    const size_t smem = sizeof(double) * ((size_t)2 * CHB_MAX_G * CHB_POST_THREADS + (size_t)2 * CHB_MAX_G * S.nsegm);
+    CHB_LAUNCH(p, k_center_of_mass, batch, CHB_POST_THREADS, smem, st, S, p->body, segmpos, com);
+    return CHB_OK;
+}
+
+extern "C" int chb_detect_escape_dev(chb_plan *p, int64_t batch, const double *segmpos, double fac, int32_t *escaped, void *stream) {
+    CHB_POST_PROLOGUE("chb_detect_escape_dev");
+    CHB_REQUIRE(segmpos && escaped, CHB_ERR_INVALID_ARGUMENT, "chb_detect_escape_dev: NULL array");
+    CHB_REQUIRE(p->body.nbody > 0, CHB_ERR_UNSUPPORTED, "chb_detect_escape_dev: the plan was created without the body tables (bodysegm, body_spacerot, body_timerev)");
+    CHB_REQUIRE(p->body.nbody <= CHB_MAX_BODY, CHB_ERR_UNSUPPORTED, "chb_detect_escape_dev: more than 64 bodies");
+    const size_t smem = sizeof(double) * ((size_t)2 * CHB_MAX_G * CHB_POST_THREADS + (size_t)2 * CHB_MAX_G * S.nsegm +
+                                          (size_t)(CHB_MAX_G + 1) * p->body.nbody);
+    CHB_LAUNCH(p, k_detect_escape, batch, CHB_POST_THREADS, smem, st, S, p->body, segmpos, fac, (int *)escaped);
+    return CHB_OK;
+}
+
+extern "C" int chb_path_stats_dev(chb_plan *p, int64_t batch, const double *segmpos, const double *segmvel, double *loop_len,
+                                  double *bin_dx_min, void *stream) {
+    CHB_POST_PROLOGUE("chb_path_stats_dev");
+    CHB_REQUIRE(segmpos && segmvel && loop_len && bin_dx_min, CHB_ERR_INVALID_ARGUMENT, "chb_path_stats_dev: NULL array");
+    const size_t smem = sizeof(double) * ((size_t)CHB_POST_THREADS + S.nsegm);
+    CHB_LAUNCH(p, k_path_stats, batch, CHB_POST_THREADS, smem, st, S, p->T.nint_min, segmpos, segmvel, loop_len, bin_dx_min);
+    return CHB_OK;
+}
+
+extern "C" int chb_compute_velocities_dev(chb_plan *p, int64_t nvec, int64_t grad_ndof, const double *mom, double *out, void *stream) {
+    const int64_t batch = nvec;
+    CHB_POST_PROLOGUE("chb_compute_velocities_dev");
+    CHB_REQUIRE(grad_ndof >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_compute_velocities_dev: negative grad_ndof");
+    CHB_REQUIRE(mom && out, CHB_ERR_INVALID_ARGUMENT, "chb_compute_velocities_dev: NULL array");
+    const long long inner = grad_ndof > 0 ? grad_ndof : 1;
+    const long long total = (long long)nvec * S.nsegm * S.G * inner;
+    const long long grid = std::min<long long>((total + 255) / 256, (long long)p->num_sms * 8);
+#ifdef CHB_HOSTSIM
+    const long long grid_sim = (total + 255) / 256;
+    CHB_LAUNCH(p, k_scale_segm, grid_sim, 256, 0, st, S, total, inner, mom, out);
+    (void)grid;
+#else
+    CHB_LAUNCH(p, k_scale_segm, grid, 256, 0, st, S, total, inner, mom, out);
+#endif
+    return CHB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // memory helpers + host-pointer operators
 // ------------------------------------------------------------------------------------------------
@@ -2408,7 +2681,8 @@ static int host_op_shapes(const chb_plan *p, int op, bool have_out0, size_t *n_i
     const size_t np = (size_t)p->sys.nparams, ns = (size_t)p->sys.segsz;
     *n_in0 = *n_in1 = *n_out0 = *n_out1 = 0;
     switch (op) {
-        case CHB_OP_PARAMS_TO_SEGMPOS: *n_in0 = np; *n_out0 = ns; break;
+        case CHB_OP_PARAMS_TO_SEGMPOS:
+        case CHB_OP_PARAMS_TO_SEGMVEL: *n_in0 = np; *n_out0 = ns; break;
         case CHB_OP_SEGMPOS_TO_PARAMS:
         case CHB_OP_SEGMPOS_TO_PARAMS_T: *n_in0 = ns; *n_out0 = np; break;
         case CHB_OP_ACTION: *n_in0 = np; *n_out0 = 1; break;
@@ -2431,6 +2705,7 @@ static int host_op_dispatch(chb_plan *p, int op, int64_t nb, const double *d_in0
                             double *d_out0, double *d_out1, bool have_out0, void *d_ws, size_t wsb, void *st) {
     switch (op) {
         case CHB_OP_PARAMS_TO_SEGMPOS: return chb_params_to_segmpos_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
+        case CHB_OP_PARAMS_TO_SEGMVEL: return chb_params_to_segmvel_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
         case CHB_OP_SEGMPOS_TO_PARAMS: return chb_segmpos_to_params_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
         case CHB_OP_SEGMPOS_TO_PARAMS_T: return chb_segmpos_to_params_T_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
         case CHB_OP_ACTION: return chb_params_to_action_dev(p, nb, d_in0, d_out0, d_ws, wsb, st);
@@ -2460,6 +2735,7 @@ extern "C" int chb_run_host(chb_plan *p, int op, int64_t batch, const double *in
     CHB_REQUIRE(batch >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_run_host: negative batch");
     if (batch == 0) return CHB_OK;
     std::lock_guard<std::mutex> lock(p->host_mutex);
+    if (op == CHB_OP_PARAMS_TO_SEGMVEL) CHB_TRY(ensure_vel_plan(p));  // before the workspace query below
     size_t n_in0, n_in1, n_out0, n_out1;
     const bool have_out0 = out0 != nullptr;
     CHB_TRY(host_op_shapes(p, op, have_out0, &n_in0, &n_in1, &n_out0, &n_out1));

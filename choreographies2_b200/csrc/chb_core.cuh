@@ -72,6 +72,9 @@ struct ChbLoop {
     int co_in[CHB_MAX_NPPL];
     int nnz_k[CHB_MAX_NNZ];
     double loopmul;  // 1/sqrt(loopnb*loopmass*4pi^2)
+    int vel;         // velocity plan (changevar_mom_vel, 4830-4914): scale velmul for k > 0, 0 for k = 0
+    double velmul;   // 1/sqrt(loopnb*loopmass)
+    double invmass;  // 1/loopmass (Compute_velocities: momentum -> velocity of the loop's segments)
     double bre[CHB_MAX_G][CHB_MAX_C], bim[CHB_MAX_G][CHB_MAX_C];
     int has_alg, alg_src;  // Adjust_after_last_gen: extra row 2*npr built from row alg_src
     double alg_rot[CHB_MAX_G * CHB_MAX_G];
@@ -155,6 +158,7 @@ CHB_HD double chb_scale(const ChbLoop &L, int n, int c, int *kout) {
     int ik = c / L.nppl;
     int k = n * L.ncm + L.nnz_k[ik];
     *kout = k;
+    if (L.vel) return k > 0 ? L.velmul : 0.0;
     return k > 0 ? L.loopmul / (double)k : L.loopmul;
 }
 

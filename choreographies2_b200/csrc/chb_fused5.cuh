@@ -47,7 +47,8 @@ struct Ch5Loop {
     const cd *gen_tw;      // [npr + 1][nnz] exp(-2 pi i m nnz_k / nint)
 };
 struct Ch5Sys {
-    int nloop, nseg, T, segm_size, segm_store, law_kind, pair_fast, pad;
+    int nloop, nseg, T, segm_size, segm_store, law_kind;
+    int tw_smem_off, tw_smem_len;  // twiddle region (cd slots behind the loop buffers), filled once per persistent CTA
     long long nparams, segsz;
     double law[4];
     Ch5Loop loops[CHF_MAX_LOOPS];
@@ -131,53 +132,113 @@ CHB_D void ch5_rfft_store(Grp &grp, const ChfLoop &L, const cd *buf, const doubl
 
 // ------------------------------------------------------------------------------------------------
 // GENERAL loop: parameters -> packed real sequences (natural order), forward FFTs, combine -> rows
+// CP = C / 2 complex sequences at compile time (1: dihedral classes, 2: k-fold / forced general layouts; 0: run-time count)
 // ------------------------------------------------------------------------------------------------
-template <class Grp>
-CHB_D void ch5_general_forward(Grp &grp, const Ch5Loop &L, const double *vec_b, cd *buf, double *red, bool want_kin) {
-    const int N = L.f.N, npr = L.f.npr, C = L.C;
+template <int CP>
+struct Ch5Basis {  // the loop's basis and mirror factors in registers for the combine passes
+    double bre[2][CP > 0 ? 2 * CP : CH5_MAX_C], bim[2][CP > 0 ? 2 * CP : CH5_MAX_C];
+    cd wmir[CP > 0 ? 2 * CP : CH5_MAX_C];
+    int ik[CP > 0 ? 2 * CP : CH5_MAX_C];
+    CHB_HD void init(const Ch5Loop &L) {
+        const int C = CP > 0 ? 2 * CP : L.C;
+#pragma unroll
+        for (int c = 0; c < (CP > 0 ? 2 * CP : CH5_MAX_C); ++c) {
+            if (c >= C) break;
+            ik[c] = c / L.nppl;
+            wmir[c] = L.wmir[ik[c]];
+#pragma unroll
+            for (int g = 0; g < 2; ++g) { bre[g][c] = L.bre[g][c]; bim[g][c] = L.bim[g][c]; }
+        }
+    }
+};
+
+// one row n >= 1 of the parameter array: C values at rows[n C ..], harmonic k_c = n ncm + nnz_k[c / nppl] > 0
+template <int CP, class Grp>
+CHB_D void ch5_general_load(Grp &grp, const Ch5Loop &L, const double *vec_b, cd *buf, double *red, bool want_kin) {
+    const int npr = L.f.npr, C = CP > 0 ? 2 * CP : L.C, Cp = CP > 0 ? CP : L.Cp;
     grp.par([&](int tid, int T) {
         double kin = 0.0;
-        for (int idx = tid; idx < npr * C; idx += T) {
-            const int n = idx / C, c = idx - n * C;
-            int kk;
-            const double sc = ch5_scale(L, n, c, &kk);
-            const long long im = ch5_mom_index(L, n, c);
-            const double p = im >= 0 ? vec_b[im] : 0.0;
-            if (kk > 0) kin += p * p;
-            double v = p * sc;
-            if (n == 0 && L.has_k0 && c < L.nppl) v *= 0.5;  // :5389-5392
-            ((double *)(buf + (c >> 1) * L.seq_stride + chf_swz(n, L.f.swm)))[c & 1] = v;
-        }
-        for (int idx = tid; idx < npr * L.Cp; idx += T) {  // zero padding of the second half
-            const int P = idx / npr, n = npr + (idx - P * npr);
-            buf[P * L.seq_stride + chf_swz(n, L.f.swm)] = mk(0.0, 0.0);
+        const double *rows = vec_b + L.f.mom_off - L.f.nco_in;
+        const double lm = L.f.loopmul;
+        const int ncm = L.f.ncm, nppl = L.nppl, swm = L.f.swm, stride = L.seq_stride;
+        for (int n = tid; n < npr; n += T) {
+            const int sl = chf_swz(n, swm), sz = chf_swz(npr + n, swm);
+            if (n == 0) {  // row 0: removed zero-frequency parameters, halved zero-frequency terms (:5389-5392)
+                for (int P = 0; P < Cp; ++P) {
+                    double v[2];
+                    for (int h = 0; h < 2; ++h) {
+                        const int c = 2 * P + h;
+                        int kk;
+                        const double sc = ch5_scale(L, 0, c, &kk);
+                        const long long im = ch5_mom_index(L, 0, c);
+                        const double p = im >= 0 ? vec_b[im] : 0.0;
+                        if (kk > 0) kin += p * p;
+                        v[h] = p * sc;
+                        if (L.has_k0 && c < nppl) v[h] *= 0.5;
+                    }
+                    buf[P * stride + sl] = mk(v[0], v[1]);
+                    buf[P * stride + sz] = mk(0.0, 0.0);
+                }
+                continue;
+            }
+            const double *r = rows + (long long)n * C;
+            double sc_prev = 0.0;
+            int ik_prev = -1;
+#pragma unroll
+            for (int P = 0; P < (CP > 0 ? CP : CH5_MAX_C / 2); ++P) {
+                if (P >= Cp) break;
+                double v[2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int c = 2 * P + h, ik = c / nppl;
+                    if (ik != ik_prev) {
+                        sc_prev = lm * chf_rcp((double)(n * ncm + L.nnz_k[ik]));
+                        ik_prev = ik;
+                    }
+                    const double p = r[c];
+                    kin = fma(p, p, kin);
+                    v[h] = p * sc_prev;
+                }
+                buf[P * stride + sl] = mk(v[0], v[1]);
+                buf[P * stride + sz] = mk(0.0, 0.0);  // zero padding of the second half
+            }
         }
         if (want_kin) red[grp.g * T + tid] += 0.5 * kin;
     });
-    for (int P = 0; P < L.Cp; ++P) chf_fft_time_to_spec(grp, buf + P * L.seq_stride, L.f);
-    // combine: rows m and 2 npr - m from F_c[m]
+}
+
+template <int CP, class Grp>
+CHB_D void ch5_general_combine(Grp &grp, const Ch5Loop &L, cd *buf) {
+    const int N = L.f.N, npr = L.f.npr, Cp = CP > 0 ? CP : L.Cp;
     grp.par([&](int tid, int T) {
+        Ch5Basis<CP> Bs;
+        Bs.init(L);
+        const int swm = L.f.swm, stride = L.seq_stride, nnz = L.nnz;
+        const int *rev = L.f.rev;
+        const bool sub1 = L.n_sub_fft == 1, twt = L.tw_trivial != 0;
         for (int m = tid; m <= npr; m += T) {
-            const int s1 = chf_swz(L.f.rev[m], L.f.swm);
-            const int m2 = (m == 0) ? 0 : N - m;
-            const int s2 = chf_swz(L.f.rev[m2], L.f.swm);
+            const int s1 = chf_swz(rev[m], swm);
+            const int s2 = chf_swz(rev[m == 0 ? 0 : N - m], swm);
             cd x = mk(0.0, 0.0), xm = mk(0.0, 0.0);
-            const bool mir = L.n_sub_fft == 1 && m > 0 && m < npr;
-            for (int P = 0; P < L.Cp; ++P) {
-                const cd A = buf[P * L.seq_stride + s1], Bq = buf[P * L.seq_stride + s2];
-                // F_2P = (A + conj B) / 2, F_2P+1 = (A - conj B) / 2i
+            const bool mir = sub1 && m > 0 && m < npr;
+#pragma unroll
+            for (int P = 0; P < (CP > 0 ? CP : CH5_MAX_C / 2); ++P) {
+                if (P >= Cp) break;
+                const cd A = buf[P * stride + s1], Bq = buf[P * stride + s2];
+                // F_2P = (A + conj B) / 2, F_2P+1 = (A - conj B) / 2i ; the factor 2 of x = 2 Re(...) cancels the halves
                 cd F[2];
-                F[0] = mk(0.5 * (A.x + Bq.x), 0.5 * (A.y - Bq.y));
-                F[1] = mk(0.5 * (A.y + Bq.y), 0.5 * (Bq.x - A.x));
+                F[0] = mk(A.x + Bq.x, A.y - Bq.y);
+                F[1] = mk(A.y + Bq.y, Bq.x - A.x);
+#pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    const int c = 2 * P + h, ik = c / L.nppl;
-                    const cd W = L.tw_trivial ? F[h] : cmul(F[h], L.gen_tw[(long long)m * L.nnz + ik]);
-                    x.x += 2.0 * (L.bre[0][c] * W.x + L.bim[0][c] * W.y);
-                    x.y += 2.0 * (L.bre[1][c] * W.x + L.bim[1][c] * W.y);
+                    const int c = 2 * P + h;
+                    const cd W = twt ? F[h] : cmul(F[h], L.gen_tw[(long long)m * nnz + Bs.ik[c]]);
+                    x.x = fma(Bs.bre[0][c], W.x, fma(Bs.bim[0][c], W.y, x.x));
+                    x.y = fma(Bs.bre[1][c], W.x, fma(Bs.bim[1][c], W.y, x.y));
                     if (mir) {
-                        const cd V = cmul(L.wmir[ik], W);  // :5147-5175
-                        xm.x += 2.0 * (L.bre[0][c] * V.x - L.bim[0][c] * V.y);
-                        xm.y += 2.0 * (L.bre[1][c] * V.x - L.bim[1][c] * V.y);
+                        const cd V = cmul(Bs.wmir[c], W);  // :5147-5175
+                        xm.x = fma(Bs.bre[0][c], V.x, fma(-Bs.bim[0][c], V.y, xm.x));
+                        xm.y = fma(Bs.bre[1][c], V.x, fma(-Bs.bim[1][c], V.y, xm.y));
                     }
                 }
             }
@@ -187,63 +248,133 @@ CHB_D void ch5_general_forward(Grp &grp, const Ch5Loop &L, const double *vec_b, 
     });
 }
 
-// rows (gradient with respect to the slice, x + i y per row) -> Hermitian-packed spectra, inverse FFTs, parameter-space result
-template <class Grp>
-CHB_D void ch5_general_adjoint(Grp &grp, const Ch5Loop &L, cd *buf, const double *kin_b, double *out_b, double *red,
-                                bool want_kin) {
-    const int N = L.f.N, npr = L.f.npr, C = L.C;
+template <int CP, class Grp>
+CHB_D void ch5_general_combine_T(Grp &grp, const Ch5Loop &L, cd *buf) {
+    const int N = L.f.N, npr = L.f.npr, Cp = CP > 0 ? CP : L.Cp;
     grp.par([&](int tid, int T) {
+        Ch5Basis<CP> Bs;
+        Bs.init(L);
+        const int swm = L.f.swm, stride = L.seq_stride, nnz = L.nnz;
+        const int *rev = L.f.rev;
+        const bool sub1 = L.n_sub_fft == 1, twt = L.tw_trivial != 0;
         for (int m = tid; m <= npr; m += T) {
-            const int s1 = chf_swz(L.f.rev[m], L.f.swm);
-            const int m2 = (m == 0) ? 0 : N - m;
-            const int s2 = chf_swz(L.f.rev[m2], L.f.swm);
+            const int s1 = chf_swz(rev[m], swm);
+            const int s2 = chf_swz(rev[m == 0 ? 0 : N - m], swm);
             const bool end = (m == 0 || m == npr);
-            const bool mir = L.n_sub_fft == 1 && !end;
+            const bool mir = sub1 && !end;
             const cd P1 = buf[s1];
             const cd P2 = mir ? buf[s2] : mk(0.0, 0.0);
             const double alpha = end ? 2.0 : 1.0;  // :5102-5106 / :5260-5263
-            for (int P = 0; P < L.Cp; ++P) {
+#pragma unroll
+            for (int P = 0; P < (CP > 0 ? CP : CH5_MAX_C / 2); ++P) {
+                if (P >= Cp) break;
                 cd X[2];
+#pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    const int c = 2 * P + h, ik = c / L.nppl;
-                    cd B = mk(L.bre[0][c] * P1.x + L.bre[1][c] * P1.y, L.bim[0][c] * P1.x + L.bim[1][c] * P1.y);
+                    const int c = 2 * P + h;
+                    cd B = mk(Bs.bre[0][c] * P1.x + Bs.bre[1][c] * P1.y, Bs.bim[0][c] * P1.x + Bs.bim[1][c] * P1.y);
                     if (mir) {
-                        const cd B2 = mk(L.bre[0][c] * P2.x + L.bre[1][c] * P2.y, L.bim[0][c] * P2.x + L.bim[1][c] * P2.y);
-                        B = cadd(B, cmul(cconj(L.wmir[ik]), cconj(B2)));
+                        const cd B2 = mk(Bs.bre[0][c] * P2.x + Bs.bre[1][c] * P2.y, Bs.bim[0][c] * P2.x + Bs.bim[1][c] * P2.y);
+                        B = cadd(B, cmul(cconj(Bs.wmir[c]), cconj(B2)));
                     }
-                    if (!L.tw_trivial) B = cmul(cconj(L.gen_tw[(long long)m * L.nnz + ik]), B);
+                    if (!twt) B = cmul(cconj(L.gen_tw[(long long)m * nnz + Bs.ik[c]]), B);
                     X[h] = cscale(B, alpha);
                 }
                 if (end) {  // the c2r ignores the imaginary parts of the first and the last coefficient
-                    buf[P * L.seq_stride + s1] = mk(X[0].x, X[1].x);
+                    buf[P * stride + s1] = mk(X[0].x, X[1].x);
                 } else {
-                    buf[P * L.seq_stride + s1] = mk(X[0].x - X[1].y, X[0].y + X[1].x);  // X_2P + i X_2P+1
-                    buf[P * L.seq_stride + s2] = mk(X[0].x + X[1].y, X[1].x - X[0].y);  // conj X_2P + i conj X_2P+1
+                    buf[P * stride + s1] = mk(X[0].x - X[1].y, X[0].y + X[1].x);  // X_2P + i X_2P+1
+                    buf[P * stride + s2] = mk(X[0].x + X[1].y, X[1].x - X[0].y);  // conj X_2P + i conj X_2P+1
                 }
             }
         }
     });
-    for (int P = 0; P < L.Cp; ++P) chf_fft_spec_to_time(grp, buf + P * L.seq_stride, L.f);
+}
+
+template <int CP, class Grp>
+CHB_D void ch5_general_store(Grp &grp, const Ch5Loop &L, const cd *buf, const double *kin_b, double *out_b, double *red,
+                              bool want_kin) {
+    const int npr = L.f.npr, C = CP > 0 ? 2 * CP : L.C, Cp = CP > 0 ? CP : L.Cp;
     grp.par([&](int tid, int T) {
         double kin = 0.0;
-        for (int idx = tid; idx < npr * C; idx += T) {
-            const int n = idx / C, c = idx - n * C;
-            const long long im = ch5_mom_index(L, n, c);
-            if (im < 0) continue;
-            int kk;
-            const double sc = ch5_scale(L, n, c, &kk);
-            double x = ((const double *)(buf + (c >> 1) * L.seq_stride + chf_swz(n, L.f.swm)))[c & 1];
-            if (n == 0 && L.has_k0 && c < L.nppl) x *= 0.5;  // :5634-5641
-            double val = x * sc;
-            if (kin_b && kk > 0) {
-                const double p = kin_b[im];
-                kin += p * p;
-                val += p;
+        const long long off = L.f.mom_off - L.f.nco_in;
+        const double lm = L.f.loopmul;
+        const int ncm = L.f.ncm, nppl = L.nppl, swm = L.f.swm, stride = L.seq_stride;
+        for (int n = tid; n < npr; n += T) {
+            const int sl = chf_swz(n, swm);
+            if (n == 0) {
+                for (int c = 0; c < C; ++c) {
+                    const long long im = ch5_mom_index(L, 0, c);
+                    if (im < 0) continue;
+                    int kk;
+                    const double sc = ch5_scale(L, 0, c, &kk);
+                    double x = ((const double *)(buf + (c >> 1) * stride + sl))[c & 1];
+                    if (L.has_k0 && c < nppl) x *= 0.5;  // :5634-5641
+                    double val = x * sc;
+                    if (kin_b && kk > 0) {
+                        const double p = kin_b[im];
+                        kin += p * p;
+                        val += p;
+                    }
+                    out_b[im] = val;
+                }
+                continue;
             }
-            out_b[im] = val;
+            double sc_prev = 0.0;
+            int ik_prev = -1;
+#pragma unroll
+            for (int P = 0; P < (CP > 0 ? CP : CH5_MAX_C / 2); ++P) {
+                if (P >= Cp) break;
+                const cd y = buf[P * stride + sl];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int c = 2 * P + h, ik = c / nppl;
+                    if (ik != ik_prev) {
+                        sc_prev = lm * chf_rcp((double)(n * ncm + L.nnz_k[ik]));
+                        ik_prev = ik;
+                    }
+                    double val = (h == 0 ? y.x : y.y) * sc_prev;
+                    const long long im = off + (long long)n * C + c;
+                    if (kin_b) {
+                        const double p = kin_b[im];
+                        kin = fma(p, p, kin);
+                        val += p;
+                    }
+                    out_b[im] = val;
+                }
+            }
         }
         if (want_kin) red[grp.g * T + tid] += 0.5 * kin;
     });
+}
+
+template <int CP, class Grp>
+CHB_D void ch5_general_forward_t(Grp &grp, const Ch5Loop &L, const double *vec_b, cd *buf, double *red, bool want_kin, const cd *twsm) {
+    ch5_general_load<CP>(grp, L, vec_b, buf, red, want_kin);
+    for (int P = 0; P < L.Cp; ++P) chf_fft_time_to_spec(grp, buf + P * L.seq_stride, L.f, false, twsm, 0);
+    ch5_general_combine<CP>(grp, L, buf);
+}
+template <class Grp>
+CHB_D void ch5_general_forward(Grp &grp, const Ch5Loop &L, const double *vec_b, cd *buf, double *red, bool want_kin, const cd *twsm) {
+    if (L.Cp == 1) ch5_general_forward_t<1>(grp, L, vec_b, buf, red, want_kin, twsm);
+    else if (L.Cp == 2) ch5_general_forward_t<2>(grp, L, vec_b, buf, red, want_kin, twsm);
+    else ch5_general_forward_t<0>(grp, L, vec_b, buf, red, want_kin, twsm);
+}
+
+// rows (gradient with respect to the slice, x + i y per row) -> Hermitian-packed spectra, inverse FFTs, parameter-space result
+template <int CP, class Grp>
+CHB_D void ch5_general_adjoint_t(Grp &grp, const Ch5Loop &L, cd *buf, const double *kin_b, double *out_b, double *red,
+                                  bool want_kin, const cd *twsm) {
+    ch5_general_combine_T<CP>(grp, L, buf);
+    for (int P = 0; P < L.Cp; ++P) chf_fft_spec_to_time(grp, buf + P * L.seq_stride, L.f, false, twsm, 0);
+    ch5_general_store<CP>(grp, L, buf, kin_b, out_b, red, want_kin);
+}
+template <class Grp>
+CHB_D void ch5_general_adjoint(Grp &grp, const Ch5Loop &L, cd *buf, const double *kin_b, double *out_b, double *red,
+                                bool want_kin, const cd *twsm) {
+    if (L.Cp == 1) ch5_general_adjoint_t<1>(grp, L, buf, kin_b, out_b, red, want_kin, twsm);
+    else if (L.Cp == 2) ch5_general_adjoint_t<2>(grp, L, buf, kin_b, out_b, red, want_kin, twsm);
+    else ch5_general_adjoint_t<0>(grp, L, buf, kin_b, out_b, red, want_kin, twsm);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -410,6 +541,22 @@ CHB_D void ch5_pair(Ctx &ctx, const Ch5Sys &F, cd *sm, bool have_fwd, const doub
     }
 }
 
+// once per persistent CTA: the stage tables that fit behind the loop buffers are copied into shared memory
+template <class Ctx>
+CHB_D void cta_fused5_prologue(Ctx &ctx, const Ch5Sys &F, cd *sm) {
+    if (F.tw_smem_len <= 0) return;
+    ctx.par([&](int tid, int nthr) {
+        for (int il = 0; il < F.nloop; ++il) {
+            const ChfLoop &L = F.loops[il].f;
+            for (int s = 0; s < L.nfac; ++s) {
+                if (L.tw_soff[s] < 0) continue;
+                cd *dst = sm + F.tw_smem_off + L.tw_soff[s];
+                for (int i = tid; i < L.tw_len[s]; i += nthr) dst[i] = L.tw[s][i];
+            }
+        }
+    });
+}
+
 // ------------------------------------------------------------------------------------------------
 // the CTA program for one state
 // ------------------------------------------------------------------------------------------------
@@ -421,6 +568,7 @@ CHB_D void cta_fused5(Ctx &ctx, const Ch5Sys &F, const ChfArgs &A, long long b, 
     double *seg_out_b = A.seg_out ? A.seg_out + b * F.segsz : (double *)0;
     double *out_b = A.vec_out ? A.vec_out + b * F.nparams : (double *)0;
     const bool have_fwd = vec_b != (const double *)0;
+    const cd *twsm = F.tw_smem_len > 0 ? sm + F.tw_smem_off : (const cd *)0;
     ctx.groups(F.nloop, F.T, [&](auto &grp) {
         grp.par([&](int tid, int T) { red[grp.g * T + tid] = 0.0; });
         const Ch5Loop &L = F.loops[grp.g];
@@ -428,9 +576,9 @@ CHB_D void cta_fused5(Ctx &ctx, const Ch5Sys &F, const ChfArgs &A, long long b, 
         cd *buf = sm + L.f.smem_off;
         if (L.kind == 1) {
             ch5_rfft_load(grp, L.f, vec_b, buf, red, A.kin_from == 1);
-            chf_fft_spec_to_time(grp, buf, L.f);
+            chf_fft_spec_to_time(grp, buf, L.f, false, twsm, 0);
         } else {
-            ch5_general_forward(grp, L, vec_b, buf, red, A.kin_from == 1);
+            ch5_general_forward(grp, L, vec_b, buf, red, A.kin_from == 1, twsm);
         }
         if (L.has_alg)  // Adjust_after_last_gen (:5290-5302): row 2 npr = alg_rot . row alg_src
             grp.par([&](int tid, int T) {
@@ -446,10 +594,10 @@ CHB_D void cta_fused5(Ctx &ctx, const Ch5Sys &F, const ChfArgs &A, long long b, 
             const Ch5Loop &L = F.loops[grp.g];
             cd *buf = sm + L.f.smem_off;
             if (L.kind == 1) {
-                chf_fft_time_to_spec(grp, buf, L.f);
+                chf_fft_time_to_spec(grp, buf, L.f, false, twsm, 0);
                 ch5_rfft_store(grp, L.f, buf, kin_b, out_b, red, A.kin_from == 2);
             } else {
-                ch5_general_adjoint(grp, L, buf, kin_b, out_b, red, A.kin_from == 2);
+                ch5_general_adjoint(grp, L, buf, kin_b, out_b, red, A.kin_from == 2, twsm);
             }
         });
     }

@@ -87,6 +87,7 @@ class NBodySystB200:
         self.segm_store = self._q(L.Q_SEGM_STORE)
         self.ncoeffs = self._nint // 2 + 1
         self._segsz = self._q(L.Q_SEGMPOS_SIZE)
+        self.nparams_incl_o = self._q(L.Q_NPARAMS_INCL_O)
         self._ws = None
 
     @property
@@ -197,6 +198,78 @@ class NBodySystB200:
         batch, lead = self._check(t, last_shape, what)
         return t, batch, lead
 
+    def _arr_call(self, fname, ins, outs, make_args):
+        """Call a ``*_dev`` entry point that takes no workspace.  ``ins``: input arrays (all NumPy or all torch CUDA tensors,
+        contiguous); ``outs``: list of ``(shape, dtype)`` of the results; ``make_args(in_ptrs, out_ptrs)`` builds the arguments
+        between the plan and the stream.  torch tensors: called on the current stream; NumPy arrays: addressed directly when the
+        library's ``*_dev`` entry points take host pointers, else staged through device buffers of the library
+        (``chb_malloc_device`` / ``chb_memcpy_*``; these operators are post-solve reductions, not the hot path)."""
+        fn = getattr(self._lib, fname)
+        if _is_torch(ins[0]):
+            import torch
+            tdt = {np.float64: torch.float64, np.int32: torch.int32}
+            res = [torch.empty(shp, dtype=tdt[dt], device=ins[0].device) for shp, dt in outs]
+            stream = C.c_void_p(torch.cuda.current_stream(ins[0].device).cuda_stream)
+            vp = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+            L.check(self._lib, fn(self._plan, *make_args([vp(a) for a in ins], [vp(r) for r in res]), stream))
+            return res
+        res = [np.empty(shp, dtype=dt) for shp, dt in outs]
+        if self._q(L.Q_HOST_POINTERS):
+            vp = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+            L.check(self._lib, fn(self._plan, *make_args([vp(a) for a in ins], [vp(r) for r in res]), None))
+            return res
+        bufs = []
+        try:
+            def dev(nbytes):
+                ptr = C.c_void_p()
+                L.check(self._lib, self._lib.chb_malloc_device(self._plan, max(int(nbytes), 16), C.byref(ptr)))
+                bufs.append(ptr)
+                return ptr
+            din = [dev(a.nbytes) for a in ins]
+            dout = [dev(r.nbytes) for r in res]
+            for a, d in zip(ins, din):
+                L.check(self._lib, self._lib.chb_memcpy_h2d(self._plan, d, C.c_void_p(a.ctypes.data), a.nbytes, None))
+            L.check(self._lib, fn(self._plan, *make_args(din, dout), None))
+            for r, d in zip(res, dout):
+                L.check(self._lib, self._lib.chb_memcpy_d2h(self._plan, C.c_void_p(r.ctypes.data), d, r.nbytes, None))
+            L.check(self._lib, self._lib.chb_stream_synchronize(self._plan, None))
+        finally:
+            for ptr in bufs:
+                self._lib.chb_free_device(self._plan, ptr)
+        return res
+
+    def _prep(self, a, last_shape, what):
+        """(contiguous float64 array, batch, leading shape) for a NumPy array or a torch CUDA tensor."""
+        if _is_torch(a):
+            return self._tprep(a, last_shape, what)
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        batch, lead = self._check(a, last_shape, what)
+        return a, batch, lead
+
+    def params_to_segmvel(self, params_mom_buf):
+        """_NBodySyst.pyx:3638-3666 (cdef :6050-6118): segment velocities, shape of ``segmpos``."""
+        if _is_torch(params_mom_buf):
+            import torch
+            x, b, lead = self._tprep(params_mom_buf, (self.nparams,), "params")
+            out = torch.empty(lead + self.segmpos_shape, dtype=torch.float64, device=x.device)
+            if b > 0:
+                # a call with an empty batch creates the velocity plan, so that the workspace query covers it
+                L.check(self._lib, self._lib.chb_params_to_segmvel_dev(self._plan, 0, None, None, None, 0, None))
+                self._ws = None
+                self._dev("chb_params_to_segmvel_dev", b, [x, out], x)
+            return out
+        return self._host(L.OP_PARAMS_TO_SEGMVEL, params_mom_buf, (self.nparams,), out0_shape=self.segmpos_shape)[0]
+
+    def params_changevar(self, params_buf_in, inv: bool = False, transpose: bool = False):
+        """_NBodySyst.pyx:2330-2410: the diagonal change of variables between the "momentum" parameters (``nparams``) and the
+        position Fourier parameters (``nparams_incl_o``, zero-padded), its transpose, inverse and inverse transpose."""
+        to_pos = (not inv and not transpose) or (inv and transpose)
+        n_in, n_out = (self.nparams, self.nparams_incl_o) if to_pos else (self.nparams_incl_o, self.nparams)
+        x, b, lead = self._prep(params_buf_in, (n_in,), "params_buf_in")
+        out, = self._arr_call("chb_params_changevar_dev", [x], [(lead + (n_out,), np.float64)],
+                              lambda i, o: (b, i[0], int(bool(inv)), int(bool(transpose)), o[0]))
+        return out
+
     # ------------------------------------------------------------------ transforms
     def params_to_segmpos(self, params_mom_buf):
         """_NBodySyst.pyx:3607-3635."""
@@ -272,18 +345,16 @@ class NBodySystB200:
 
     def segmpos_to_hash(self, segmpos):
         """_NBodySyst.pyx:2542-2560 (cdef segm_pos_to_hash :6271-6369): ``len(Hash_exp)`` weighted power sums of the pair
-        distances, the orbit fingerprint used to filter duplicates (find.py:285-308, 905-935).  Returns ``[..., nexp]``."""
-        if _is_torch(segmpos):
-            import torch
-            x, b, lead = self._tprep(segmpos, self.segmpos_shape, "segmpos")
-            out = torch.empty((len(self.Hash_exp), b), dtype=torch.float64, device=x.device)
-            for k, e in enumerate(self.Hash_exp):
-                self._dev("chb_segmpos_to_hash_dev", b, [x, float(e), out[k]], x)
-            return out.transpose(0, 1).reshape(lead + (len(self.Hash_exp),)).contiguous()
-        a = np.asarray(segmpos)
-        cols = [np.asarray(self._host(L.OP_HASH, a, self.segmpos_shape, out0_shape=(), scalar=float(e))[0]).reshape(-1)
-                for e in self.Hash_exp]
-        return np.stack(cols, axis=-1).reshape(a.shape[:-3] + (len(self.Hash_exp),))
+        distances, the orbit fingerprint used to filter duplicates (find.py:285-308, 905-935); all exponents in ONE pass over
+        the pair distances (``chb_segmpos_to_hash_multi_dev``).  Returns ``[..., nexp]``."""
+        x, b, lead = self._prep(segmpos, self.segmpos_shape, "segmpos")
+        exps = np.ascontiguousarray(self.Hash_exp, dtype=np.float64)
+        nexp = int(exps.shape[0])
+        if b == 0:
+            return (x.new_empty if _is_torch(x) else np.empty)(lead + (nexp,))
+        out, = self._arr_call("chb_segmpos_to_hash_multi_dev", [x], [(lead + (nexp,), np.float64)],
+                              lambda i, o: (b, i[0], nexp, C.c_void_p(exps.ctypes.data), o[0]))
+        return out
 
     # ------------------------------------------------------------------ ODE right-hand sides (SURVEY 8f rank 4)
     def _forces(self, pos_flat, dpos_flat=None):
@@ -341,6 +412,70 @@ class NBodySystB200:
     def Compute_grad_forces_vectorized(self, t, pos_flat, dpos_flat):
         """_NBodySyst.pyx:4249-4268: ``[nvec, nsegm*geodim]`` positions, ``[nvec, nsegm*geodim, grad_ndof]`` tangents."""
         return self._forces(pos_flat, dpos_flat)
+
+    def _velocities(self, mom_flat, grad_mom_flat=None):
+        vs = self.nsegm * self.geodim
+        if grad_mom_flat is None:
+            x, nvec, lead = self._prep(mom_flat, (vs,), "mom_flat")
+            if nvec == 0:
+                return x
+            out, = self._arr_call("chb_compute_velocities_dev", [x], [(tuple(x.shape), np.float64)], lambda i, o: (nvec, 0, i[0], o[0]))
+            return out
+        if len(grad_mom_flat.shape) < 2 or grad_mom_flat.shape[-2] != vs:
+            raise ValueError(f"grad_mom_flat: expected shape [..., {vs}, grad_ndof]")
+        ndof = int(grad_mom_flat.shape[-1])
+        g, nvec, lead = self._prep(grad_mom_flat, (vs, ndof), "grad_mom_flat")
+        if nvec == 0 or ndof == 0:
+            return g
+        out, = self._arr_call("chb_compute_velocities_dev", [g], [(tuple(g.shape), np.float64)], lambda i, o: (nvec, ndof, i[0], o[0]))
+        return out
+
+    def Compute_velocities(self, t, mom_flat):
+        """_NBodySyst.pyx:4081-4094 (cdef 8106-8133): velocities of the segments from their momenta, ``mom / mass``."""
+        return self._velocities(mom_flat)
+
+    def Compute_velocities_vectorized(self, t, mom_flat):
+        """_NBodySyst.pyx:4116-4131: ``[nvec, nsegm*geodim]``."""
+        return self._velocities(mom_flat)
+
+    def Compute_grad_velocities(self, t, mom_flat, grad_mom_flat):
+        """_NBodySyst.pyx:4098-4113 (cdef 8135-8160): tangent of the above, ``[nsegm*geodim, grad_ndof]``."""
+        return self._velocities(mom_flat, grad_mom_flat)
+
+    def Compute_grad_velocities_vectorized(self, t, mom_flat, grad_mom_flat):
+        """_NBodySyst.pyx:4133-4150: ``[nvec, nsegm*geodim, grad_ndof]``."""
+        return self._velocities(mom_flat, grad_mom_flat)
+
+    def Compute_init_pos_mom(self, params_mom_buf):
+        """_NBodySyst.pyx:4060-4077: initial positions and momenta (first stored sample of every segment) of the reduced ODE."""
+        seg = self.params_to_segmpos(params_mom_buf)
+        vel = self.params_to_segmvel(params_mom_buf)
+        mass = self.tables.loopmass[self.tables.bodyloop[self.tables.gensegm_to_body]]
+        if _is_torch(seg):
+            import torch
+            mass = torch.as_tensor(mass, device=seg.device)
+        xo = seg[..., :, 0, :].reshape(tuple(seg.shape[:-3]) + (-1,))
+        po = (vel[..., :, 0, :] * mass[:, None]).reshape(tuple(seg.shape[:-3]) + (-1,))
+        return xo, po
+
+    def Get_ODE_def(self, params_mom_buf, vector_calls: bool = True, LowLevel: bool = False, NoSymIfPossible: bool = True,
+                    grad: bool = False):
+        """_NBodySyst.pyx:4310-4444: the reduced ODE of one segment period as a dict for the reference's symplectic integrators
+        (``scipy_plus.ODE.SymplecticIVP``): Python callables backed by the library's kernels.  ``LowLevel`` C callbacks cannot
+        reach the device and are rejected."""
+        if LowLevel:
+            raise ValueError("Get_ODE_def: LowLevelCallable C callbacks are CPU function pointers; use LowLevel=False")
+        xo, po = self.Compute_init_pos_mom(params_mom_buf)
+        d = {"t_span": (0., 1. / self.nint_min), "x0": xo, "v0": po, "vector_calls": vector_calls}
+        if vector_calls:
+            d["fun"], d["gun"] = self.Compute_velocities_vectorized, self.Compute_forces_vectorized
+            if grad:
+                d["grad_fun"], d["grad_gun"] = self.Compute_grad_velocities_vectorized, self.Compute_grad_forces_vectorized
+        else:
+            d["fun"], d["gun"] = self.Compute_velocities, self.Compute_forces
+            if grad:
+                d["grad_fun"], d["grad_gun"] = self.Compute_grad_velocities, self.Compute_grad_forces
+        return d
 
     def params_resize(self, params_buf_in, nint_fac: int = 1):
         """_NBodySyst.pyx:2413-2465: the parameters of this ``nint`` level re-expressed at ``nint = 2 nint_min nint_fac``
@@ -516,127 +651,74 @@ class NBodySystB200:
         return True
 
     # ------------------------------------------------------------------ post-solve reductions (find.py:285-308, 376-380)
-    def _body_tables(self, like):
-        T = self.tables
-        if T.bodysegm is None:
-            raise ValueError("these tables carry no per-body symmetries (bodysegm / body_spacerot / body_timerev): "
-                             "re-extract them with extract_tables from a live NBodySyst")
-        mass = T.loopmass[T.bodyloop]
-        if _is_torch(like):
-            import torch
-            key = ("body", str(like.device))
-            if getattr(self, "_body_cache", None) is None or self._body_cache[0] != key:
-                self._body_cache = (key, tuple(torch.as_tensor(np.ascontiguousarray(a), device=like.device)
-                                               for a in (T.bodysegm, T.body_spacerot, T.body_timerev, mass)))
-            return self._body_cache[1]
-        return T.bodysegm, T.body_spacerot, T.body_timerev, mass
-
     def ComputeCenterOfMass(self, segmpos):
-        """_NBodySyst.pyx:3968-4009, batched: mass-weighted mean position over all bodies and the whole period, from the stored
-        segments and the symmetry that carries each body onto them.  ``[..., nsegm, segm_store, geodim] -> [..., geodim]``."""
-        self._check(segmpos, self.segmpos_shape, "segmpos")
-        bodysegm, rot, trev, mass = self._body_tables(segmpos)
-        n = self.segm_size
-        s_fwd = segmpos[..., :, 0:n, :].sum(-2)                     # TimeRev > 0: samples 0 .. segm_size-1
-        if (self.tables.body_timerev < 0).any():
-            if self.segm_store <= n:
-                raise ValueError("ComputeCenterOfMass: a time-reversed body segment needs segm_store = segm_size + 1")
-            s_rev = s_fwd - segmpos[..., :, 0, :] + segmpos[..., :, n, :]   # TimeRev < 0: samples 1 .. segm_size
-        else:
-            s_rev = s_fwd
-        tot = None
-        for ib in range(self.tables.nbody):
-            for ii in range(self.tables.nint_min):
-                src = s_fwd if int(self.tables.body_timerev[ib, ii]) > 0 else s_rev
-                v = src[..., int(self.tables.bodysegm[ib, ii]), :] @ rot[ib, ii].T * float(self.tables.loopmass[self.tables.bodyloop[ib]])
-                tot = v if tot is None else tot + v
-        totmass = float(self.tables.loopmass[self.tables.bodyloop].sum()) * self.tables.nint_min
-        return tot / (n * totmass)
+        """_NBodySyst.pyx:3968-4009, batched (``chb_center_of_mass_dev``, one CTA per state): mass-weighted mean position over
+        all bodies and the whole period, from the stored segments and the symmetry that carries each body onto them.
+        ``[..., nsegm, segm_store, geodim] -> [..., geodim]``."""
+        self._need_body_tables()
+        x, b, lead = self._prep(segmpos, self.segmpos_shape, "segmpos")
+        if b == 0:
+            return (x.new_empty if _is_torch(x) else np.empty)(lead + (self.geodim,))
+        out, = self._arr_call("chb_center_of_mass_dev", [x], [(lead + (self.geodim,), np.float64)], lambda i, o: (b, i[0], o[0]))
+        return out
 
     def DetectEscape(self, segmpos, fac: float = 2.):
-        """_NBodySyst.pyx:2125-2192, batched: per body the box spanned by the rotated min / max corners of its segments, an edge
-        between two bodies whose box centres are closer than ``fac`` times the sum of the box diagonals; escaped = that graph
-        is not connected.  Returns a bool (one state) or a NumPy bool array over the leading dimensions."""
-        batch, lead = self._check(segmpos, self.segmpos_shape, "segmpos")
-        bodysegm, rot, trev, mass = self._body_tables(segmpos)
-        torch_in = _is_torch(segmpos)
-        lo_s = segmpos.amin(-2) if torch_in else segmpos.min(-2)    # [..., nsegm, G]
-        hi_s = segmpos.amax(-2) if torch_in else segmpos.max(-2)
-        nb = self.tables.nbody
-        mids, sizes = [], []
-        for ib in range(nb):
-            pts = []
-            for ii in range(self.tables.nint_min):
-                k = int(self.tables.bodysegm[ib, ii])
-                pts.append(lo_s[..., k, :] @ rot[ib, ii].T)
-                pts.append(hi_s[..., k, :] @ rot[ib, ii].T)
-            if torch_in:
-                import torch
-                P = torch.stack(pts, -2)
-                lo, hi = P.amin(-2), P.amax(-2)
-                sizes.append(((hi - lo) ** 2).sum(-1).sqrt())
-            else:
-                P = np.stack(pts, -2)
-                lo, hi = P.min(-2), P.max(-2)
-                sizes.append(np.sqrt(((hi - lo) ** 2).sum(-1)))
-            mids.append((hi + lo) / 2)
-        if torch_in:
-            import torch
-            M, S = torch.stack(mids, -2), torch.stack(sizes, -1)    # [..., nb, G], [..., nb]
-            D = ((M[..., :, None, :] - M[..., None, :, :]) ** 2).sum(-1).sqrt()
-            adj = (D < fac * (S[..., :, None] + S[..., None, :])).cpu().numpy()
-        else:
-            M, S = np.stack(mids, -2), np.stack(sizes, -1)
-            D = np.sqrt(((M[..., :, None, :] - M[..., None, :, :]) ** 2).sum(-1))
-            adj = D < fac * (S[..., :, None] + S[..., None, :])
-        reach = adj | np.eye(nb, dtype=bool)
-        for _ in range(max(1, int(np.ceil(np.log2(max(nb, 2)))))):  # transitive closure by repeated squaring
-            r = reach.astype(np.int32)
-            reach = (r @ r) > 0
-        escaped = ~reach[..., 0, :].all(-1)
-        return bool(escaped) if escaped.ndim == 0 else escaped
+        """_NBodySyst.pyx:2125-2192, batched (``chb_detect_escape_dev``, one CTA per state): per body the box spanned by the
+        rotated min / max corners of its segments, an edge between two bodies whose box centres are closer than ``fac`` times
+        the sum of the box diagonals; escaped = that graph is not connected.  Returns a bool (one state), a NumPy bool array
+        (NumPy input) or a bool tensor (device input) over the leading dimensions."""
+        self._need_body_tables()
+        x, b, lead = self._prep(segmpos, self.segmpos_shape, "segmpos")
+        if b == 0:
+            return np.zeros(lead, dtype=bool)
+        out, = self._arr_call("chb_detect_escape_dev", [x], [(lead if lead else (1,), np.int32)],
+                              lambda i, o: (b, i[0], float(fac), o[0]))
+        esc = out != 0
+        if lead == ():
+            return bool(esc.reshape(-1)[0])
+        return esc
 
     def segm_to_path_stats(self, segmpos, segmvel):
-        """_NBodySyst.pyx:3903-3943 (cdef :7420-7529), batched: length of every loop (trapezoid rule on ``|v|`` when the
-        segments store their end point, plain sum otherwise) and the minimum distance of every binary interaction over the
-        stored samples.  ``segmvel`` has the shape of ``segmpos``.  Returns ``(loop_len [..., nloop], bin_dx_min [..., nbin])``."""
-        self._check(segmpos, self.segmpos_shape, "segmpos")
-        self._check(segmvel, self.segmpos_shape, "segmvel")
-        T, n = self.tables, self.segm_size
-        torch_in = _is_torch(segmpos)
-        speed = (segmvel * segmvel).sum(-1).sqrt() if torch_in else np.sqrt((segmvel * segmvel).sum(-1))   # [..., nsegm, store]
-        if self.segm_store == n:
-            val = speed.sum(-1)
-        else:
-            val = speed[..., 1:n].sum(-1) + 0.5 * (speed[..., 0] + speed[..., n])
-        segm_len = val * (T.nint_min / n)
-        seg_loop = T.bodyloop[T.gensegm_to_body]
-        loops = [segm_len[..., np.nonzero(seg_loop == il)[0].tolist()].sum(-1) / T.nint_min for il in range(T.nloop)]
-        mins = []
-        for ib in range(T.nbin):
-            src = segmpos[..., int(T.bin_source[ib]), :, :]
-            if not T.bin_spacerot_isid[ib]:
-                R = T.bin_spacerot[ib].T
-                if torch_in:
-                    import torch
-                    R = torch.as_tensor(np.ascontiguousarray(R), device=segmpos.device)
-                src = src @ R
-            d = src - segmpos[..., int(T.bin_target[ib]), :, :]
-            d2 = (d * d).sum(-1)
-            mins.append((d2.amin(-1) if torch_in else d2.min(-1)))
-        if torch_in:
-            import torch
-            return torch.stack(loops, -1), torch.stack(mins, -1).sqrt()
-        return np.stack(loops, -1), np.sqrt(np.stack(mins, -1))
+        """_NBodySyst.pyx:3903-3943 (cdef :7420-7529), batched (``chb_path_stats_dev``, one CTA per state): length of every loop
+        (trapezoid rule on ``|v|`` when the segments store their end point, plain sum otherwise) and the minimum distance of
+        every binary interaction over the stored samples.  ``segmvel`` has the shape of ``segmpos`` (``params_to_segmvel``).
+        Returns ``(loop_len [..., nloop], bin_dx_min [..., nbin])``."""
+        x, b, lead = self._prep(segmpos, self.segmpos_shape, "segmpos")
+        v, bv, _ = self._prep(segmvel, self.segmpos_shape, "segmvel")
+        if b != bv:
+            raise ValueError("segmpos and segmvel hold different numbers of states")
+        nbin = self.tables.nbin
+        if b == 0:
+            mk = x.new_empty if _is_torch(x) else np.empty
+            return mk(lead + (self.nloop,)), mk(lead + (nbin,))
+        ll, bm = self._arr_call("chb_path_stats_dev", [x, v], [(lead + (self.nloop,), np.float64), (lead + (nbin,), np.float64)],
+                                lambda i, o: (b, i[0], i[1], o[0], o[1]))
+        return ll, bm
+
+    def _need_body_tables(self):
+        if self.tables.bodysegm is None:
+            raise ValueError("these tables carry no per-body symmetries (bodysegm / body_spacerot / body_timerev): "
+                             "re-extract them with extract_tables from a live NBodySyst")
+
+    @property
+    def LawIsHomo(self) -> bool:
+        return True  # gravity_pot and power_law_pot are homogeneous (Detect_homo_inter_law, _NBodySyst.pyx:1692-1718)
+
+    @property
+    def Homo_exp(self) -> float:
+        """``xsq V'(xsq) / V(xsq)`` (Detect_homo_inter_law, _NBodySyst.pyx:1692-1718): -1/2 for gravity, n/2 for the power law."""
+        if self.tables.inter_law == 0:
+            return -0.5
+        return float(self.tables.inter_law_params[2]) + 2.0
 
     def TestHashSame(self, Hash_a, Hash_b, rtol: float = 1e-5, detect_multiples: bool = True) -> bool:
-        """_NBodySyst.pyx:2036-2067.  For a homogeneous law (gravity / power law: Homo_exp = n) two orbits that differ by a
+        """_NBodySyst.pyx:2036-2067.  For a homogeneous law (gravity / power law: Homo_exp = n / 2) two orbits that differ by a
         rescaling have hashes whose ratios follow a power law; otherwise the hashes must agree entry by entry."""
         Ha, Hb = np.asarray(Hash_a, dtype=np.float64), np.asarray(Hash_b, dtype=np.float64)
         n = self.Hash_exp.shape[0]
         test = np.zeros(n)
         if detect_multiples:
-            homo = -1.0 if self.tables.inter_law == 0 else 2.0 * (float(self.tables.inter_law_params[2]) + 2.0)
+            homo = self.Homo_exp
             ref = (Ha[0] / Hb[0]) ** ((homo - 1) / (2 * self.Hash_exp[0]))
             for i in range(1, n):
                 test[i] = (Ha[i] / Hb[i]) ** ((homo - 1) / (2 * self.Hash_exp[i])) - ref

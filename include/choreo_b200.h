@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define CHB_ABI_VERSION 1
+#define CHB_ABI_VERSION 2
 
 enum chb_status {
     CHB_OK = 0,
@@ -99,6 +99,12 @@ typedef struct chb_tables {
     const double *bin_spacerot;         /* _BinSpaceRot [nbin][geodim][geodim] */
     const int32_t *bin_spacerot_isid;   /* _BinSpaceRotIsId   */
     const double *bin_prodchargesum;    /* _BinProdChargeSum (already divided by nint_min, :818) */
+    /* ABI 2, optional (all three NULL or all three given): per (body, interval of the period) the stored segment the body runs
+     * on and the symmetry that carries it there -- only the post-solve reductions (chb_center_of_mass_dev, chb_detect_escape_dev)
+     * read them */
+    const int64_t *bodysegm;      /* _bodysegm [nbody][nint_min]                                   */
+    const double *body_spacerot;  /* intersegm_to_all[ib][iint].SpaceRot [nbody][nint_min][geodim][geodim] */
+    const int64_t *body_timerev;  /* intersegm_to_all[ib][iint].TimeRev  [nbody][nint_min]        */
 } chb_tables;
 
 typedef struct chb_plan chb_plan;
@@ -117,6 +123,7 @@ enum chb_query {
     CHB_Q_LAUNCHES = 10,      /* kernels launched by this plan since creation (counter)  */
     CHB_Q_FUSED = 11,         /* 0: staged kernels; else the version of the fused single-kernel path that serves this level (3 or 4) */
     CHB_Q_SEGMPOS_SIZE = 12,  /* nsegm*segm_store*geodim                                 */
+    CHB_Q_NPARAMS_INCL_O = 14, /* NBodySyst.nparams_incl_o: length of the position-parameter array of params_changevar */
     CHB_Q_HOST_POINTERS = 13  /* 1 when the *_dev entry points of this build address host memory (CPU emulation build of the
                                  test suite), 0 for the CUDA library (device pointers only)                              */
 };
@@ -135,7 +142,8 @@ int chb_plan_query(const chb_plan *plan, int what, int64_t *value_out);
 int chb_plan_set_chunk(chb_plan *plan, int64_t chunk);
 /* 0 = generic staged kernels only; 4 (default) = newest fused kernel the layout supports: version 4 (rows moved by bulk
  * asynchronous copies, natural-order in-place passes) for 4096-sample RFFT loops, else version 3; 3 = force version 3
- * (A/B measurements) */
+ * (A/B measurements).  Layouts versions 3 / 4 do not serve (GENERAL_SYM loops, segm_store = segm_size + 1, rotated or
+ * time-reversed segments) run the general fused kernel (CHB_Q_FUSED reports 5) for any non-zero value. */
 int chb_plan_set_fused(chb_plan *plan, int enable);
 
 /* bytes of device workspace any *_dev operator below needs for `batch` states */
@@ -262,7 +270,8 @@ enum chb_op {
     CHB_OP_POT = 10,
     CHB_OP_POT_GRAD = 11,
     CHB_OP_POT_HESS = 12,
-    CHB_OP_HASH = 13 /* in0=segmpos out0=hash (scalar = exponent) */
+    CHB_OP_HASH = 13, /* in0=segmpos out0=hash (scalar = exponent) */
+    CHB_OP_PARAMS_TO_SEGMVEL = 14 /* in0=params out0=segmvel (ABI 2) */
 };
 int chb_run_host(chb_plan *plan, int op, int64_t batch, const double *in0, const double *in1, double scalar,
                  double *out0, double *out1);
@@ -279,6 +288,33 @@ int chb_compute_grad_forces_dev(chb_plan *plan, int64_t nvec, int64_t grad_ndof,
 /* host-pointer form of both (forces and / or grad_forces; dpos and grad_forces are given together or both NULL) */
 int chb_compute_forces_host(chb_plan *plan, int64_t nvec, int64_t grad_ndof, const double *pos, const double *dpos,
                             double *forces, double *grad_forces);
+
+
+/* ---- ABI 2: velocities, change of variables, post-solve reductions (device pointers, asynchronous on `stream`) ------------ */
+/* params_to_segmvel, :3638-3666 / cdef :6050-6118 (changevar_mom_vel :4830-4914, velocity basis = i * position basis :852-854,
+ * InterSpaceRotVel / ALG_SpaceRotVel = TimeRev * position rotation, _ActionSym.pyx:268-291); segmvel has the shape of segmpos */
+int chb_params_to_segmvel_dev(chb_plan *plan, int64_t batch, const double *params, double *segmvel,
+                              void *workspace, size_t workspace_bytes, void *stream);
+/* params_changevar, :2330-2410 (changevar_mom_pos :4489-4573, _T :4746-4827, _inv :4662-4743, _invT :4576-4660).
+ *   inv = 0, transpose = 0: in [batch][nparams]        -> out [batch][nparams_incl_o]
+ *   inv = 0, transpose = 1: in [batch][nparams_incl_o] -> out [batch][nparams]
+ *   inv = 1, transpose = 0: in [batch][nparams_incl_o] -> out [batch][nparams]
+ *   inv = 1, transpose = 1: in [batch][nparams]        -> out [batch][nparams_incl_o]      (CHB_Q_NPARAMS_INCL_O) */
+int chb_params_changevar_dev(chb_plan *plan, int64_t batch, const double *in, int inv, int transpose, double *out, void *stream);
+/* segmpos_to_hash, :2542-2560 / cdef segm_pos_to_hash :6271-6369 with ALL exponents in one pass over the pair distances:
+ * exponents is a HOST array of nexp <= 16 values (the reference's Hash_exp), hash [batch][nexp] */
+int chb_segmpos_to_hash_multi_dev(chb_plan *plan, int64_t batch, const double *segmpos, int nexp, const double *exponents,
+                                  double *hash, void *stream);
+/* ComputeCenterOfMass, :3968-4009 ; com [batch][geodim] (needs the ABI 2 body tables) */
+int chb_center_of_mass_dev(chb_plan *plan, int64_t batch, const double *segmpos, double *com, void *stream);
+/* DetectEscape, :2125-2192 ; escaped [batch] int32, 1 = the graph of overlapping body boxes is not connected */
+int chb_detect_escape_dev(chb_plan *plan, int64_t batch, const double *segmpos, double fac, int32_t *escaped, void *stream);
+/* segm_to_path_stats, :3903-3943 / cdef :7420-7529 ; loop_len [batch][nloop], bin_dx_min [batch][nbin] */
+int chb_path_stats_dev(chb_plan *plan, int64_t batch, const double *segmpos, const double *segmvel, double *loop_len,
+                       double *bin_dx_min, void *stream);
+/* Compute_velocities(_vectorized) / Compute_grad_velocities(_vectorized), :4081-4150 / cdef :8106-8160: out = mom / segment mass;
+ * mom, out [nvec][nsegm*geodim] (grad_ndof = 0) or [nvec][nsegm*geodim][grad_ndof] */
+int chb_compute_velocities_dev(chb_plan *plan, int64_t nvec, int64_t grad_ndof, const double *mom, double *out, void *stream);
 
 /* ---- memory helpers so a NumPy-only caller needs no CUDA binding ---------------------------------- */
 int chb_malloc_device(chb_plan *plan, size_t bytes, void **ptr_out);

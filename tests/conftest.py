@@ -73,3 +73,29 @@ def relerr(a, b):
         return 0.0
     den = max(float(np.max(np.abs(b))), 1e-300)
     return float(np.max(np.abs(a - b))) / den
+
+
+@pytest.fixture(params=["hostsim", pytest.param("cuda", marks=pytest.mark.gpu)])
+def backend(request):
+    """Library handle a reference-comparison test runs on: the g++ emulation of the CTA programs (CPU suite) or the CUDA
+    library (``-m gpu``; ``None`` selects the product loader).  The reference (oracle/_ref) is the checker in both."""
+    if request.param == "hostsim":
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from hostsim import build_hostsim
+        return build_hostsim.load()
+    from choreographies2_b200 import _lib
+    assert _lib.load().chb_device_count() >= 1, "no sm_100 device visible: GPU tests need a B200"
+    return None
+
+
+def make_nbs(tables, nint, backend):
+    from choreographies2_b200 import NBodySystB200
+    return NBodySystB200(tables, nint) if backend is None else NBodySystB200(tables, nint, _lib_handle=backend)
+
+
+def need_reference():
+    from oracle import ref_loader
+    if not ref_loader.reference_available():
+        pytest.skip("oracle/_ref not built")
+    ref_loader.import_reference()
+    return ref_loader

@@ -40,7 +40,7 @@ def test_library_is_sm100a_only():
 
 
 def test_abi_version_and_errors(cuda_lib):
-    assert cuda_lib.chb_abi_version() == 1
+    assert cuda_lib.chb_abi_version() == 2
     plan = C.c_void_p()
     assert cuda_lib.chb_plan_create(None, 0, C.byref(plan)) == 1  # CHB_ERR_INVALID_ARGUMENT
     assert b"NULL" in cuda_lib.chb_last_error_string()

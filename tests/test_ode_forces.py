@@ -95,26 +95,32 @@ def test_forces_hostsim_matches_numpy():
     _check(_sim(), ["3C", "3D", "5Dq", "20B", "3B"])
 
 
-def test_forces_match_reference():
-    from oracle import ref_loader
-    if not ref_loader.reference_available():
-        pytest.skip("oracle/_ref not built")
-    ref_loader.import_reference()
+@pytest.mark.parametrize("name", ["3C", "5Dq", "3D", "3B", "5q", "64C", "2D1_3dim", "20B"])
+def test_forces_match_reference(name, backend):
+    """Compute_forces / Compute_grad_forces per vector against the unmodified reference; runs on the emulation (CPU suite) and,
+    with -m gpu, on the CUDA library (dense gather kernels for 20B / 64C, rotated interactions for 5q)."""
+    from conftest import make_nbs, need_reference
+    ref_loader = need_reference()
     from choreographies2_b200 import extract_tables
-    sim = _sim()
-    for name in ("3C", "5Dq", "3D", "3B"):
-        NBS = ref_loader.build_named(name)
-        NBS.nint = 2 * NBS.nint_min * 4
-        nbs = NBodySystB200(extract_tables(NBS), NBS.nint, _lib_handle=sim)
-        vs = NBS.nsegm * NBS.geodim
-        rng = np.random.default_rng(3)
-        pos = rng.standard_normal((4, vs))
-        dpos = rng.standard_normal((4, vs, 2 * vs))
-        F = nbs.Compute_forces_vectorized(np.zeros(4), pos)
-        gF = nbs.Compute_grad_forces_vectorized(np.zeros(4), pos, dpos)
-        for i in range(4):
-            assert relerr(F[i], np.asarray(NBS.Compute_forces(0.0, pos[i]))) < TOL, (name, i)
-            assert relerr(gF[i], np.asarray(NBS.Compute_grad_forces(0.0, pos[i], dpos[i]))) < TOL, (name, i)
+    if name == "64C" and backend is not None:
+        pytest.skip("64C on the emulation takes minutes; covered on the GPU")
+    NBS = ref_loader.build_named(name)
+    NBS.nint = 2 * NBS.nint_min * 4
+    nbs = make_nbs(extract_tables(NBS), NBS.nint, backend)
+    vs = NBS.nsegm * NBS.geodim
+    rng = np.random.default_rng(3)
+    nvec = 4 if backend is not None else 40
+    pos = rng.standard_normal((nvec, vs))
+    dpos = rng.standard_normal((nvec, vs, min(2 * vs, 24)))
+    F = nbs.Compute_forces_vectorized(np.zeros(nvec), pos)
+    gF = nbs.Compute_grad_forces_vectorized(np.zeros(nvec), pos, dpos)
+    # the reference's own Compute_grad_forces segfaults on interactions with a space rotation (5q; probed in this container),
+    # so the tangent forces of such systems are checked against the finite-difference property in _check instead
+    ref_grad_ok = bool(np.asarray(NBS.BinSpaceRotIsId).all())
+    for i in range(0, nvec, max(1, nvec // 4)):
+        assert relerr(F[i], np.asarray(NBS.Compute_forces(0.0, pos[i].copy()))) < TOL, (name, i)
+        if ref_grad_ok:
+            assert relerr(gF[i], np.asarray(NBS.Compute_grad_forces(0.0, pos[i].copy(), dpos[i].copy()))) < TOL, (name, i)
 
 
 @pytest.mark.gpu
