@@ -22,7 +22,7 @@ STATUS_NAMES = {
 }
 # enum chb_query
 Q_NINT, Q_NPARAMS, Q_SEGM_SIZE, Q_SEGM_STORE, Q_NSEGM, Q_GEODIM, Q_NLOOP, Q_NBIN, Q_DEVICE, Q_CHUNK, Q_LAUNCHES, \
-    Q_FUSED, Q_SEGMPOS_SIZE, Q_HOST_POINTERS, Q_NPARAMS_INCL_O = range(15)
+    Q_FUSED, Q_SEGMPOS_SIZE, Q_HOST_POINTERS, Q_NPARAMS_INCL_O, Q_STAGED_TRANSFORM, Q_PAIR_KERNEL = range(17)
 # enum chb_op
 (OP_PARAMS_TO_SEGMPOS, OP_SEGMPOS_TO_PARAMS, OP_SEGMPOS_TO_PARAMS_T, OP_ACTION, OP_ACTION_GRAD, OP_ACTION_HESS,
  OP_SEGMPOS_ACTION, OP_SEGMPOS_ACTION_GRAD, OP_SEGMPOS_ACTION_HESS, OP_KIN, OP_POT, OP_POT_GRAD, OP_POT_HESS,

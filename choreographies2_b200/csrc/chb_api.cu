@@ -26,6 +26,7 @@
 #include "chb_fused.cuh"
 #include "chb_fused4.cuh"
 #include "chb_fused5.cuh"
+#include "chb_big.cuh"
 #include "chb_ode.cuh"
 #include "chb_post.cuh"
 
@@ -97,6 +98,8 @@ struct chb_plan {
     int pair_dense_enabled = 1;  // dense pair kernel when the level's interaction graph allows it (A/B knob: CHB_PAIR_DENSE=0)
     int dense_threads = 256;
     size_t dense_smem[3] = {0, 0, 0};
+    int tile_threads = 256;
+    size_t tile_smem[3] = {0, 0, 0};
     // staging for chb_run_host
     std::mutex host_mutex;
     void *stage_dev = nullptr;
@@ -113,6 +116,9 @@ struct chb_plan {
     ChbBodyTab body;               // device copies of the body tables (valid when body.nbody > 0)
     const long long *d_pos_off = nullptr;  // [nloop + 1] offsets of the loops in position-parameter space (params_changevar)
     long long nparams_incl_o = 0;
+    int big_active = 0;     // staged transforms by the parity-split kernels of chb_big.cuh (planar RFFT systems without a fused kernel)
+    ChbBigSys bigsys;
+    size_t big_smem = 0;
     int fused5_active = 0;  // the level is served by the general fused kernel (chb_fused5.cuh) instead of versions 3 / 4
     Ch5Sys f5;              // passed by value (constant bank) to k_fused5
 };
@@ -684,6 +690,7 @@ static int fused5_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm
         smem_cd += (long long)FL.Cp * f.N + 16;  // + the Adjust_after_last_gen row, keeps the next loop 256-byte aligned
         maxN = std::max(maxN, f.N);
         for (int j = 0; j < L.nppl; ++j) { FL.co_in[j] = L.co_in[j]; FL.co_prefix[j] = L.co_prefix[j]; }
+        for (int c = 0; c < L.C; ++c) FL.ikc[c] = c / L.nppl;
         FL.tw_trivial = 1;
         for (int ik = 0; ik < L.nnz; ++ik) {
             FL.nnz_k[ik] = L.nnz_k[ik];
@@ -806,6 +813,125 @@ static int fused5_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm
         p->fused_smem += (size_t)off * sizeof(cd);
     }
     return 1;
+}
+
+// ---- parity-split staged transforms (chb_big.cuh) ----------------------------------------------------
+// returns 1 when k_big_fwd / k_big_adj can serve the level's transforms (and fills p->bigsys), 0 when not, <0 on error
+static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_size, int segm_store) {
+    const HostTables &T = p->T;
+    if (T.G != 2 || segm_store != segm_size || T.nloop > CHB_BIG_MAX_LOOPS || T.vel) return 0;
+    ChbBigSys &F = p->bigsys;
+    memset(&F, 0, sizeof(F));
+    F.nloop = T.nloop;
+    F.segm_size = segm_size;
+    F.nparams = p->sys.nparams;
+    F.segsz = p->sys.segsz;
+    int maxNh = 0;
+    std::map<int, int> first_loop_of_N;
+    for (int il = 0; il < T.nloop; ++il) {
+        const ChbLoop &L = loops[il];
+        if (L.shortcut != CHB_RFFT || L.nnz != 1 || L.nppl != 4 || L.n_sub_fft != 1 || !L.has_k0) return 0;
+        const int N = 2 * L.npr, Nh = L.npr;
+        if (Nh < 2 || N % segm_size != 0) return 0;
+        ChfLoop &h = F.loops[il].h;
+        h.N = Nh;
+        h.npr = L.npr;
+        std::vector<int> fac;
+        if (!ch5_factorize(Nh, fac)) return 0;
+        h.nfac = (int)fac.size();
+        for (int i = 0; i < h.nfac; ++i) h.fac[i] = fac[i];
+        h.swm = (Nh % 16 == 0) ? 15 : 0;
+        h.mom_off = L.mom_off;
+        h.nco_in = L.nco_in;
+        h.ncm = L.ncm;
+        h.co0 = L.co_in[0] ? L.co_prefix[0] : -1;
+        h.co2 = L.co_in[2] ? L.co_prefix[2] : -1;
+        h.loopmul = L.loopmul;
+        maxNh = std::max(maxNh, Nh);
+        std::vector<int> slot_seg(N / segm_size, -1);
+        for (int s = 0; s < T.nsegm; ++s)
+            if ((int)T.bodyloop[T.seg_body[s]] == il) {
+                if (T.seg_iintrel[s] >= (int64_t)slot_seg.size() || slot_seg[T.seg_iintrel[s]] >= 0) return 0;
+                slot_seg[T.seg_iintrel[s]] = s;
+            }
+        for (int v : slot_seg)
+            if (v < 0) return 0;
+        if (level_upload(p, slot_seg, &F.loops[il].slot_seg)) return -1;
+    }
+    int Tg = ((maxNh / 32 + 31) / 32) * 32;
+    Tg = std::max(64, std::min(Tg, CHF_MAX_THREADS));
+    F.T = Tg;
+    size_t tw_room = 0;
+    {
+        const size_t base = CHF_RED_BYTES + (size_t)maxNh * sizeof(cd);
+        if (base + 1024 > p->smem_limit) return 0;
+        tw_room = (p->smem_limit - base - 1024) / sizeof(cd);
+    }
+    int max_tw = 0;
+    for (int il = 0; il < T.nloop; ++il) {
+        ChbBigLoop &BL = F.loops[il];
+        ChfLoop &h = BL.h;
+        auto it = first_loop_of_N.find(h.N);
+        if (it != first_loop_of_N.end()) {
+            const ChbBigLoop &G0 = F.loops[it->second];
+            h.rev = G0.h.rev;
+            for (int i = 0; i < h.nfac; ++i) { h.tw[i] = G0.h.tw[i]; h.tw_len[i] = G0.h.tw_len[i]; h.tw_soff[i] = G0.h.tw_soff[i]; }
+            BL.t_hi = G0.t_hi;
+            BL.t_lo = G0.t_lo;
+            continue;
+        }
+        first_loop_of_N[h.N] = il;
+        const int Nh = h.N, N = 2 * Nh;
+        std::vector<int> rev(Nh);
+        for (int k = 0; k < Nh; ++k) {
+            int kk = k, pos = 0, Lcur = Nh;
+            for (int i = 0; i < h.nfac; ++i) {
+                const int r = h.fac[i], t = kk % r;
+                kk /= r;
+                Lcur /= r;
+                pos += t * Lcur;
+            }
+            rev[k] = pos;
+        }
+        if (level_upload(p, rev, &h.rev)) return -1;
+        int Lcur = Nh, off = 0;
+        size_t room = tw_room;
+        for (int i = 0; i < h.nfac; ++i) {
+            const int r = h.fac[i], Lp = Lcur / r, nb = chf_nbase(r);
+            std::vector<cd> tw((size_t)std::max(1, Lp * nb));
+            for (int j = 0; j < Lp; ++j)
+                for (int e = 0; e < nb; ++e) {
+                    double c, sn;
+                    exact_root((long long)j * (1LL << e), Lcur, &c, &sn);
+                    tw[(size_t)e * Lp + j] = mk(c, sn);
+                }
+            if (level_upload(p, tw, &h.tw[i])) return -1;
+            h.tw_len[i] = Lp > 1 ? Lp * nb : 0;
+            h.tw_soff[i] = -1;
+            if (h.tw_len[i] > 0 && (size_t)h.tw_len[i] <= room) {  // stage table also in shared memory
+                h.tw_soff[i] = off;
+                off += h.tw_len[i];
+                room -= h.tw_len[i];
+            }
+            Lcur = Lp;
+        }
+        max_tw = std::max(max_tw, off);
+        std::vector<cd> thi((size_t)(Nh + 127) / 128 + 1), tlo(128);
+        for (size_t j = 0; j < thi.size(); ++j) {
+            double c, sn;
+            exact_root((long long)j * 128, N, &c, &sn);
+            thi[j] = mk(c, sn);
+        }
+        for (int j = 0; j < 128; ++j) {
+            double c, sn;
+            exact_root(j, N, &c, &sn);
+            tlo[j] = mk(c, sn);
+        }
+        if (level_upload(p, thi, &BL.t_hi) || level_upload(p, tlo, &BL.t_lo)) return -1;
+    }
+    F.tw_smem_len = max_tw;
+    p->big_smem = CHF_RED_BYTES + ((size_t)maxNh + max_tw) * sizeof(cd);
+    return p->big_smem <= p->smem_limit ? 1 : 0;
 }
 
 extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
@@ -1115,6 +1241,24 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
             S.pair_dense = p->dense_smem[2] <= p->smem_limit ? 1 : 0;
         }
         if (getenv("CHB_PAIR_DENSE") && atoi(getenv("CHB_PAIR_DENSE")) == 0) S.pair_dense = 0;
+        // tiled one-sided kernel (cta_pair_tile) on the same conditions, up to 64 segments (A/B knob: CHB_PAIR_TILE=0)
+        S.pair_tilek = 0;
+        if (S.pair_dense && T.nsegm <= 64 && !(getenv("CHB_PAIR_TILE") && atoi(getenv("CHB_PAIR_TILE")) == 0)) {
+            const int nblk = (T.nsegm + CHB_TILE_SB - 1) / CHB_TILE_SB, ngrp = std::max(1, 8 / nblk);
+            const int TS = 32 * ngrp, SP = nblk * CHB_TILE_SB;
+            const size_t arrt = (size_t)SP * TS * sizeof(cd);
+            p->tile_threads = 32 * nblk * ngrp;
+            p->tile_smem[0] = red_bytes + arrt;
+            p->tile_smem[1] = red_bytes + 3 * arrt;
+            p->tile_smem[2] = red_bytes + 4 * arrt;
+            if (p->tile_smem[2] <= p->smem_limit) {
+                S.pair_tilek = 1;
+                S.tile_nblk = nblk;
+                S.tile_ngrp = ngrp;
+                S.pair_tile = TS;
+                S.pair_ntiles = (segm_store + TS - 1) / TS;
+            }
+        }
     }
     p->nint = nint;
     p->ready = true;
@@ -1132,6 +1276,13 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
             if (getenv("CHB_FUSED5") && atoi(getenv("CHB_FUSED5")) == 0) rc5 = 0;  // A/B knob
             p->fused5_active = rc5;
             p->fused_active = rc5;
+        }
+        p->big_active = 0;
+        {  // staged path (also the A/B path of fused layouts): parity-split transform kernels where the layout allows them
+            int rcb = big_setup(p, loops, segm_size, segm_store);
+            if (rcb < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: transform setup failed"); }
+            if (getenv("CHB_BIG") && atoi(getenv("CHB_BIG")) == 0) rcb = 0;  // A/B knob
+            p->big_active = rcb;
         }
         p->ready = true;
     }
@@ -1192,6 +1343,8 @@ extern "C" int chb_plan_query(const chb_plan *p, int what, int64_t *v) {
         case CHB_Q_SEGM_STORE: *v = p->sys.segm_store; break;
         case CHB_Q_SEGMPOS_SIZE: *v = p->sys.segsz; break;
         case CHB_Q_NPARAMS_INCL_O: *v = p->nparams_incl_o; break;
+        case CHB_Q_STAGED_TRANSFORM: *v = p->big_active ? 1 : 0; break;
+        case CHB_Q_PAIR_KERNEL: *v = p->sys.pair_tilek ? 2 : (p->sys.pair_dense ? 1 : 0); break;
 #ifdef CHB_HOSTSIM
         case CHB_Q_HOST_POINTERS: *v = 1; break;
 #else
@@ -1611,6 +1764,25 @@ CHB_KERNEL void k_pair_dense(ChbSys S, const double *seg, const double *dseg, do
                          globalmul, CHB_NTHREADS, spos, sdpos, sout, sw, red);
 }
 
+template <int MODE>
+CHB_KERNEL void
+#ifndef CHB_HOSTSIM
+__launch_bounds__(256, 2)
+#endif
+k_pair_tile(ChbSys S, const double *seg, const double *dseg, double *out, double *pot_part, double globalmul) {
+    CHB_CTX_DECL;
+    const long long blk = CHB_BLOCK_ID;
+    const int tile = (int)(blk % S.pair_ntiles);
+    const long long b = blk / S.pair_ntiles;
+    double *red = (double *)CHB_SMEM;
+    const size_t arr = (size_t)S.tile_nblk * CHB_TILE_SB * 32 * S.tile_ngrp;
+    cd *xs = (cd *)(red + 1024);
+    cd *accA = xs + arr, *accB = accA + arr, *dxs = accB + arr;
+    cta_pair_tile<MODE>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
+                        out ? out + b * S.segsz : (double *)0, pot_part ? pot_part + b * S.pair_ntiles + tile : (double *)0, tile,
+                        globalmul, S.tile_nblk, S.tile_ngrp, xs, dxs, accA, accB, red);
+}
+
 CHB_KERNEL void k_kin(ChbSys S, const double *params, double *kin_out, int kin_stride) {
     CHB_CTX_DECL;
     const long long b = CHB_BLOCK_ID;
@@ -1788,8 +1960,38 @@ CHB_KERNEL void CHF_BOUNDS k_fused5(CH5_SYS_PARAM, ChfArgs A) {
     for (long long k = CHB_BLOCK_ID; k < nwork; k += CHB_GRID_DIM) {
         const long long b = A.live_list ? (long long)A.live_list[k] : k;
         if (A.skip && A.skip[b]) continue;  // CTA-uniform
-        cta_fused5<NSEG, PMODE>(ctx, F, A, b, red, sm, bnd);
+        const long long kp = k + CHB_GRID_DIM;
+        const long long b_pf = kp < nwork ? (A.live_list ? (long long)A.live_list[kp] : kp) : A.nstates;
+        cta_fused5<NSEG, PMODE>(ctx, F, A, b, b_pf, red, sm, bnd);
     }
+}
+
+// parity-split staged transforms (chb_big.cuh): one CTA per (state, loop, parity)
+CHB_KERNEL void CHF_BOUNDS k_big_fwd(ChbBigSys F, ChbSys S, const double *params, double *segmpos, double *kin_part) {
+    CHB_CTX_DECL;
+    const long long blk = CHB_BLOCK_ID;
+    const int par = (int)(blk & 1);
+    const int il = (int)((blk >> 1) % F.nloop);
+    const long long b = (blk >> 1) / F.nloop;
+    const ChbBigLoop &L = F.loops[il];
+    double *red = (double *)CHB_SMEM;
+    cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
+    cd *tw = buf + L.h.N;
+    cta_big_prologue(ctx, L.h, tw);
+    cta_big_fwd(ctx, F, S, L, par, params + b * F.nparams, segmpos ? segmpos + b * F.segsz : (double *)0,
+                kin_part ? kin_part + b * F.nloop + il : (double *)0, buf, tw, red);
+}
+CHB_KERNEL void CHF_BOUNDS k_big_adj(ChbBigSys F, ChbSys S, const double *seg, double *out, const double *kin_src) {
+    CHB_CTX_DECL;
+    const long long blk = CHB_BLOCK_ID;
+    const int par = (int)(blk & 1);
+    const int il = (int)((blk >> 1) % F.nloop);
+    const long long b = (blk >> 1) / F.nloop;
+    const ChbBigLoop &L = F.loops[il];
+    cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
+    cd *tw = buf + L.h.N;
+    cta_big_prologue(ctx, L.h, tw);
+    cta_big_adj(ctx, F, S, L, par, seg + b * F.segsz, out + b * F.nparams, kin_src ? kin_src + b * F.nparams : (const double *)0, buf, tw);
 }
 
 #ifndef CHB_HOSTSIM
@@ -1852,12 +2054,21 @@ static unsigned long long smem_mask(const chb_plan *p) {
 
 static int launch_fwd(chb_plan *p, int64_t nb, const double *params, double *segmpos, Workspace &W, bool want_kin,
                       unsigned long long mask, chb_stream_t st) {
+    if (p->big_active) {
+        CHB_LAUNCH(p, k_big_fwd, 2 * nb * p->sys.nloop, p->bigsys.T, p->big_smem, st, p->bigsys, p->sys, params, segmpos,
+                   want_kin ? W.kin_part : (double *)0);
+        return CHB_OK;
+    }
     CHB_LAUNCH(p, k_fwd, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, p->sys, params, segmpos, W.scratch,
                want_kin ? W.kin_part : (double *)0, mask);
     return CHB_OK;
 }
 static int launch_adj(chb_plan *p, int64_t nb, const double *seg, double *out, const double *kin_src, Workspace &W,
                       int mode, unsigned long long mask, chb_stream_t st) {
+    if (p->big_active && mode == 0) {
+        CHB_LAUNCH(p, k_big_adj, 2 * nb * p->sys.nloop, p->bigsys.T, p->big_smem, st, p->bigsys, p->sys, seg, out, kin_src);
+        return CHB_OK;
+    }
     CHB_LAUNCH(p, k_adj, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, p->sys, seg, out, kin_src, W.scratch, mode,
                mask);
     return CHB_OK;
@@ -1872,6 +2083,15 @@ static int launch_pair(chb_plan *p, int mode, int64_t nb, const double *seg, con
 static int launch_pair_sys(chb_plan *p, const ChbSys &Sy, int mode, int64_t nb, const double *seg, const double *dseg,
                            double *out, double *pot_part, double globalmul, chb_stream_t st) {
     const long long grid = nb * p->sys.pair_ntiles;
+    if (p->sys.pair_tilek) {
+        if (mode == 0)
+            CHB_LAUNCH(p, k_pair_tile<0>, grid, p->tile_threads, p->tile_smem[0], st, Sy, seg, dseg, out, pot_part, globalmul);
+        else if (mode == 1)
+            CHB_LAUNCH(p, k_pair_tile<1>, grid, p->tile_threads, p->tile_smem[1], st, Sy, seg, dseg, out, pot_part, globalmul);
+        else
+            CHB_LAUNCH(p, k_pair_tile<2>, grid, p->tile_threads, p->tile_smem[2], st, Sy, seg, dseg, out, pot_part, globalmul);
+        return CHB_OK;
+    }
     if (p->sys.pair_dense) {
         if (mode == 0)
             CHB_LAUNCH(p, k_pair_dense<0>, grid, p->dense_threads, p->dense_smem[1], st, Sy, seg, dseg, out, pot_part, globalmul);

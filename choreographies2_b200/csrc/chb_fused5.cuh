@@ -41,6 +41,7 @@ struct Ch5Loop {
     int seq_stride;   // cd slots between the sequences of the loop
     int co_in[CHB_MAX_NPPL], co_prefix[CHB_MAX_NPPL];
     int nnz_k[CH5_MAX_NNZ];
+    int ikc[CH5_MAX_C];  // c / nppl: index into nnz_k of real sequence c (a table: no integer division in the kernels)
     double bre[2][CH5_MAX_C], bim[2][CH5_MAX_C];
     double alg_rot[4];
     cd wmir[CH5_MAX_NNZ];  // exp(+2 pi i nnz_k / ncoeff_min)
@@ -69,7 +70,7 @@ CHB_HD long long ch5_mom_index(const Ch5Loop &L, int n, int c) {
     return L.f.mom_off + (long long)n * L.C + c - L.f.nco_in;
 }
 CHB_HD double ch5_scale(const Ch5Loop &L, int n, int c, int *kout) {  // changevar_mom_pos (:4512-4566)
-    const int k = n * L.f.ncm + L.nnz_k[c / L.nppl];
+    const int k = n * L.f.ncm + L.nnz_k[L.ikc[c]];
     *kout = k;
     return k > 0 ? L.f.loopmul / (double)k : L.f.loopmul;
 }
@@ -144,7 +145,7 @@ struct Ch5Basis {  // the loop's basis and mirror factors in registers for the c
 #pragma unroll
         for (int c = 0; c < (CP > 0 ? 2 * CP : CH5_MAX_C); ++c) {
             if (c >= C) break;
-            ik[c] = c / L.nppl;
+            ik[c] = L.ikc[c];
             wmir[c] = L.wmir[ik[c]];
 #pragma unroll
             for (int g = 0; g < 2; ++g) { bre[g][c] = L.bre[g][c]; bim[g][c] = L.bim[g][c]; }
@@ -152,7 +153,7 @@ struct Ch5Basis {  // the loop's basis and mirror factors in registers for the c
     }
 };
 
-// one row n >= 1 of the parameter array: C values at rows[n C ..], harmonic k_c = n ncm + nnz_k[c / nppl] > 0
+// one row n >= 1 of the parameter array: C values at rows[n C ..], harmonic k_c = n ncm + nnz_k[ikc[c]] > 0
 template <int CP, class Grp>
 CHB_D void ch5_general_load(Grp &grp, const Ch5Loop &L, const double *vec_b, cd *buf, double *red, bool want_kin) {
     const int npr = L.f.npr, C = CP > 0 ? 2 * CP : L.C, Cp = CP > 0 ? CP : L.Cp;
@@ -190,7 +191,7 @@ CHB_D void ch5_general_load(Grp &grp, const Ch5Loop &L, const double *vec_b, cd 
                 double v[2];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    const int c = 2 * P + h, ik = c / nppl;
+                    const int c = 2 * P + h, ik = L.ikc[c];
                     if (ik != ik_prev) {
                         sc_prev = lm * chf_rcp((double)(n * ncm + L.nnz_k[ik]));
                         ik_prev = ik;
@@ -328,7 +329,7 @@ CHB_D void ch5_general_store(Grp &grp, const Ch5Loop &L, const cd *buf, const do
                 const cd y = buf[P * stride + sl];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    const int c = 2 * P + h, ik = c / nppl;
+                    const int c = 2 * P + h, ik = L.ikc[c];
                     if (ik != ik_prev) {
                         sc_prev = lm * chf_rcp((double)(n * ncm + L.nnz_k[ik]));
                         ik_prev = ik;
@@ -561,7 +562,7 @@ CHB_D void cta_fused5_prologue(Ctx &ctx, const Ch5Sys &F, cd *sm) {
 // the CTA program for one state
 // ------------------------------------------------------------------------------------------------
 template <int NSEG, int PMODE, class Ctx>
-CHB_D void cta_fused5(Ctx &ctx, const Ch5Sys &F, const ChfArgs &A, long long b, double *red, cd *sm, cd *bnd) {
+CHB_D void cta_fused5(Ctx &ctx, const Ch5Sys &F, const ChfArgs &A, long long b, long long b_pf, double *red, cd *sm, cd *bnd) {
     const double *vec_b = A.vec_in ? A.vec_in + b * F.nparams : (const double *)0;
     const double *kin_b = A.kin_src ? A.kin_src + b * F.nparams : (const double *)0;
     const double *seg_in_b = A.seg_in ? A.seg_in + b * F.segsz : (const double *)0;
@@ -580,6 +581,11 @@ CHB_D void cta_fused5(Ctx &ctx, const Ch5Sys &F, const ChfArgs &A, long long b, 
         } else {
             ch5_general_forward(grp, L, vec_b, buf, red, A.kin_from == 1, twsm);
         }
+        if (b_pf < A.nstates)  // ask L2 for the rows of the state this CTA takes next (they arrive while this one is computed)
+            grp.one([&]() {
+                chf_prefetch_l2(A.vec_in + b_pf * F.nparams, L.f.mom_off - L.f.nco_in, (long long)L.f.npr * L.C,
+                                A.vec_in + A.nstates * F.nparams);
+            });
         if (L.has_alg)  // Adjust_after_last_gen (:5290-5302): row 2 npr = alg_rot . row alg_src
             grp.par([&](int tid, int T) {
                 (void)T;

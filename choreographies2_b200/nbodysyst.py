@@ -115,6 +115,11 @@ class NBodySystB200:
         """0 = staged kernels, 3 / 4 = version of the fused kernel serving this nint level."""
         return self._q(L.Q_FUSED)
 
+    @property
+    def staged_kernels(self):
+        """(transform kind, pair kernel) of the staged path: (0 generic | 1 parity-split, 0 colour rounds | 1 dense | 2 tiled)."""
+        return self._q(L.Q_STAGED_TRANSFORM), self._q(L.Q_PAIR_KERNEL)
+
     def set_chunk(self, chunk: int) -> None:
         L.check(self._lib, self._lib.chb_plan_set_chunk(self._plan, int(chunk)))
         self._ws = None

@@ -107,7 +107,7 @@ def find_batched(make_nbs: Callable[[int], Any], x0, nint0: int, *, gradtol: flo
         go = np.ones(ids.size, dtype=bool)
         body_tables = getattr(nbs.tables, "bodysegm", None) is not None
         if Check_Escape and body_tables:  # find.py:290-297: an escaped loop ends the attempt before anything else is looked at
-            esc = np.asarray(nbs.DetectEscape(nbs.params_to_segmpos(best_x))).reshape(-1)
+            esc = np.asarray(xp.to_numpy(nbs.DetectEscape(nbs.params_to_segmpos(best_x)))).reshape(-1)
             out[esc], go = ESCAPED, go & ~esc
         hit = go & precise & ~needs_ref
         out[hit], go = FOUND, go & ~hit

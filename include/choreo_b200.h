@@ -123,6 +123,8 @@ enum chb_query {
     CHB_Q_LAUNCHES = 10,      /* kernels launched by this plan since creation (counter)  */
     CHB_Q_FUSED = 11,         /* 0: staged kernels; else the version of the fused single-kernel path that serves this level (3 or 4) */
     CHB_Q_SEGMPOS_SIZE = 12,  /* nsegm*segm_store*geodim                                 */
+    CHB_Q_STAGED_TRANSFORM = 15, /* staged path: 0 = generic per-loop kernels (any layout), 1 = parity-split kernels of planar RFFT systems */
+    CHB_Q_PAIR_KERNEL = 16,      /* staged pair kernel: 0 = colour rounds (any layout), 1 = dense two-sided, 2 = tiled one-sided */
     CHB_Q_NPARAMS_INCL_O = 14, /* NBodySyst.nparams_incl_o: length of the position-parameter array of params_changevar */
     CHB_Q_HOST_POINTERS = 13  /* 1 when the *_dev entry points of this build address host memory (CPU emulation build of the
                                  test suite), 0 for the CUDA library (device pointers only)                              */

@@ -19,6 +19,8 @@ def build(force=False):
     deps = [SRC, os.path.join(os.path.dirname(SRC), "chb_core.cuh"), os.path.join(os.path.dirname(SRC), "chb_fused.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_fused4.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_fused5.cuh"),
+            os.path.join(os.path.dirname(SRC), "chb_big.cuh"),
+            os.path.join(os.path.dirname(SRC), "chb_post.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_krylov.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_ode.cuh"),
             os.path.join(ROOT, "include", "choreo_b200.h")]

@@ -102,5 +102,5 @@ def test_postsolve_reductions_on_device_tensors():
     seg_h[3, 0] += 80.0
     seg_d = torch.from_numpy(seg_h).cuda()
     assert np.abs(nbs.ComputeCenterOfMass(seg_d).cpu().numpy() - nbs.ComputeCenterOfMass(seg_h)).max() < 1e-12
-    assert np.array_equal(nbs.DetectEscape(seg_d), nbs.DetectEscape(seg_h))
-    assert np.array_equal(nbs.DetectEscape(seg_d, 0.01), nbs.DetectEscape(seg_h, 0.01))
+    assert np.array_equal(nbs.DetectEscape(seg_d).cpu().numpy(), nbs.DetectEscape(seg_h))
+    assert np.array_equal(nbs.DetectEscape(seg_d, 0.01).cpu().numpy(), nbs.DetectEscape(seg_h, 0.01))
