@@ -97,6 +97,8 @@ SYMBOLS = {
     "chb_detect_escape_dev": (C.c_int, _dev_op + [_vp, C.c_double, _vp, _vp]),
     "chb_path_stats_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _vp]),
     "chb_compute_velocities_dev": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
+    "chb_newton_workspace_bytes": (C.c_int, [_vp, _i64, C.c_int, C.POINTER(_sz)]),
+    "chb_newton_krylov_dev": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "chb_run_host": (C.c_int, [_vp, C.c_int, _i64, _vp, _vp, C.c_double, _vp, _vp]),
     "chb_malloc_device": (C.c_int, [_vp, _sz, C.POINTER(_vp)]),
     "chb_free_device": (C.c_int, [_vp, _vp]),
@@ -106,6 +108,11 @@ SYMBOLS = {
     "chb_memcpy_d2h": (C.c_int, [_vp, _vp, _vp, _sz, _vp]),
     "chb_stream_synchronize": (C.c_int, [_vp, _vp]),
 }
+
+
+class chb_newton_opts(C.Structure):
+    _fields_ = [("f_tol", C.c_double), ("smin", C.c_double), ("maxiter", C.c_int32), ("restart", C.c_int32),
+                ("line_search", C.c_int32), ("tol_norm", C.c_int32)]
 
 
 class ChoreoB200Error(RuntimeError):

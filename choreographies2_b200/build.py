@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libchoreo_b200.so")
 SOURCES = ["chb_api.cu"]
-HEADERS = ["chb_core.cuh", "chb_fused.cuh", "chb_fused4.cuh", "chb_fused5.cuh", "chb_big.cuh", "chb_post.cuh", "chb_krylov.cuh", "chb_ode.cuh", os.path.join("..", "..", "include", "choreo_b200.h")]
+HEADERS = ["chb_core.cuh", "chb_fused.cuh", "chb_fused4.cuh", "chb_fused5.cuh", "chb_big.cuh", "chb_post.cuh", "chb_newton.cuh", "chb_krylov.cuh", "chb_ode.cuh", os.path.join("..", "..", "include", "choreo_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

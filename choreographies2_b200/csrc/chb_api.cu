@@ -29,6 +29,7 @@
 #include "chb_big.cuh"
 #include "chb_ode.cuh"
 #include "chb_post.cuh"
+#include "chb_newton.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // errors
@@ -1241,9 +1242,12 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
             S.pair_dense = p->dense_smem[2] <= p->smem_limit ? 1 : 0;
         }
         if (getenv("CHB_PAIR_DENSE") && atoi(getenv("CHB_PAIR_DENSE")) == 0) S.pair_dense = 0;
-        // tiled one-sided kernel (cta_pair_tile) on the same conditions, up to 64 segments (A/B knob: CHB_PAIR_TILE=0)
+        // tiled one-sided kernel (cta_pair_tile) on the same conditions, up to 64 segments.  Measured on B200 (profiles/
+        // r02_configs.txt): 17 FP64 instructions per unordered pair instead of 30, but only 22 % FP64 pipe utilisation (two
+        // 8-warp CTAs per SM, weight loads and predicates per pair) against 62 % for cta_pair_dense: 0.78 ms vs 0.36 ms per 256
+        // states of 64C.  Kept as an opt-in A/B path (CHB_PAIR_TILE=1); the dense kernel is the default.
         S.pair_tilek = 0;
-        if (S.pair_dense && T.nsegm <= 64 && !(getenv("CHB_PAIR_TILE") && atoi(getenv("CHB_PAIR_TILE")) == 0)) {
+        if (S.pair_dense && T.nsegm <= 64 && getenv("CHB_PAIR_TILE") && atoi(getenv("CHB_PAIR_TILE")) == 1) {
             const int nblk = (T.nsegm + CHB_TILE_SB - 1) / CHB_TILE_SB, ngrp = std::max(1, 8 / nblk);
             const int TS = 32 * ngrp, SP = nblk * CHB_TILE_SB;
             const size_t arrt = (size_t)SP * TS * sizeof(cd);
@@ -2534,6 +2538,363 @@ extern "C" int chb_segmpos_dparams_to_action_hess_listed_dev(chb_plan *p, int64_
                                                              double *hess, void *ws, size_t ws_bytes, void *stream) {
     CHB_REQUIRE(live_list && live_count, CHB_ERR_INVALID_ARGUMENT, "chb_segmpos_dparams_to_action_hess_listed_dev: NULL list");
     return hess_common(p, batch, segmpos, dparams, nullptr, live_list, live_count, hess, ws, ws_bytes, stream);
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// Batched Newton-Krylov driver, whole solve inside the library (chb_newton.cuh): the host sequences launches and reads counters,
+// every per-state decision (termination, forcing term, Armijo / Wolfe line search, best iterate) is taken on the device.
+// ------------------------------------------------------------------------------------------------
+struct NkArrays {  // device arrays of one solve, carved from the caller's workspace
+    double *V, *w, *F, *Ft, *Fd, *xt, *dx, *seg, *R, *g, *cs, *target, *ns, *phi_t, *fmax_t, *xn2, *dxn2;
+    long long *kdone;
+    unsigned char *done, *mask;
+    int *lists, *counts;  // lists [2][B]; counts [m + 8]: [0..m] GMRES live counts, [m + 1] live states, [m + 2], [m + 3] pending evaluations of kind 1 / 2
+    void *opws;
+    size_t opws_bytes;
+};
+static size_t nk_ws_bytes(const chb_plan *p, int64_t B, int m) {
+    const size_t n = (size_t)p->sys.nparams, ss = (size_t)p->sys.segsz, Bz = (size_t)B;
+    size_t b = 0;
+    b += align_up(sizeof(double) * (size_t)(m + 1) * Bz * n);      // V
+    b += 6 * align_up(sizeof(double) * Bz * n);                    // w F Ft Fd xt dx
+    b += align_up(sizeof(double) * Bz * ss);                       // seg
+    b += align_up(sizeof(double) * Bz * (size_t)(m + 1) * m) + align_up(sizeof(double) * Bz * (m + 1)) + align_up(sizeof(double) * Bz * m * 2);
+    b += align_up(sizeof(double) * Bz) * 5 + align_up(sizeof(double) * Bz * NK_STRIDE);
+    b += align_up(sizeof(long long) * Bz) + 2 * align_up(Bz) + align_up(sizeof(int) * 2 * Bz) + align_up(sizeof(int) * (size_t)(m + 8));
+    size_t op = 0;
+    chb_workspace_bytes(p, B, &op);
+    return b + align_up(op) + 512;
+}
+static NkArrays nk_carve(const chb_plan *p, void *base, int64_t B, int m) {
+    const size_t n = (size_t)p->sys.nparams, ss = (size_t)p->sys.segsz, Bz = (size_t)B;
+    NkArrays a;
+    char *q = (char *)(((uintptr_t)base + 255) & ~(uintptr_t)255);
+    auto take = [&](size_t bytes) { char *r = q; q += align_up(bytes); return (void *)r; };
+    a.V = (double *)take(sizeof(double) * (size_t)(m + 1) * Bz * n);
+    a.w = (double *)take(sizeof(double) * Bz * n);
+    a.F = (double *)take(sizeof(double) * Bz * n);
+    a.Ft = (double *)take(sizeof(double) * Bz * n);
+    a.Fd = (double *)take(sizeof(double) * Bz * n);
+    a.xt = (double *)take(sizeof(double) * Bz * n);
+    a.dx = (double *)take(sizeof(double) * Bz * n);
+    a.seg = (double *)take(sizeof(double) * Bz * ss);
+    a.R = (double *)take(sizeof(double) * Bz * (size_t)(m + 1) * m);
+    a.g = (double *)take(sizeof(double) * Bz * (m + 1));
+    a.cs = (double *)take(sizeof(double) * Bz * m * 2);
+    a.target = (double *)take(sizeof(double) * Bz);
+    a.phi_t = (double *)take(sizeof(double) * Bz);
+    a.fmax_t = (double *)take(sizeof(double) * Bz);
+    a.xn2 = (double *)take(sizeof(double) * Bz);
+    a.dxn2 = (double *)take(sizeof(double) * Bz);
+    a.ns = (double *)take(sizeof(double) * Bz * NK_STRIDE);
+    a.kdone = (long long *)take(sizeof(long long) * Bz);
+    a.done = (unsigned char *)take(Bz);
+    a.mask = (unsigned char *)take(Bz);
+    a.lists = (int *)take(sizeof(int) * 2 * Bz);
+    a.counts = (int *)take(sizeof(int) * (size_t)(m + 8));
+    a.opws = (void *)q;
+    a.opws_bytes = 0;
+    chb_workspace_bytes(p, B, &a.opws_bytes);
+    return a;
+}
+
+// ---- one thread per state ----
+#ifndef CHB_HOSTSIM
+#define NK_FOR_STATE(b, B) const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x; if (b < (B))
+#define NK_ATOMIC_INC(ptr) atomicAdd((ptr), 1)
+#else
+#define NK_FOR_STATE(b, B) for (long long b = sim_block_id * sim_nthreads; b < (B) && b < (sim_block_id + 1) * sim_nthreads; ++b)
+static inline int nk_host_inc(int *p) { return (*p)++; }
+#define NK_ATOMIC_INC(ptr) nk_host_inc(ptr)
+#endif
+// first residual: norms of F(x0), eta = 1e-3, best iterate = x0
+CHB_KERNEL void k_nk_init(long long B, double *ns, const double *sumsq, const double *fmax) {
+    NK_FOR_STATE(b, B) {
+        double *st = ns + b * NK_STRIDE;
+        for (int k = 0; k < NK_STRIDE; ++k) st[k] = 0.0;
+        st[NK_ETA] = 1e-3;
+        st[NK_FNORM] = sqrt(sumsq[b]);
+        st[NK_FMAX] = fmax[b];
+        const double f = st[NK_FNORM];
+        st[NK_BEST] = (f == f) ? f : 1e100;
+    }
+}
+CHB_KERNEL void k_nk_begin(long long B, double *ns, NkOpts O, int m, double *g, double *target, long long *kdone, unsigned char *done,
+                           unsigned char *mask, int *list0, int *counts) {
+    NK_FOR_STATE(b, B) {
+        double *st = ns + b * NK_STRIDE;
+        const int live = nk_begin_state(st, O);
+        done[b] = live ? 0 : 1;
+        mask[b] = live ? 0 : 1;
+        kdone[b] = 0;
+        if (live) {
+            g[b * (m + 1)] = st[NK_FNORM];               // beta
+            target[b] = st[NK_TOL] * st[NK_FNORM];       // rtol * |rhs|
+            list0[NK_ATOMIC_INC(&counts[0])] = (int)b;
+            NK_ATOMIC_INC(&counts[m + 1]);
+        }
+    }
+}
+CHB_KERNEL void k_nk_ls_start(long long B, double *ns, NkOpts O, const double *xn2, const double *dxn2, int *counts, int m) {
+    NK_FOR_STATE(b, B) {
+        double *st = ns + b * NK_STRIDE;
+        st[NK_XNORM2] = xn2[b];
+        st[NK_DXNORM2] = dxn2[b];
+        nk_ls_start(st, O);
+        const int t = (int)st[NK_LS_TASK];
+        if (t == 1) NK_ATOMIC_INC(&counts[m + 2]);
+        if (t == 2) NK_ATOMIC_INC(&counts[m + 3]);
+    }
+}
+// mask[b] = 0 for the states that want an evaluation of this kind
+CHB_KERNEL void k_nk_mask(long long B, const double *ns, int kind, unsigned char *mask) {
+    NK_FOR_STATE(b, B) { mask[b] = ((int)ns[b * NK_STRIDE + NK_LS_TASK] == kind) ? 0 : 1; }
+}
+CHB_KERNEL void k_nk_ls_update(long long B, double *ns, NkOpts O, int kind, const double *phi_t, const double *fmax_t, int *counts, int m) {
+    NK_FOR_STATE(b, B) {
+        double *st = ns + b * NK_STRIDE;
+        nk_ls_update(st, O, kind, phi_t[b], fmax_t[b]);
+        const int t = (int)st[NK_LS_TASK];
+        if (t == 1) NK_ATOMIC_INC(&counts[m + 2]);
+        if (t == 2) NK_ATOMIC_INC(&counts[m + 3]);
+    }
+}
+// end of the iteration: forcing terms; mask[b] = 0 where the new iterate is the best so far (current_best.update, nonlin.py:13-39)
+CHB_KERNEL void k_nk_end(long long B, double *ns, NkOpts O, unsigned char *mask) {
+    NK_FOR_STATE(b, B) {
+        double *st = ns + b * NK_STRIDE;
+        const bool live = st[NK_LIVE] != 0.0;
+        nk_end_state(st, O);
+        bool better = false;
+        if (live && st[NK_FNORM] < st[NK_BEST]) {
+            st[NK_BEST] = st[NK_FNORM];
+            better = true;
+        }
+        mask[b] = better ? 0 : 1;
+    }
+}
+CHB_KERNEL void k_nk_finish(long long B, const double *ns, int32_t *status, int32_t *nit, double *fmax, double *fnorm2, double *best_fnorm) {
+    NK_FOR_STATE(b, B) {
+        const double *st = ns + b * NK_STRIDE;
+        const int s = (int)st[NK_STATUS];
+        status[b] = s == 0 ? 2 : s;  // still running after maxiter iterations: status 2 (the for / else of nonlin.py:109-156)
+        nit[b] = (int)st[NK_NIT];
+        if (fmax) fmax[b] = st[NK_FMAX];
+        if (fnorm2) fnorm2[b] = st[NK_FNORM];
+        if (best_fnorm) best_fnorm[b] = st[NK_BEST];
+    }
+}
+
+// ---- one CTA per state: row operations ----
+// op 0: out = a / |F|          (first Krylov vector)          rows with NK_LIVE
+// op 1: out = a + s_eval * d   (trial point)                  rows whose mask byte is 0
+// op 2: a += s_final * d, c = e  (accept: x, F)               rows with NK_LIVE
+// op 3: out = a                (best iterate)                 rows whose mask byte is 0
+CHB_KERNEL void k_nk_rows(long long n, int op, const double *ns, const unsigned char *mask, double *out, double *a, const double *d,
+                          double *c, const double *e) {
+    const long long b = CHB_BLOCK_ID;
+    const double *st = ns + b * NK_STRIDE;
+    if ((op == 0 || op == 2) && st[NK_LIVE] == 0.0) return;
+    if ((op == 1 || op == 3) && mask[b]) return;
+    const double s = op == 0 ? 1.0 / st[NK_FNORM] : (op == 1 ? st[NK_S_EVAL] : st[NK_S_FINAL]);
+    const size_t o = (size_t)b * n;
+#ifndef CHB_HOSTSIM
+    for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+#else
+    for (long long i = 0; i < n; ++i) {
+#endif
+        if (op == 0) out[o + i] = a[o + i] * s;
+        else if (op == 1) out[o + i] = fma(s, d[o + i], a[o + i]);
+        else if (op == 2) { a[o + i] = fma(s, d[o + i], a[o + i]); c[o + i] = e[o + i]; }
+        else out[o + i] = a[o + i];
+    }
+}
+// per-row sum of squares (non-finite when the row has a non-finite entry) and max |.| of the rows whose mask byte is 0 (NULL: all)
+CHB_KERNEL void k_nk_row_stats(long long n, const double *a, const unsigned char *mask, double *sumsq, double *maxabs) {
+    const long long b = CHB_BLOCK_ID;
+    if (mask && mask[b]) return;
+    const double *r = a + (size_t)b * n;
+#ifndef CHB_HOSTSIM
+    __shared__ double s1[8], s2[8];
+    double p = 0.0, mx = 0.0;
+    for (long long e = threadIdx.x; e < n; e += 256) {
+        const double x = r[e];
+        p = fma(x, x, p);
+        mx = fmax(mx, fabs(x));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        p += __shfl_xor_sync(0xffffffffu, p, o);
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if ((threadIdx.x & 31) == 0) { s1[threadIdx.x >> 5] = p; s2[threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double P = 0.0, M = 0.0;
+        for (int i = 0; i < 8; ++i) { P += s1[i]; M = fmax(M, s2[i]); }
+        sumsq[b] = P;
+        if (maxabs) maxabs[b] = M;
+    }
+#else
+    double p = 0.0, mx = 0.0;
+    for (long long e = 0; e < n; ++e) { p += r[e] * r[e]; mx = std::fmax(mx, std::fabs(r[e])); }
+    sumsq[b] = p;
+    if (maxabs) maxabs[b] = mx;
+#endif
+}
+
+static int nk_read_counts(chb_plan *p, const int *d_counts, int n, int *h, chb_stream_t st) {
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaMemcpyAsync(h, d_counts, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+    CHB_CUDA(cudaStreamSynchronize(st));
+#else
+    (void)st;
+    memcpy(h, d_counts, sizeof(int) * n);
+#endif
+    (void)p;
+    return CHB_OK;
+}
+static int nk_zero(void *d, size_t bytes, chb_stream_t st) {
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaMemsetAsync(d, 0, bytes, st));
+#else
+    (void)st;
+    memset(d, 0, bytes);
+#endif
+    return CHB_OK;
+}
+// gradient of the action at the rows whose mask byte is 0 (all rows when mask == NULL); the staged kernels compute every row
+static int nk_grad(chb_plan *p, int64_t B, const double *x, double *grad, const unsigned char *mask, NkArrays &A, chb_stream_t st) {
+    if (use_fused(p)) {
+        ChfArgs a = chf_args(x, x, nullptr, nullptr, grad, nullptr, 0);
+        a.skip = mask;
+        return launch_fused(p, 1, B, a, st);
+    }
+    return chb_params_to_action_grad_dev(p, B, x, nullptr, grad, nullptr, A.opws, A.opws_bytes, (void *)st);
+}
+static int nk_segmpos(chb_plan *p, int64_t B, const double *x, double *seg, const unsigned char *mask, NkArrays &A, chb_stream_t st) {
+    if (use_fused(p)) {
+        ChfArgs a = chf_args(x, nullptr, nullptr, seg, nullptr, nullptr, 0);
+        a.skip = mask;
+        return launch_fused(p, 3, B, a, st);
+    }
+    return chb_params_to_segmpos_dev(p, B, x, seg, A.opws, A.opws_bytes, (void *)st);
+}
+
+extern "C" int chb_newton_workspace_bytes(const chb_plan *p, int64_t batch, int restart, size_t *bytes) {
+    CHB_REQUIRE(p && bytes && batch >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_newton_workspace_bytes: bad argument");
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_newton_workspace_bytes: call chb_plan_set_nint first");
+    CHB_REQUIRE(restart >= 1 && restart <= 62, CHB_ERR_INVALID_ARGUMENT, "chb_newton_workspace_bytes: 1 <= restart <= 62");
+    *bytes = nk_ws_bytes(p, std::max<int64_t>(batch, 1), restart);
+    return CHB_OK;
+}
+
+extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, const chb_newton_opts *opts, int32_t *status, int32_t *nit,
+                                     double *fnorm_max, double *fnorm_2, double *best_x, double *best_fnorm, int64_t *counters,
+                                     void *ws, size_t ws_bytes, void *stream) {
+    CHB_REQUIRE(p && opts, CHB_ERR_INVALID_ARGUMENT, "chb_newton_krylov_dev: NULL plan / options");
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_newton_krylov_dev: call chb_plan_set_nint first");
+    CHB_REQUIRE(batch >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_newton_krylov_dev: negative batch");
+    if (counters) counters[0] = counters[1] = counters[2] = counters[3] = 0;
+    if (batch == 0) return CHB_OK;
+    CHB_REQUIRE(x && status && nit, CHB_ERR_INVALID_ARGUMENT, "chb_newton_krylov_dev: NULL array");
+    CHB_REQUIRE(opts->line_search >= 0 && opts->line_search <= 2, CHB_ERR_INVALID_ARGUMENT,
+                "chb_newton_krylov_dev: line_search must be 0 (none), 1 (armijo) or 2 (wolfe)");
+    CHB_REQUIRE(opts->tol_norm == 0 || opts->tol_norm == 1, CHB_ERR_INVALID_ARGUMENT, "chb_newton_krylov_dev: tol_norm must be 0 (max) or 1 (2-norm)");
+    CHB_REQUIRE(opts->restart >= 1 && opts->restart <= 62 && opts->maxiter >= 0, CHB_ERR_INVALID_ARGUMENT,
+                "chb_newton_krylov_dev: need 1 <= restart <= 62, maxiter >= 0");
+    const int m = opts->restart;
+    const long long n = p->sys.nparams;
+    CHB_REQUIRE(n * 8 <= 200 * 1024, CHB_ERR_UNSUPPORTED, "chb_newton_krylov_dev: more than 25600 parameters per state");
+    CHB_REQUIRE(ws && ws_bytes >= nk_ws_bytes(p, batch, m), CHB_ERR_WORKSPACE, "chb_newton_krylov_dev: workspace missing or too small");
+    CHB_SET_DEVICE();
+    chb_stream_t st = (chb_stream_t)stream;
+    NkArrays A = nk_carve(p, ws, batch, m);
+    NkOpts O;
+    O.f_tol = opts->f_tol; O.smin = opts->smin; O.maxiter = opts->maxiter; O.restart = m;
+    O.line_search = opts->line_search; O.tol_norm = opts->tol_norm; O.track_best = best_x ? 1 : 0;
+    const long long B = batch;
+    const unsigned gs = (unsigned)((B + 127) / 128);
+    const int64_t l0 = p->launches;
+    int64_t n_u1 = 0, n_u2 = 0, n_it = 0;
+    int hc[4];
+    // F(x0), norms, per-state scalars
+    CHB_TRY(nk_grad(p, B, x, A.F, nullptr, A, st));
+    n_u1 += B;
+    CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, A.F, (const unsigned char *)nullptr, A.phi_t, A.fmax_t);
+    CHB_LAUNCH(p, k_nk_init, gs, 128, 0, st, B, A.ns, A.phi_t, A.fmax_t);
+    if (best_x) {
+        CHB_TRY(nk_zero(A.mask, (size_t)B, st));
+        CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr);
+    }
+    for (int it = 0; it < opts->maxiter; ++it) {
+        CHB_TRY(nk_zero(A.counts, sizeof(int) * (size_t)(m + 8), st));
+        CHB_LAUNCH(p, k_nk_begin, gs, 128, 0, st, B, A.ns, O, m, A.g, A.target, A.kdone, A.done, A.mask, A.lists, A.counts);
+        CHB_TRY(nk_read_counts(p, A.counts + m + 1, 1, hc, st));
+        const int nlive = hc[0];
+        if (nlive == 0) break;
+        ++n_it;
+        // jacobian.setup / update (:2013-2019): segment positions of the current iterate; first Krylov vector F / |F|
+        CHB_TRY(nk_segmpos(p, B, x, A.seg, A.mask, A, st));
+        CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 0, A.ns, A.mask, A.V, A.F, (const double *)nullptr, (double *)nullptr, (const double *)nullptr);
+        // GMRES(m), one cycle, zero initial guess: per inner iteration one Hessian-vector launch over the running states and one
+        // step launch (Arnoldi + Givens + stopping test + the list of the next iteration)
+        for (int j = 0; j < m; ++j) {
+            if (j > 0 && (j & 3) == 0) {
+                CHB_TRY(nk_read_counts(p, A.counts + j, 1, hc, st));
+                if (hc[0] == 0) break;
+            }
+            CHB_TRY(hess_common(p, B, A.seg, A.V + (size_t)j * B * n, nullptr, A.lists + (size_t)(j & 1) * B, A.counts + j, A.w, A.opws,
+                                A.opws_bytes, (void *)st));
+            CHB_TRY(chb_gmres_step_dev(p, B, n, j, m, A.V, A.w, A.done, A.R, A.g, A.cs, A.target, (int64_t *)A.kdone,
+                                       A.lists + (size_t)((j + 1) & 1) * B, A.counts + j + 1, (void *)st));
+        }
+        CHB_TRY(chb_gmres_solution_dev(p, B, n, m, A.V, A.R, A.g, (const int64_t *)A.kdone, -1.0, A.dx, (void *)st));  // dx = -J^-1 F
+        // line search on phi(s) = |F(x + s dx)|^2
+        CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, (const double *)x, (const unsigned char *)A.mask, A.xn2, (double *)nullptr);
+        CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, (const double *)A.dx, (const unsigned char *)A.mask, A.dxn2, (double *)nullptr);
+        CHB_TRY(nk_zero(A.counts + m + 2, 2 * sizeof(int), st));
+        CHB_LAUNCH(p, k_nk_ls_start, gs, 128, 0, st, B, A.ns, O, A.xn2, A.dxn2, A.counts, m);
+        {   // one read: the live counts of the GMRES iterations (Hessian-vector evaluations) and the pending evaluations
+            std::vector<int> all((size_t)m + 4);
+            CHB_TRY(nk_read_counts(p, A.counts, m + 4, all.data(), st));
+            for (int j = 0; j < m; ++j) n_u2 += all[j];
+            hc[0] = all[m + 2];
+            hc[1] = all[m + 3];
+        }
+        int guard = 0;
+        while ((hc[0] > 0 || hc[1] > 0) && guard++ < 400) {
+            const int use_kind = hc[1] > 0 ? 2 : 1;  // probes first: a state alternates probe / stored evaluations
+            double *Fout = use_kind == 1 ? A.Ft : A.Fd;
+            CHB_LAUNCH(p, k_nk_mask, gs, 128, 0, st, B, A.ns, use_kind, A.mask);
+            CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 1, A.ns, A.mask, A.xt, x, (const double *)A.dx, (double *)nullptr, (const double *)nullptr);
+            CHB_TRY(nk_grad(p, B, A.xt, Fout, A.mask, A, st));
+            n_u1 += use_kind == 1 ? hc[0] : hc[1];
+            CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, (const double *)Fout, (const unsigned char *)A.mask, A.phi_t, A.fmax_t);
+            CHB_TRY(nk_zero(A.counts + m + 2, 2 * sizeof(int), st));
+            CHB_LAUNCH(p, k_nk_ls_update, gs, 128, 0, st, B, A.ns, O, use_kind, A.phi_t, A.fmax_t, A.counts, m);
+            CHB_TRY(nk_read_counts(p, A.counts + m + 2, 2, hc, st));
+        }
+        // accept: x += s dx, F = F(x + s dx) (the stored evaluation), forcing terms, best iterate
+        CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 2, A.ns, A.mask, (double *)nullptr, x, (const double *)A.dx, A.F, (const double *)A.Ft);
+        CHB_LAUNCH(p, k_nk_end, gs, 128, 0, st, B, A.ns, O, A.mask);
+        if (best_x)
+            CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr);
+    }
+    CHB_LAUNCH(p, k_nk_finish, gs, 128, 0, st, B, A.ns, status, nit, fnorm_max, fnorm_2, best_fnorm);
+    {
+        if (counters) {
+            counters[0] = n_u1;
+            counters[1] = n_u2;
+            counters[2] = p->launches - l0;
+            counters[3] = n_it;
+        }
+    }
+#ifndef CHB_HOSTSIM
+    CHB_CUDA(cudaStreamSynchronize(st));
+#endif
+    return CHB_OK;
 }
 
 // per-row sum of squares and max |.| of a [batch][n] array in one pass (norms of the Newton driver)

@@ -499,10 +499,11 @@ CHB_D void ch5_pair(Ctx &ctx, const Ch5Sys &F, cd *sm, bool have_fwd, const doub
             }
         }
         if (gns) {
-            // end samples (trapezoid weight 1/2): thread 0 takes i = 0, the first thread of the next warp i = segm_size
-            const int t2 = nthr > 32 ? 32 : 0;
+            // end samples (trapezoid weight 1/2): the last threads of the last two warps take them (they own the fewest
+            // interior samples), i = 0 and i = segm_size
+            const int t1 = nthr - 1, t2 = nthr > 32 ? nthr - 33 : nthr - 1;
             for (int which = 0; which < 2; ++which) {
-                if (tid != (which == 0 ? 0 : t2)) continue;
+                if (tid != (which == 0 ? t1 : t2)) continue;
                 const int i = which == 0 ? 0 : F.segm_size;
                 Ch5Samp<NSEG, PMODE> r;
                 int slot[NSEG];

@@ -655,6 +655,60 @@ class NBodySystB200:
                                                         ptr(live_count_next) if live_count_next is not None else None, stream))
         return True
 
+    def newton_krylov(self, x, f_tol: float, maxiter: int, restart: int = 20, smin: float = 1e-2, line_search: Optional[str] = "armijo",
+                      tol_norm: str = "max", track_best: bool = False):
+        """The whole batched Newton-Krylov solve inside the library (``chb_newton_krylov_dev``): ``x`` ``[batch, nparams]`` is
+        updated IN PLACE (torch CUDA tensor, or a NumPy array with the emulation build).  Returns a dict with ``status``,
+        ``nit`` (int32 arrays of the carrier), ``fnorm_max``, ``fnorm_2``, ``best_x`` / ``best_fnorm`` (when ``track_best``)
+        and the counters ``n_grad_evals``, ``n_hess_evals``, ``launches``, ``iterations``; None when the library cannot
+        address ``x``."""
+        if not self._direct_ok(x):
+            return None
+        ls = {None: 0, "armijo": 1, "wolfe": 2}
+        if line_search not in ls:
+            raise ValueError(f"line_search must be None, 'armijo' or 'wolfe' (nonlin.py:129), got {line_search!r}")
+        if tol_norm not in ("max", "l2"):
+            raise ValueError("tol_norm must be 'max' or 'l2'")
+        b, n = int(x.shape[0]), int(x.shape[1])
+        if n != self.nparams:
+            raise ValueError(f"x: expected trailing shape ({self.nparams},), got {tuple(x.shape)}")
+        opts = L.chb_newton_opts(float(f_tol), float(smin), int(maxiter), int(restart), ls[line_search], 1 if tol_norm == "l2" else 0)
+        need = C.c_size_t()
+        L.check(self._lib, self._lib.chb_newton_workspace_bytes(self._plan, b, int(restart), C.byref(need)))
+        counters = (C.c_int64 * 4)()
+        if _is_torch(x):
+            import torch
+            if x.dtype != torch.float64 or not x.is_cuda or not x.is_contiguous():
+                raise ValueError("newton_krylov: x must be a contiguous float64 CUDA tensor")
+            mk = lambda shape, dt: torch.empty(shape, dtype=dt, device=x.device)  # noqa: E731
+            i32, f64 = torch.int32, torch.float64
+            key = ("nk_ws", str(x.device))
+            ws = getattr(self, "_nk_ws", None)
+            if ws is None or ws.numel() < need.value or ws.device != x.device:
+                self._nk_ws = None
+                ws = self._nk_ws = torch.empty(int(need.value), dtype=torch.uint8, device=x.device)
+            vp = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
+            stream = C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)
+            wsp, wsn = C.c_void_p(ws.data_ptr()), ws.numel()
+        else:
+            if x.dtype != np.float64 or not x.flags.c_contiguous:
+                raise ValueError("newton_krylov: x must be a C-contiguous float64 array")
+            mk = lambda shape, dt: np.empty(shape, dtype=dt)  # noqa: E731
+            i32, f64 = np.int32, np.float64
+            ws = np.empty(int(need.value), dtype=np.uint8)
+            vp = lambda t: C.c_void_p(t.ctypes.data) if t is not None else None  # noqa: E731
+            stream = None
+            wsp, wsn = C.c_void_p(ws.ctypes.data), ws.size
+        status, nit = mk((b,), i32), mk((b,), i32)
+        fmax, f2 = mk((b,), f64), mk((b,), f64)
+        best_x = mk((b, n), f64) if track_best else None
+        best_f = mk((b,), f64) if track_best else None
+        L.check(self._lib, self._lib.chb_newton_krylov_dev(self._plan, b, vp(x), C.byref(opts), vp(status), vp(nit), vp(fmax), vp(f2),
+                                                            vp(best_x), vp(best_f), counters, wsp, wsn, stream))
+        return {"status": status, "nit": nit, "fnorm_max": fmax, "fnorm_2": f2, "best_x": best_x, "best_fnorm": best_f,
+                "n_grad_evals": int(counters[0]), "n_hess_evals": int(counters[1]), "launches": int(counters[2]),
+                "iterations": int(counters[3])}
+
     # ------------------------------------------------------------------ post-solve reductions (find.py:285-308, 376-380)
     def ComputeCenterOfMass(self, segmpos):
         """_NBodySyst.pyx:3968-4009, batched (``chb_center_of_mass_dev``, one CTA per state): mass-weighted mean position over

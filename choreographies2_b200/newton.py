@@ -107,6 +107,7 @@ class NewtonResult:
     n_hess_evals: int      # U2 evaluations
     best_x: Any = None     # [B, nparams] iterate with the smallest 2-norm of the gradient seen (track_best; nonlin.py:13-39)
     best_fnorm: Any = None  # [B] that 2-norm (array of the carrier)
+    launches: int = 0      # kernel launches of the solve (library driver)
 
 
 def gmres_batched(xp: _XP, matvec, rhs, rtol, restart: int = 20, arnoldi=None, step=None):
@@ -272,6 +273,22 @@ def newton_krylov_batched(nbs, x0, f_tol: float = 1e-10, maxiter: int = 50, rest
     ``track_best``: also return, per state, the iterate with the smallest gradient 2-norm (``current_best``, find.py:204,252)."""
     if tol_norm not in ("max", "l2"):
         raise ValueError("tol_norm must be 'max' or 'l2'")
+    if line_search not in (None, "armijo", "wolfe"):
+        raise ValueError(f"line_search must be None, 'armijo' or 'wolfe' (nonlin.py:129), got {line_search!r}")
+    # the whole solve inside the library (per-state control on the device, no array-level glue) when it can address the arrays
+    if hasattr(nbs, "newton_krylov") and nbs._direct_ok(x0) and os.environ.get("CHB_NEWTON_LIB", "1") not in ("", "0"):
+        xp = _XP(x0)
+        x = xp.copy(x0)
+        if xp.torch and not x.is_contiguous():
+            x = x.contiguous()
+        r = nbs.newton_krylov(x, f_tol, maxiter, restart, smin, line_search, tol_norm, track_best)
+        if r is not None:
+            return NewtonResult(x=x, status=xp.to_numpy(r["status"]).astype(np.int64), nit=xp.to_numpy(r["nit"]).astype(np.int64),
+                                fnorm=xp.to_numpy(r["fnorm_max"]), n_grad_evals=r["n_grad_evals"], n_hess_evals=r["n_hess_evals"],
+                                best_x=r["best_x"], best_fnorm=r["best_fnorm"], launches=r["launches"])
+    if line_search == "wolfe":
+        raise ValueError("line_search='wolfe' needs the library driver (chb_newton_krylov_dev): device tensors, or NumPy arrays "
+                         "with a build whose entry points take host pointers")
     with np.errstate(all="ignore"):
         return _newton_krylov_batched(nbs, x0, f_tol, maxiter, restart, smin, line_search, tol_norm, track_best)
 

@@ -318,6 +318,32 @@ int chb_path_stats_dev(chb_plan *plan, int64_t batch, const double *segmpos, con
  * mom, out [nvec][nsegm*geodim] (grad_ndof = 0) or [nvec][nsegm*geodim][grad_ndof] */
 int chb_compute_velocities_dev(chb_plan *plan, int64_t nvec, int64_t grad_ndof, const double *mom, double *out, void *stream);
 
+/* ---- the whole batched Newton-Krylov solve inside the library ----------------------------------------------------------------
+ * Replaces, for `batch` independent states at once, what the reference runs per state on the host: nonlin_solve_pp
+ * (choreo/scipy_plus/nonlin.py:54-171: termination test, inexact-Newton forcing terms), its line search (:194-234 on scipy's
+ * scalar_search_armijo / scalar_search_wolfe1 = MINPACK-2 dcsrch, derphi by forward difference) and scipy's
+ * KrylovJacobian(gmres, restart = inner_maxiter, maxiter 1) as wired by NBodySyst.GetKrylovJacobian (_NBodySyst.pyx:2004-2032).
+ * Every per-state decision is taken on the device; the host sequences launches and reads a few counters. */
+typedef struct chb_newton_opts {
+    double f_tol;        /* TerminationCondition(f_tol): a state is converged when norm(F) <= f_tol                          */
+    double smin;         /* smallest step of the line search (nonlin_solve_pp smin; find.py linesearch_smin)                 */
+    int32_t maxiter;     /* Newton iterations                                                                                */
+    int32_t restart;     /* GMRES restart length = KrylovJacobian inner_maxiter (1..62)                                      */
+    int32_t line_search; /* 0 none (s = smin), 1 "armijo", 2 "wolfe"                                                         */
+    int32_t tol_norm;    /* 0 max norm (nonlin_solve_pp default), 1 2-norm (np.linalg.norm, what find.py passes)            */
+} chb_newton_opts;
+int chb_newton_workspace_bytes(const chb_plan *plan, int64_t batch, int restart, size_t *bytes_out);
+/* x [batch][nparams] in: starting points, out: final iterates.  status [batch]: 1 converged, 2 iteration limit, 3 non-finite
+ * residual, 4 zero Newton step (a ValueError in the reference, nonlin.py:118-121); nit [batch] Newton iterations;
+ * fnorm_max / fnorm_2 [batch] (nullable) norms of the final residual; best_x [batch][nparams] / best_fnorm [batch] (nullable):
+ * the iterate with the smallest residual 2-norm (current_best, nonlin.py:13-39, updated after every iteration as find.py:249-257
+ * does); counters (HOST, nullable) [4]: gradient evaluations, Hessian-vector evaluations (states x calls), kernel launches,
+ * Newton iterations of the batch.
+ * All array pointers are device pointers; the call returns when the solve is finished. */
+int chb_newton_krylov_dev(chb_plan *plan, int64_t batch, double *x, const chb_newton_opts *opts, int32_t *status, int32_t *nit,
+                          double *fnorm_max, double *fnorm_2, double *best_x, double *best_fnorm, int64_t *counters,
+                          void *workspace, size_t workspace_bytes, void *stream);
+
 /* ---- memory helpers so a NumPy-only caller needs no CUDA binding ---------------------------------- */
 int chb_malloc_device(chb_plan *plan, size_t bytes, void **ptr_out);
 int chb_free_device(chb_plan *plan, void *ptr);

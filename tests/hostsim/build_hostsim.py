@@ -21,6 +21,7 @@ def build(force=False):
             os.path.join(os.path.dirname(SRC), "chb_fused5.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_big.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_post.cuh"),
+            os.path.join(os.path.dirname(SRC), "chb_newton.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_krylov.cuh"),
             os.path.join(os.path.dirname(SRC), "chb_ode.cuh"),
             os.path.join(ROOT, "include", "choreo_b200.h")]

@@ -147,3 +147,51 @@ def test_make_params_bounds_matches_reference():
         lo, hi = map(np.asarray, NBS.Make_params_bounds(0.1, 3, 50, 1e-16))
         mlo, mhi = extract_tables(NBS).make_params_bounds(nint, 0.1, 3, 50, 1e-16)
         assert np.abs(lo - mlo).max() < 1e-300 + 1e-15 * np.abs(lo).max() and np.abs(hi - mhi).max() < 1e-15 * np.abs(hi).max()
+
+
+@pytest.mark.parametrize("line_search,smin", [("armijo", 1e-2), ("wolfe", 0.1), (None, 0.1)])
+def test_library_driver_tracks_reference_iterations(line_search, smin, backend):
+    """chb_newton_krylov_dev (whole solve in the library: GMRES(20), forcing terms, Armijo / Wolfe line search on the device)
+    against the unmodified nonlin_solve_pp + KrylovJacobian iteration by iteration, from find.py-style starts: the iterates
+    agree to rounding for the first iterations (the search is chaotic far from a solution, so rounding grows slowly)."""
+    from conftest import make_nbs, need_reference
+    ref_loader = need_reference()
+    from oracle import ref_find
+    from choreo.scipy_plus.nonlin import nonlin_solve_pp
+    from choreographies2_b200 import extract_tables
+    import warnings
+    NBS = ref_loader.build_named("3C")
+    NBS.nint_fac = 16
+    nbs = make_nbs(extract_tables(NBS), int(NBS.nint), backend)
+    x0 = ref_find.find_starts(NBS, range(4))
+    # the wolfe search differentiates phi by a forward difference of step ~1e-8 (nonlin.py:211-213): its step lengths, and so the
+    # iterates, carry the rounding of phi amplified by 1e8 -- in the reference as much as here
+    tols = ((1, 1e-6), (2, 1e-6), (4, 1e-4)) if line_search == "wolfe" else ((1, 1e-10), (2, 1e-9), (4, 1e-6))
+    for mit, tol in tols:
+        if backend is None:
+            import torch
+            x = torch.from_numpy(x0).cuda()
+        else:
+            x = x0.copy()
+        r = nbs.newton_krylov(x, 1e-13, mit, 20, smin, line_search, "l2", False)
+        xb = x.cpu().numpy() if backend is None else x
+        nit = r["nit"].cpu().numpy() if backend is None else r["nit"]
+        for i in range(4):
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                jac = NBS.GetKrylovJacobian(True, {"method": "gmres"})
+                xr, info = nonlin_solve_pp(NBS.params_to_action_grad, x0[i].copy(), jacobian=jac, f_tol=1e-13, maxiter=mit,
+                                           line_search=line_search, full_output=True, raise_exception=False, smin=smin,
+                                           tol_norm=np.linalg.norm)
+            assert int(nit[i]) == int(info["nit"]) == mit
+            assert np.abs(xr - xb[i]).max() < tol * max(1.0, np.abs(xr).max()), (line_search, mit, i)
+
+
+def test_line_search_argument_is_validated(sim):
+    nbs, xs, _ = _figure_eight(sim)
+    with pytest.raises(ValueError, match="line_search"):
+        newton_krylov_batched(nbs, xs[None, :], line_search="wolf")
+    with pytest.raises(ValueError, match="line_search"):
+        nbs.newton_krylov(xs[None, :].copy(), 1e-9, 5, line_search="strong")
+    res = newton_krylov_batched(nbs, xs[None, :] + 1e-3, f_tol=1e-11, maxiter=30, line_search="wolfe", smin=0.1, tol_norm="l2")
+    assert res.status[0] == 1

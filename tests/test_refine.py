@@ -159,3 +159,25 @@ def test_group_duplicates(sim):
     H = nbs.segmpos_to_hash(batch)
     assert refine.group_duplicates(nbs, H).tolist() == [0, 1, 0, 0, 1]
     assert refine.group_duplicates(nbs, H, detect_multiples=False).tolist() == [0, 1, 2, 0, 4]
+
+
+def test_find_full_schedule_identical_orbits(backend):
+    """The reference's own 3C search settings (tests/NewSym_data/3C/choreo_config.json: wolfe, smin 0.1, six optimiser levels
+    1e-1 .. 1e-11 in the 2-norm, refinement x2) on find.py seeds: for every seed the reference saves an orbit, the batched
+    driver stops with the same outcome at the same refinement level on the same orbit (hash and action; the orbits are equal
+    up to the rotation / phase the symmetric problem leaves free, which the hash is blind to).  Seed 3 is the figure-eight."""
+    from conftest import need_reference
+    need_reference()
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import find_compare
+    if backend is None:   # the CUDA library: full size (nint_init 600 -> nint 3600 .. ), 32 seeds
+        rows, summ = find_compare.compare(32, 600, "cuda", 4, verbose=False)
+    else:                 # emulation: same settings at a coarse discretisation
+        rows, summ = find_compare.compare(12, 16, "hostsim", 2, verbose=False)
+    assert summ["reference_saved"] >= len(rows) // 2
+    for row in rows:
+        if row["ref"][0] in (refine.FOUND, refine.APPROX):
+            assert row["same"], row
+            assert row["hash_same"] and row["hash_rel"] < 1e-9, row
+            assert abs(row["action_ref"] - row["action_b200"]) < 1e-11 * abs(row["action_ref"]), row
+    assert abs(rows[3]["action_b200"] - 10.4830237879556) < 1e-9
