@@ -56,6 +56,9 @@ def parse_args():
     ap.add_argument("--stages", action="store_true", help="also time the staged operators separately")
     ap.add_argument("--no-newton", action="store_true", help="skip the Newton orbit solves/hour leg")
     ap.add_argument("--newton-batch", type=int, default=8192, help="random starts per GPU in the solves/hour leg")
+    ap.add_argument("--newton-reps", type=int, default=5, help="timed repetitions of the solves/hour leg (median reported)")
+    ap.add_argument("--newton-ref-seeds", type=int, default=0, help="seeds of the CPU arm of the solves/hour leg (0 = auto)")
+    ap.add_argument("--no-configs", dest="configs", action="store_false", help="skip the extra BASELINE configurations")
     return ap.parse_args()
 
 
@@ -165,9 +168,18 @@ def cpu_baseline(args, nparams):
     best = float("inf")
     for _ in range(3):
         t = time.perf_counter(); cpu_eval_loop(obj, x); best = min(best, time.perf_counter() - t)
+    # what find.py:267 actually calls per Newton / line-search evaluation is the gradient alone: reported beside U1
+    bestg = float("inf")
+    for _ in range(3):
+        t = time.perf_counter()
+        for i in range(n):
+            obj.params_to_action_grad(x[i])
+        bestg = min(bestg, time.perf_counter() - t)
     if ctx is not None:
         ctx.restore_original_limits() if hasattr(ctx, "restore_original_limits") else None
-    return {"value": n / best, "unit": UNIT, "cores": 1, "kind": kind,
+    return {"value": n / best, "unit": UNIT, "cores": 1, "kind": kind, "grad_only_per_s": n / bestg,
+            "note": "U1 on the CPU = params_to_action + params_to_action_grad (two forward transforms; the action goes through the "
+                    "function-pointer law, _NBodySyst.pyx:6425) against ONE fused pass on the GPU; grad_only_per_s is the gradient alone",
             "sample": f"{n} states of the same workload ({args.system}, nint {args.nint}), params_to_action + "
                       f"params_to_action_grad per state, best of 3, 1 thread, FFT backend scipy"}
 
@@ -232,8 +244,141 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if not args.no_newton:  # second half of the metric on the same host cores: the reference's search loop, P processes
+        try:
+            line["newton"] = search_cpu_arm(3072, P, max(1, (args.newton_ref_seeds or 4 * P) // P))
+        except Exception as exc:
+            line["newton"] = {"error": f"{type(exc).__name__}: {exc}"}
     print(json.dumps(line))
     return 0
+
+
+
+FP64_PEAK_TFLOPS = 37.0  # measured FMA peak of this pool's B200 (tools/fp64_peak.cu, profiles/r01_fp64_pcie_peaks.json)
+
+
+def config_entry(label, system, nint, batch, dev, hbm_peak):
+    """U1 rate of one of the other BASELINE configurations, device-resident, with both rooflines of SURVEY.md 8(d)."""
+    import torch
+    from choreographies2_b200 import NBodySystB200, PlanTables
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", f"{system}.npz"))
+    nbs = NBodySystB200(T, nint, device=dev.index)
+    x = torch.rand((batch, nbs.nparams), dtype=torch.float64, device=dev, generator=torch.Generator(device=dev).manual_seed(1234))
+    for _ in range(3):
+        nbs.params_to_action_and_grad(x)
+    l0 = nbs.kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    steps = 5
+    e0.record()
+    for _ in range(steps):
+        nbs.params_to_action_and_grad(x)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    rate = batch / (ms * 1e-3)
+    # algorithmic work per U1 (SURVEY.md 8(d)): bytes 8 (2 nparams + 1); flops = two transforms + pair loop
+    G, S, nbin = T.geodim, T.nsegm, T.nbin
+    lvl = T.level(nint)
+    nseq = sum((G if int(T.shortcut[il]) == 1 else int(T.nnz[il] * T.nppl[il])) * 2.5 * (2 * int(lvl.npr[il])) *
+               np.log2(max(2.0, 2.0 * int(lvl.npr[il]))) for il in range(T.nloop))
+    flops = 2.0 * nseq + nbin * lvl.segm_store * (8 * G + 10) + 4.0 * nbs.nparams
+    alg_bytes = 8 * (2 * nbs.nparams + 1)
+    staged_bytes = alg_bytes + 32 * S * lvl.segm_store * G
+    fused = bool(nbs.fused)
+    return {"workload": f"{label}, batch {batch}, U1", "value": rate, "unit": UNIT, "ms_per_step": ms, "fused_version": int(nbs.fused_version),
+            "staged_kernels": list(nbs.staged_kernels), "gpu_launches_per_step": int((nbs.kernel_launches - l0) // steps),
+            "roofline_hbm": {"alg_bytes_per_unit": alg_bytes, "achieved_gbs": alg_bytes * rate / 1e9, "frac": alg_bytes * rate / 1e9 / hbm_peak,
+                             "staged_bytes_per_unit": None if fused else staged_bytes,
+                             "frac_on_staged_bytes": None if fused else staged_bytes * rate / 1e9 / hbm_peak},
+            "roofline_fp64": {"alg_flops_per_unit": flops, "achieved_tflops": flops * rate / 1e12, "peak_tflops": FP64_PEAK_TFLOPS,
+                              "frac": flops * rate / 1e12 / FP64_PEAK_TFLOPS}}
+
+
+def _search_cpu_worker(task):
+    """CPU arm of the solves/hour leg: the reference's search loop (oracle/ref_find.reference_find = unmodified nonlin_solve_pp,
+    KrylovJacobian, params_resize ...) on a list of seeds, one process, BLAS threads pinned to 1."""
+    seeds, nint0 = task
+    _limit_threads()
+    from oracle import ref_loader, ref_find
+    ref_loader.import_reference()
+    NBS = ref_loader.build_named("3C")
+    fac0 = nint0 // (2 * int(NBS.nint_min))
+    NBS.nint_fac = fac0
+    x0 = ref_find.find_starts(NBS, seeds)
+    cfg = {k: v for k, v in ref_find.CONFIG_3C.items() if k not in ("nint_fac_init", "coeff_ampl_o", "k_infl", "k_max", "coeff_ampl_min")}
+    t = time.perf_counter()
+    outs = [ref_find.reference_find(NBS, x0[i], fac0, **cfg)[0] for i in range(len(seeds))]
+    return time.perf_counter() - t, outs
+
+
+def search_cpu_arm(nint0, nproc, seeds_per_proc):
+    """solves/hour of the reference's search loop on `nproc` host processes (the reference's own scaling model, find.py:836-850)."""
+    import multiprocessing as mp
+    from oracle import ref_loader
+    if not ref_loader.reference_available():
+        return None
+    tasks = [(list(range(p * seeds_per_proc, (p + 1) * seeds_per_proc)), nint0) for p in range(nproc)]
+    t0 = time.perf_counter()
+    if nproc == 1:
+        res = [_search_cpu_worker(tasks[0])]
+    else:
+        with mp.get_context("spawn").Pool(nproc) as pool:
+            res = pool.map(_search_cpu_worker, tasks, chunksize=1)
+    wall = time.perf_counter() - t0
+    busy = max(r[0] for r in res)
+    outs = [o for r in res for o in r[1]]
+    n = len(outs)
+    return {"solves_per_hour": n / busy * 3600.0, "seconds_busiest_process": busy, "seconds_wall_incl_startup": wall, "seeds": n, "processes": nproc,
+            "saved": int(sum(1 for o in outs if o in (1, 2))), "kind": "reference",
+            "sample": f"{n} find.py seeds through the reference's search loop (oracle/ref_find.reference_find: unmodified nonlin_solve_pp + "
+                      f"KrylovJacobian(gmres) + params_resize, settings of tests/NewSym_data/3C/choreo_config.json), {nproc} process(es), 1 BLAS thread each"}
+
+
+def newton_leg(args, rank, world, dev, barrier, max_over_ranks):
+    import torch
+    from choreographies2_b200 import NBodySystB200, PlanTables
+    from choreographies2_b200 import refine
+    Tn = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nint0, Bn = 3072, int(args.newton_batch)
+    plans = {}
+
+    def make(nint):
+        if nint not in plans:
+            plans[nint] = NBodySystB200(Tn, nint, device=dev.index)
+        return plans[nint]
+
+    starts = refine.find_starts(Tn, nint0, range(rank * Bn, (rank + 1) * Bn), **refine.RANDOM_CONFIG_3C)
+    x0n = torch.from_numpy(starts).to(dev)
+    kw = dict(refine.SEARCH_CONFIG_3C)
+    refine.find_batched(make, x0n[:min(Bn, 256)].clone(), nint0, **kw)  # warm-up: plans of the levels, workspaces, allocator
+    times, res = [], None
+    l0 = sum(p.kernel_launches for p in plans.values())
+    for _ in range(max(1, args.newton_reps)):
+        barrier()
+        t0 = time.perf_counter()
+        res = refine.find_batched(make, x0n, nint0, **kw)
+        torch.cuda.synchronize()
+        times.append(max_over_ranks(time.perf_counter() - t0))
+    launches = (sum(p.kernel_launches for p in plans.values()) - l0) // max(1, args.newton_reps)
+    ts = sorted(times)
+    med = ts[len(ts) // 2]
+    saved = int(((res.outcome == refine.FOUND) | (res.outcome == refine.APPROX)).sum())
+    out = {"solves_per_hour": world * Bn / med * 3600.0, "saved_orbits_per_hour": world * saved / med * 3600.0,
+           "seconds_median": med, "seconds_min": ts[0], "seconds_max": ts[-1], "repetitions": len(ts), "batch_per_gpu": Bn,
+           "system": "3C", "nint0": nint0, "nparams0": int(make(nint0).nparams),
+           "settings": "find.py loop with the reference's 3C configuration: GMRES(20), wolfe line search smin 0.1, optimiser levels "
+                       "gradtol 1e-1 .. 1e-11 (2-norm) with maxiter 100/1000/1000/1000/500/500, refinement x2 up to 4 times, "
+                       "Newt_err_norm_max 1e-11 / 1e-8; starts x_avg + x_ptp U[0,1) from Make_params_bounds(0.1, 3, 50, 1e-16)",
+           "rank0": {"found": int((res.outcome == refine.FOUND).sum()), "approximate": int((res.outcome == refine.APPROX).sum()),
+                     "not_converged": int((res.outcome == refine.NOT_CONVERGED).sum()), "collision": int((res.outcome == refine.COLLISION).sum()),
+                     "escaped": int((res.outcome == refine.ESCAPED).sum()), "refined_at_least_once": int((res.level > 0).sum()),
+                     "U1_evals": int(res.n_grad_evals), "U2_evals": int(res.n_hess_evals), "gpu_launches": int(launches),
+                     "newton_iterations_mean": float(res.newton_iterations.mean())},
+           "note": "a solve = one run of the search loop from one random start to termination (saved, abandoned, escaped ...)"}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        n = args.newton_ref_seeds or 48
+        out["cpu_baseline"] = search_cpu_arm(nint0, 1, n)
+    return out
 
 
 # ------------------------------------------------------------------------------------------------ our arm
@@ -373,40 +518,26 @@ def run_b200(args):
         assert abs(float(a_h.sum()) - checksum) <= 1e-9 * abs(checksum)
 
     # ---- second half of the metric: Newton orbit solves/hour ----------------------------------------------------------
-    # every rank solves its own shard of find.py-style random starts (seeded by global index) of the 3C system at nint 3072
-    # with the batched Newton-Krylov driver (GMRES(20) + Armijo, the reference's settings); no collective on the path
+    # every rank runs the search loop of find.py (refine.find_batched: the reference's 3C settings -- wolfe line search, smin 0.1,
+    # six optimiser levels 1e-1 .. 1e-11 in the 2-norm, refinement x2 up to 4 times) on its own shard of find.py-style random
+    # starts (seeded by global index) of the 3C system from nint 3072; no collective on the path.  Timed `--newton-reps` times.
     newton = None
     if not args.no_newton:
         try:
-            from choreographies2_b200.newton import newton_krylov_batched
-            Tn = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
-            n_nint, Bn = 3072, int(args.newton_batch)
-            nbs_n = NBodySystB200(Tn, n_nint, device=dev.index)
-            x_min, x_max = Tn.make_params_bounds(n_nint, 0.1, 3, 50, 1e-16)
-            starts = np.empty((Bn, nbs_n.nparams))
-            for i in range(Bn):  # find.py:105-108,158: np.random.seed(seed); x = x_min + x_ptp * U[0, 1)
-                np.random.seed(rank * Bn + i)
-                starts[i] = x_min + (x_max - x_min) * np.random.random(nbs_n.nparams)
-            x0n = torch.from_numpy(starts).to(dev)
-            newton_krylov_batched(nbs_n, x0n, f_tol=1e-9, maxiter=2)  # warm-up: plan, workspaces, caching allocator
-            barrier()
-            l0 = nbs_n.kernel_launches
-            t0 = time.perf_counter()
-            res = newton_krylov_batched(nbs_n, x0n, f_tol=1e-9, maxiter=60)
-            torch.cuda.synchronize()
-            dtn = max_over_ranks(time.perf_counter() - t0)
-            newton = {"solves_per_hour": world * Bn / dtn * 3600.0, "seconds": dtn, "batch_per_gpu": Bn, "system": "3C",
-                      "nint": n_nint, "nparams": int(nbs_n.nparams),
-                      "settings": "f_tol 1e-9 (max norm), <= 60 Newton iterations, GMRES(20), Armijo smin 1e-2, "
-                                  "starts x_min + (x_max - x_min) U[0,1) from Make_params_bounds(0.1, 3, 50, 1e-16)",
-                      "rank0": {"converged": int((res.status == 1).sum()), "iteration_limit": int((res.status == 2).sum()),
-                                "non_finite": int((res.status == 3).sum()), "U1_evals": int(res.n_grad_evals),
-                                "U2_evals": int(res.n_hess_evals), "gpu_launches": int(nbs_n.kernel_launches - l0)},
-                      "note": "a solve = one run from one random start to termination; reference solver on one host core: "
-                              "profiles/r01_solves_*.json (about 1.0e5 solves/hour per process)"}
-            del nbs_n, x0n, res
+            newton = newton_leg(args, rank, world, dev, barrier, max_over_ranks)
         except Exception as exc:  # the first half of the metric stands on its own
             newton = {"error": f"{type(exc).__name__}: {exc}"}
+
+    # ---- the other BASELINE configurations as extra entries (parity cases with a measured rate; not the headline) -----------
+    configs = None
+    if args.configs and world == 1:
+        configs = []
+        for label, system, nint, batch in (("C1 3C nint 3072", "3C", 3072, 4096), ("C3 5Dq nint 10240", "5Dq", 10240, 1024),
+                                           ("C4 64C nint 16384", "64C", 16384, 256)):
+            try:
+                configs.append(config_entry(label, system, nint, batch, dev, peak))
+            except Exception as exc:
+                configs.append({"workload": label, "error": f"{type(exc).__name__}: {exc}"})
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -427,6 +558,8 @@ def run_b200(args):
             line["stages"] = stages
         if newton is not None:
             line["newton"] = newton
+        if configs is not None:
+            line["configs"] = configs
         print(json.dumps(line))
     return 0
 

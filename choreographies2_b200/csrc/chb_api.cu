@@ -2170,8 +2170,9 @@ static int launch_fused(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A0, c
     p->fsys.pf_stride = (int)std::min<int64_t>(nb, (int64_t)p->fused_resident);
     (void)nb_states;
     {
-        const char *dbg = getenv("CHB_FUSED_DBG");  // profiling only: results are wrong when phases are skipped
-        p->fsys.dbg = dbg ? atoi(dbg) : 0;
+        // profiling only (phases are skipped, results are wrong): read ONCE per process, never per launch
+        static const int dbg_once = [] { const char *e = getenv("CHB_FUSED_DBG"); return e ? atoi(e) : 0; }();
+        p->fsys.dbg = dbg_once;
     }
     // version 4: U1 (action + gradient) and U2 (Hessian-vector on cached segment positions) with the kinetic rows = the
     // transformed rows, 16-byte aligned vectors
@@ -2179,8 +2180,8 @@ static int launch_fused(chb_plan *p, int pmode, int64_t nb, const ChfArgs &A0, c
         (pmode == 1 || A.seg_in) && (((uintptr_t)A.vec_in | (uintptr_t)A.vec_out | (uintptr_t)A.seg_in | (uintptr_t)A.seg_out) & 15) == 0) {
         p->fsys.ver = 4;
         {
-            const char *sg = getenv("CHB_FUSED_STAGGER_NS");
-            p->fsys.stagger_ns = sg ? atoi(sg) : 0;  // measured: no gain (profiles/README.md), kept as a knob
+            static const int stagger_once = [] { const char *e = getenv("CHB_FUSED_STAGGER_NS"); return e ? atoi(e) : 0; }();
+            p->fsys.stagger_ns = stagger_once;  // measured: no gain (profiles/README.md), kept as a knob
         }
         if (p->fsys.nseg == 3) {
             if (pmode == 1) CHB_LAUNCH(p, (k_fused4<3, 1>), nb, p->fused_threads, p->fused_smem, st, p->fsys, A);
@@ -2819,6 +2820,12 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
     const int64_t l0 = p->launches;
     int64_t n_u1 = 0, n_u2 = 0, n_it = 0;
     int hc[4];
+    if (!use_fused(p)) {
+        // the staged kernels compute every state of the batch, also the ones whose solve has stopped: their Krylov vectors must
+        // at least be finite numbers
+        CHB_TRY(nk_zero(A.V, sizeof(double) * (size_t)(m + 1) * (size_t)B * (size_t)n, st));
+        CHB_TRY(nk_zero(A.w, sizeof(double) * (size_t)B * (size_t)n, st));
+    }
     // F(x0), norms, per-state scalars
     CHB_TRY(nk_grad(p, B, x, A.F, nullptr, A, st));
     n_u1 += B;

@@ -94,9 +94,14 @@ CHB_D void ch4_load_pass(Grp &grp, const ChfLoop &L, cd *buf, double *red, bool 
             s.xm = pr == 0 ? 0 : 1;
             s.base = 2 * klo;
             double p[H][4];
+            // a row is two 16-byte halves and the lanes of a pair sit 32 bytes apart (klo ascending / M - klo descending): the
+            // even lane takes the low half first, the odd lane the high half first, so the two lanes of every pair hit different
+            // bank groups in both requests (no 2-way conflict); a select puts the halves back in order
+            const int hsw = tid & 1;
 #pragma unroll
             for (int q = 0; q < H; ++q) {
-                const cd lo = buf[512 * q + 2 * klo], hi = buf[512 * q + 2 * klo + 1];
+                const cd u = buf[512 * q + 2 * klo + hsw], v = buf[512 * q + 2 * klo + (hsw ^ 1)];
+                const cd lo = hsw ? v : u, hi = hsw ? u : v;
                 p[q][0] = lo.x; p[q][1] = lo.y; p[q][2] = hi.x; p[q][3] = hi.y;
             }
             double c0 = 0.0, c2 = 0.0;
@@ -136,8 +141,12 @@ CHB_D void ch4_load_pass(Grp &grp, const ChfLoop &L, cd *buf, double *red, bool 
             }
             ChfDft<R, +1>::run(s.a);
             cd *p = buf + s.base;
+            const int hsw = tid & 1;  // same half-swap as the row reads: conflict-free stores
 #pragma unroll
-            for (int t = 0; t < R; ++t) p[512 * (t >> 1) + (t & 1)] = s.a[t];
+            for (int t = 0; t < R; t += 2) {
+                p[512 * (t >> 1) + hsw] = hsw ? s.a[t + 1] : s.a[t];
+                p[512 * (t >> 1) + (hsw ^ 1)] = hsw ? s.a[t] : s.a[t + 1];
+            }
         });
 }
 
@@ -157,8 +166,13 @@ CHB_D void ch4_store_pass(Grp &grp, const ChfLoop &L, cd *buf, double *red, bool
             s.xm = pr == 0 ? 0 : 1;
             s.base = 2 * klo;
             const cd *p = buf + s.base;
+            const int hsw = tid & 1;  // half-swap between the lanes of a pair: conflict-free reads (see ch4_load_pass)
 #pragma unroll
-            for (int t = 0; t < R; ++t) s.a[t] = p[512 * (t >> 1) + (t & 1)];
+            for (int t = 0; t < R; t += 2) {
+                const cd u = p[512 * (t >> 1) + hsw], v = p[512 * (t >> 1) + (hsw ^ 1)];
+                s.a[t] = hsw ? v : u;
+                s.a[t + 1] = hsw ? u : v;
+            }
             ChfDft<R, -1>::run(s.a);  // a[q] = Y[klo + q M]
             const bool dc = klo == 0;
 #pragma unroll
@@ -199,8 +213,9 @@ CHB_D void ch4_store_pass(Grp &grp, const ChfLoop &L, cd *buf, double *red, bool
                             if (want_kin) kin += (p[u][0] * p[u][0] + p[u][1] * p[u][1]) + (p[u][2] * p[u][2] + p[u][3] * p[u][3]);
                             v[0] += p[u][0]; v[1] += p[u][1]; v[2] += p[u][2]; v[3] += p[u][3];
                         }
-                        rows[512 * t] = mk(v[0], v[1]);
-                        rows[512 * t + 1] = mk(v[2], v[3]);
+                        const int hsw = tid & 1;
+                        rows[512 * t + hsw] = hsw ? mk(v[2], v[3]) : mk(v[0], v[1]);
+                        rows[512 * t + (hsw ^ 1)] = hsw ? mk(v[0], v[1]) : mk(v[2], v[3]);
                     }
                 }
             }

@@ -21,6 +21,28 @@ import numpy as np
 
 from .newton import _XP, newton_krylov_batched
 
+# Solver settings of the reference's 3C search configuration (tests/NewSym_data/3C/choreo_config.json, sections Solver_Optim /
+# Solver_Loop / Solver_Discr / Phys_Random as choreo.find.ChoreoLoadFromDict maps them, find.py:700-750): the keyword arguments of
+# find_batched for BASELINE config 1 and the sweep of config 5
+SEARCH_CONFIG_3C = dict(
+    gradtol_list=[1e-1, 1e-3, 1e-5, 1e-7, 1e-9, 1e-11], maxiter_list=[100, 1000, 1000, 1000, 500, 500], krylov_method="gmres",
+    line_search="wolfe", linesearch_smin=0.1, Newt_err_norm_max=1e-11, Newt_err_norm_max_save=1e-8, n_reconverge_it_max=4,
+    mul_coarse_to_fine=3.0)
+RANDOM_CONFIG_3C = dict(coeff_ampl_o=0.1, k_infl=3, k_max=50, coeff_ampl_min=1e-16)  # Make_params_bounds arguments (Phys_Random)
+
+
+def find_starts(tables, nint: int, seeds, coeff_ampl_o=0.1, k_infl=3, k_max=50, coeff_ampl_min=1e-16) -> np.ndarray:
+    """Random starts exactly as find.py:105-108,158 draws them: ``np.random.seed(seed); x = x_avg + x_ptp * U[0, 1)`` with
+    ``x_avg = (x_min + x_min) / 2`` (sic) and ``x_ptp = x_max - x_min`` from ``Make_params_bounds`` (one seed per start)."""
+    x_min, x_max = tables.make_params_bounds(nint, coeff_ampl_o, k_infl, k_max, coeff_ampl_min)
+    x_avg, x_ptp = (x_min + x_min) / 2, x_max - x_min
+    out = np.empty((len(seeds), x_min.shape[0]))
+    for r, s in enumerate(seeds):
+        np.random.seed(int(s))
+        out[r] = x_avg + x_ptp * np.random.random(x_min.shape[0])
+    return out
+
+
 # per-state outcome codes
 FOUND, APPROX, NOT_CONVERGED, COLLISION, TOO_BIG_ON_ENTRY, ESCAPED = 1, 2, 3, 4, 5, 6
 OUTCOME = {FOUND: "found solution", APPROX: "found approximate solution",
@@ -171,19 +193,77 @@ def find_batched(make_nbs: Callable[[int], Any], x0, nint0: int, *, gradtol: flo
                         newton_iterations=nit_tot, n_grad_evals=n_grad, n_hess_evals=n_hess, optim_level=optim_level)
 
 
+def hash_test_values(nbs, Hash_a, Hash_b, detect_multiples: bool = True) -> np.ndarray:
+    """The test values of ``TestHashSame`` (_NBodySyst.pyx:2036-2067), vectorised: ``Hash_a`` ``[nexp]`` against every row of
+    ``Hash_b`` ``[M, nexp]``; two orbits are "the same" when the infinity norm of a row is below ``rtol``."""
+    Ha, Hb = np.asarray(Hash_a, dtype=np.float64), np.atleast_2d(np.asarray(Hash_b, dtype=np.float64))
+    exps = np.asarray(nbs.Hash_exp, dtype=np.float64)
+    with np.errstate(all="ignore"):
+        if detect_multiples and nbs.LawIsHomo:
+            pw = (nbs.Homo_exp - 1.0) / (2.0 * exps)
+            ref = (Ha[0] / Hb[:, 0]) ** pw[0]
+            test = (Ha[None, 1:] / Hb[:, 1:]) ** pw[None, 1:] - ref[:, None]
+        else:
+            test = (Hb - Ha[None, :]) / (Hb + Ha[None, :])
+    return test
+
+
 def group_duplicates(nbs, hashes, rtol: float = 1e-5, detect_multiples: bool = True) -> np.ndarray:
     """Duplicate filter of the search loop over a batch (``Check_Duplicates``, find.py:905-935, minus the store folder): orbit
     ``b`` joins the first earlier orbit whose hash passes ``TestHashSame`` (_NBodySyst.pyx:2036-2067), else it starts a new
     group.  ``hashes``: ``[B, nexp]`` from ``nbs.segmpos_to_hash`` (NumPy array or device tensor).  Returns the group
-    representative (index of the first member) of every orbit, ``[B]``."""
+    representative (index of the first member) of every orbit, ``[B]``.  One vectorised comparison per group."""
     H = hashes.detach().cpu().numpy() if type(hashes).__module__.startswith("torch") else np.asarray(hashes)
-    rep = np.arange(H.shape[0])
-    firsts: List[int] = []
-    for b in range(H.shape[0]):
-        for f in firsts:
-            if nbs.TestHashSame(H[f], H[b], rtol, detect_multiples):
-                rep[b] = f
-                break
-        else:
-            firsts.append(b)
+    B = H.shape[0]
+    rep = np.full(B, -1, dtype=np.int64)
+    for b in range(B):
+        if rep[b] >= 0:
+            continue
+        rep[b] = b
+        rest = np.nonzero(rep[b + 1:] < 0)[0] + b + 1
+        if rest.size:
+            t = hash_test_values(nbs, H[b], H[rest], detect_multiples)
+            same = np.abs(np.nan_to_num(t, nan=np.inf)).max(axis=1) < rtol
+            rep[rest[same]] = b
     return rep
+
+
+class DuplicateStore:
+    """The orbits found so far (hash + action), the role of the store folder in ``Check_Duplicates`` (find.py:865-935): ``add``
+    returns, per candidate, the index of the stored orbit it duplicates (or -1 and stores it).  ``load_folder`` reads the
+    ``Hash`` / ``Action`` fields of the reference's solution descriptors (``*.json`` written by ``Write_Descriptor``)."""
+
+    def __init__(self, nbs, rtol: float = 1e-5, detect_multiples: bool = True):
+        self.nbs, self.rtol, self.detect_multiples = nbs, float(rtol), bool(detect_multiples)
+        self.hashes: List[np.ndarray] = []
+        self.actions: List[float] = []
+
+    def load_folder(self, folder: str) -> int:
+        import json
+        import os
+        n = 0
+        for fn in sorted(os.listdir(folder)):
+            if fn.endswith(".json"):
+                with open(os.path.join(folder, fn)) as f:
+                    info = json.load(f)
+                if info.get("Hash") is not None:
+                    self.hashes.append(np.asarray(info["Hash"], dtype=np.float64))
+                    self.actions.append(float(info.get("Action", np.nan)))
+                    n += 1
+        return n
+
+    def add(self, hashes, actions=None) -> np.ndarray:
+        H = hashes.detach().cpu().numpy() if type(hashes).__module__.startswith("torch") else np.asarray(hashes, dtype=np.float64)
+        H = np.atleast_2d(H)
+        out = np.full(H.shape[0], -1, dtype=np.int64)
+        for b in range(H.shape[0]):
+            if self.hashes:
+                t = hash_test_values(self.nbs, H[b], np.stack(self.hashes), self.detect_multiples)
+                # TestHashSame(Hash_a = candidate, Hash_b = stored)
+                same = np.nonzero(np.abs(np.nan_to_num(t, nan=np.inf)).max(axis=1) < self.rtol)[0]
+                if same.size:
+                    out[b] = int(same[0])
+                    continue
+            self.hashes.append(H[b].copy())
+            self.actions.append(float(actions[b]) if actions is not None else float("nan"))
+        return out

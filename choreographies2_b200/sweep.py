@@ -37,6 +37,39 @@ def chunk_schedule(n: int, world: int, chunk: int) -> Sequence[Tuple[int, int, i
     return out
 
 
+class ChunkQueue:
+    """Dynamic work queue of seed chunks shared by the ranks (solves have variable iteration counts, so a rank
+    that finishes early takes the next chunk instead of idling behind a static split).  The queue is ONE atomic counter in a
+    ``torch.distributed.TCPStore`` on the host network (``add`` is atomic): no device collective, nothing on the data path.
+    With ``world == 1`` (or no store) it degenerates to a local counter."""
+
+    def __init__(self, n: int, chunk: int, rank: int = 0, world: int = 1, host: str = "127.0.0.1", port: Optional[int] = None,
+                 key: str = "chb_next_chunk"):
+        if chunk < 1 or n < 0:
+            raise ValueError("ChunkQueue: need n >= 0 and chunk >= 1")
+        self.n, self.chunk, self.key = int(n), int(chunk), key
+        self.nchunks = (self.n + self.chunk - 1) // self.chunk
+        self._local = 0
+        self.store = None
+        if world > 1:
+            from torch.distributed import TCPStore
+            if port is None:
+                port = int(os.environ.get("MASTER_PORT", "29500")) + 23
+            self.store = TCPStore(host, int(port), world, is_master=(rank == 0), wait_for_workers=True)
+
+    def next(self) -> Optional[Tuple[int, int]]:
+        """Claim the next unclaimed chunk: ``(lo, hi)`` seed bounds, or None when the queue is empty."""
+        if self.store is None:
+            c = self._local
+            self._local += 1
+        else:
+            c = int(self.store.add(self.key, 1)) - 1
+        if c >= self.nchunks:
+            return None
+        lo = c * self.chunk
+        return lo, min(self.n, lo + self.chunk)
+
+
 def env_rank_world() -> Tuple[int, int, int]:
     """(rank, world, local_rank) from the torchrun environment (1 process when absent)."""
     return (int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")),

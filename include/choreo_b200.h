@@ -18,7 +18,9 @@
  *     (chb_workspace_bytes) so one plan can serve several streams;
  *   - "_host" operators take HOST pointers, stage through plan-owned pinned/device buffers and
  *     return when the result is in the host buffer (one call at a time per plan);
- *   - a plan is immutable between chb_plan_set_nint calls; tables are copied at creation.
+ *   - a plan is immutable between chb_plan_set_nint calls; tables are copied at creation;
+ *   - one plan serves ONE stream / host thread at a time: the launch bookkeeping and the caller's workspace are not duplicated per
+ *     stream (several streams: one plan and one workspace each -- plans are a few hundred KB of tables).
  */
 #ifndef CHOREO_B200_H
 #define CHOREO_B200_H

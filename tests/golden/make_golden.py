@@ -72,6 +72,16 @@ def export_systems():
     return systems
 
 
+def export_configs(names=("3C",)):
+    """The reference's own search configurations (tests/NewSym_data/<name>/choreo_config.json) that the drop-in test feeds to
+    ``choreo.find.ChoreoLoadFromDict`` / ``Find_Choreo``, copied verbatim as fixtures ``<name>_choreo_config.json``."""
+    for name in names:
+        with open(os.path.join(REF, "tests", "NewSym_data", name, "choreo_config.json")) as f:
+            d = json.load(f)
+        with open(os.path.join(HERE, f"{name}_choreo_config.json"), "w") as f:
+            json.dump(d, f, indent=None, separators=(",", ":"), sort_keys=True)
+
+
 def golden_for(NBS, rng, out, prefix, facs=NINT_FACS):
     T = extract_tables(NBS)
     for k, v in T.to_dict().items():
@@ -101,6 +111,7 @@ def golden_for(NBS, rng, out, prefix, facs=NINT_FACS):
 def main():
     systems = export_systems()
     print(f"systems.json: {len(systems)} systems")
+    export_configs()
     for name, desc in systems.items():
         if name == "64C":
             continue  # setup takes seconds and the vectors are large; covered live + by a dedicated fixture below

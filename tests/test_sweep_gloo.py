@@ -101,3 +101,71 @@ def test_sharded_eval_gloo_matches_single_process(world, n):
     assert np.array_equal(out["action"], act)
     assert np.array_equal(out["grad0"], grad[:, 0])
     assert np.array_equal(out["gradnorm"], np.linalg.norm(grad, axis=1))
+
+
+def _queue_worker(rank, world, port, n, chunk, delay, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import time
+    import torch.distributed as dist
+    from choreographies2_b200 import NBodySystB200, PlanTables, sweep as sw, refine
+    from hostsim import build_hostsim
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+        lib = build_hostsim.load()
+        nint = 3 * 2 * 16
+        queue = sw.ChunkQueue(n, chunk, rank, world)
+        mine, outcome = [], []
+        while True:
+            c = queue.next()
+            if c is None:
+                break
+            time.sleep(delay * rank)  # rank 1 is the slow one: the fast rank must end up with more chunks
+            lo, hi = c
+            x0 = refine.find_starts(T, nint, range(lo, hi))
+            res = refine.find_batched(lambda ni: NBodySystB200(T, ni, _lib_handle=lib), x0, nint, gradtol=1e-9, maxiter=30,
+                                      n_reconverge_it_max=0, Newt_err_norm_max=1e-7, Newt_err_norm_max_save=1e-5)
+            mine.append((lo, hi))
+            outcome.append(res.outcome)
+        idx = np.concatenate([np.arange(lo, hi) for lo, hi in mine]) if mine else np.zeros(0, dtype=np.int64)
+        rec = {"outcome": np.concatenate(outcome) if outcome else np.zeros(0, dtype=np.int64)}
+        q.put((rank, mine, sw.gather_records(rec, idx)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_dynamic_chunk_queue_gloo():
+    """sweep.ChunkQueue over two gloo ranks: every chunk is claimed exactly once, the slower rank takes fewer chunks, and the
+    gathered per-seed outcomes equal a single-process run (the result does not depend on who solved which chunk)."""
+    import multiprocessing as mp
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from choreographies2_b200 import NBodySystB200, PlanTables, refine
+    from hostsim import build_hostsim
+    n, chunk, world = 14, 2, 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_queue_worker, args=(r, world, port, n, chunk, 0.4, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = {r: (mine, merged) for r, mine, merged in (q.get(timeout=300) for _ in range(world))}
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    claimed = sorted(got[0][0] + got[1][0])
+    assert claimed == [(lo, min(n, lo + chunk)) for lo in range(0, n, chunk)]
+    assert len(got[0][0]) > len(got[1][0]) >= 1
+    merged = got[0][1]
+    assert got[1][1] is None and merged["index"].tolist() == list(range(n))
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    lib = build_hostsim.load()
+    nint = 3 * 2 * 16
+    res = refine.find_batched(lambda ni: NBodySystB200(T, ni, _lib_handle=lib), refine.find_starts(T, nint, range(n)), nint, gradtol=1e-9,
+                              maxiter=30, n_reconverge_it_max=0, Newt_err_norm_max=1e-7, Newt_err_norm_max_save=1e-5)
+    assert np.array_equal(merged["outcome"], res.outcome)
+    # single-process queue
+    from choreographies2_b200 import sweep as sw
+    q1 = sw.ChunkQueue(5, 2)
+    assert [q1.next(), q1.next(), q1.next(), q1.next()] == [(0, 2), (2, 4), (4, 5), None]
