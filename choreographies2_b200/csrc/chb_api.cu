@@ -1234,6 +1234,15 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
             int rcw = level_upload(p, Wm, &S.pair_w);
             if (rcw) { free_level(p); return rcw; }
             S.pair_spad = spad;
+            {   // every pair of distinct segments interacts with the same weight?
+                bool uni = true;
+                const double w0 = Wm[1];
+                for (int a = 0; a < T.nsegm && uni; ++a)
+                    for (int b = 0; b < T.nsegm && uni; ++b)
+                        if (a != b) uni = Wm[(size_t)a * spad + b] == w0;
+                S.pair_uniform = (uni && w0 != 0.0 && !(getenv("CHB_PAIR_UNIFORM") && atoi(getenv("CHB_PAIR_UNIFORM")) == 0)) ? 1 : 0;
+                S.pair_wu = w0;
+            }
             const size_t arrd = (size_t)tile * spad * sizeof(cd), wbytes = (size_t)T.nsegm * spad * sizeof(double);
             p->dense_threads = 256 / spad * spad >= spad ? 256 : spad;
             p->dense_smem[0] = red_bytes + wbytes + arrd;
@@ -1752,7 +1761,7 @@ CHB_KERNEL void k_pair(ChbSys S, const double *seg, const double *dseg, double *
                    globalmul, spos, sdpos, sout, red);
 }
 
-template <int MODE>
+template <int MODE, bool UNI>
 CHB_KERNEL void k_pair_dense(ChbSys S, const double *seg, const double *dseg, double *out, double *pot_part, double globalmul) {
     CHB_CTX_DECL;
     const long long blk = CHB_BLOCK_ID;
@@ -1760,15 +1769,15 @@ CHB_KERNEL void k_pair_dense(ChbSys S, const double *seg, const double *dseg, do
     const long long b = blk / S.pair_ntiles;
     double *red = (double *)CHB_SMEM;
     double *sw = red + 1024;
-    cd *spos = (cd *)(sw + (size_t)S.nsegm * S.pair_spad);
+    cd *spos = (cd *)(sw + (UNI ? (size_t)0 : (size_t)S.nsegm * S.pair_spad));
     cd *sout = spos + (size_t)S.pair_tile * S.pair_spad;
     cd *sdpos = sout + (size_t)S.pair_tile * S.pair_spad;
-    cta_pair_dense<MODE>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
+    cta_pair_dense<MODE, UNI>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
                          out ? out + b * S.segsz : (double *)0, pot_part ? pot_part + b * S.pair_ntiles + tile : (double *)0, tile,
                          globalmul, CHB_NTHREADS, spos, sdpos, sout, sw, red);
 }
 
-template <int MODE>
+template <int MODE, bool UNI>
 CHB_KERNEL void
 #ifndef CHB_HOSTSIM
 __launch_bounds__(256, 2)
@@ -1782,7 +1791,7 @@ k_pair_tile(ChbSys S, const double *seg, const double *dseg, double *out, double
     const size_t arr = (size_t)S.tile_nblk * CHB_TILE_SB * 32 * S.tile_ngrp;
     cd *xs = (cd *)(red + 1024);
     cd *accA = xs + arr, *accB = accA + arr, *dxs = accB + arr;
-    cta_pair_tile<MODE>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
+    cta_pair_tile<MODE, UNI>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
                         out ? out + b * S.segsz : (double *)0, pot_part ? pot_part + b * S.pair_ntiles + tile : (double *)0, tile,
                         globalmul, S.tile_nblk, S.tile_ngrp, xs, dxs, accA, accB, red);
 }
@@ -2087,22 +2096,24 @@ static int launch_pair(chb_plan *p, int mode, int64_t nb, const double *seg, con
 static int launch_pair_sys(chb_plan *p, const ChbSys &Sy, int mode, int64_t nb, const double *seg, const double *dseg,
                            double *out, double *pot_part, double globalmul, chb_stream_t st) {
     const long long grid = nb * p->sys.pair_ntiles;
+    // uniform-weight variants only for the plan's own law and weights (the hash sums reuse the same weights)
+    const bool uni = p->sys.pair_uniform != 0;
     if (p->sys.pair_tilek) {
-        if (mode == 0)
-            CHB_LAUNCH(p, k_pair_tile<0>, grid, p->tile_threads, p->tile_smem[0], st, Sy, seg, dseg, out, pot_part, globalmul);
-        else if (mode == 1)
-            CHB_LAUNCH(p, k_pair_tile<1>, grid, p->tile_threads, p->tile_smem[1], st, Sy, seg, dseg, out, pot_part, globalmul);
-        else
-            CHB_LAUNCH(p, k_pair_tile<2>, grid, p->tile_threads, p->tile_smem[2], st, Sy, seg, dseg, out, pot_part, globalmul);
+        const bool tu = uni && (p->sys.nsegm % CHB_TILE_SB == 0);
+#define CHB_TILE_LAUNCH(M, U) CHB_LAUNCH(p, (k_pair_tile<M, U>), grid, p->tile_threads, p->tile_smem[M == 0 ? 0 : M], st, Sy, seg, dseg, out, pot_part, globalmul)
+        if (mode == 0) { if (tu) CHB_TILE_LAUNCH(0, true); else CHB_TILE_LAUNCH(0, false); }
+        else if (mode == 1) { if (tu) CHB_TILE_LAUNCH(1, true); else CHB_TILE_LAUNCH(1, false); }
+        else { if (tu) CHB_TILE_LAUNCH(2, true); else CHB_TILE_LAUNCH(2, false); }
+#undef CHB_TILE_LAUNCH
         return CHB_OK;
     }
     if (p->sys.pair_dense) {
-        if (mode == 0)
-            CHB_LAUNCH(p, k_pair_dense<0>, grid, p->dense_threads, p->dense_smem[1], st, Sy, seg, dseg, out, pot_part, globalmul);
-        else if (mode == 1)
-            CHB_LAUNCH(p, k_pair_dense<1>, grid, p->dense_threads, p->dense_smem[1], st, Sy, seg, dseg, out, pot_part, globalmul);
-        else
-            CHB_LAUNCH(p, k_pair_dense<2>, grid, p->dense_threads, p->dense_smem[2], st, Sy, seg, dseg, out, pot_part, globalmul);
+        const size_t wb = uni ? (size_t)p->sys.nsegm * p->sys.pair_spad * sizeof(double) : 0;  // no weight matrix in shared memory
+#define CHB_DENSE_LAUNCH(M, U, SM) CHB_LAUNCH(p, (k_pair_dense<M, U>), grid, p->dense_threads, (SM) - wb, st, Sy, seg, dseg, out, pot_part, globalmul)
+        if (mode == 0) { if (uni) CHB_DENSE_LAUNCH(0, true, p->dense_smem[1]); else CHB_DENSE_LAUNCH(0, false, p->dense_smem[1]); }
+        else if (mode == 1) { if (uni) CHB_DENSE_LAUNCH(1, true, p->dense_smem[1]); else CHB_DENSE_LAUNCH(1, false, p->dense_smem[1]); }
+        else { if (uni) CHB_DENSE_LAUNCH(2, true, p->dense_smem[2]); else CHB_DENSE_LAUNCH(2, false, p->dense_smem[2]); }
+#undef CHB_DENSE_LAUNCH
         return CHB_OK;
     }
     if (mode == 0)

@@ -117,6 +117,8 @@ struct ChbSys {
     // [nsegm][pair_spad], pair_spad = nsegm rounded up to a multiple of 32; pair_dense = 1 when the level uses it
     int pair_dense, pair_spad;
     const double *pair_w;
+    int pair_uniform;  // all interacting pairs share the weight pair_wu
+    double pair_wu;
     int pair_tilek, tile_nblk, tile_ngrp;  // cta_pair_tile serves the level: segment blocks of 8, groups of 32 samples per CTA
     long long scratch_per_state;  // cd slots
 };
@@ -764,7 +766,9 @@ CHB_HD double chb_rsqrt_fast(double d) {
 #endif
 }
 
-template <int MODE, class Ctx>
+// UNI: every interacting pair has the same weight S.pair_wu (equal masses and charges -- every nC / nB test system): no weight
+// matrix in shared memory (more resident CTAs), no weight loads or multiplies inside the loop
+template <int MODE, bool UNI, class Ctx>
 CHB_D void cta_pair_dense(Ctx &ctx, const ChbSys &S, const double *seg_b, const double *dseg_b, double *out_b,
                            double *pot_out, int tile, double globalmul, int nthreads, cd *spos, cd *sdpos, cd *sout,
                            double *sw, double *red) {
@@ -778,7 +782,8 @@ CHB_D void cta_pair_dense(Ctx &ctx, const ChbSys &S, const double *seg_b, const 
             spos[i * SP + s] = ((const cd *)seg_b)[src];
             if (MODE == 2) sdpos[i * SP + s] = ((const cd *)dseg_b)[src];
         }
-        for (int idx = tid; idx < nS * SP; idx += nthr) sw[idx] = S.pair_w[idx];
+        if (!UNI)
+            for (int idx = tid; idx < nS * SP; idx += nthr) sw[idx] = S.pair_w[idx];
         red[tid] = 0.0;
     });
     const double inv_size = 1.0 / (double)S.segm_size;
@@ -799,7 +804,7 @@ CHB_D void cta_pair_dense(Ctx &ctx, const ChbSys &S, const double *seg_b, const 
             double gx = 0.0, gy = 0.0, e = 0.0;
 #pragma unroll 4
             for (int s = 0; s < nS; ++s) {
-                const double w = sw[s * SP + t];
+                const double w = UNI ? 1.0 : sw[s * SP + t];  // UNI: the s == t term (d = 0, x^2 forced to 1) only adds to e, removed below
                 const cd xs = xrow[s];
                 const double dx = xs.x - xt.x, dy = xs.y - xt.y;
                 double xsq = fma(dx, dx, dy * dy);
@@ -836,10 +841,20 @@ CHB_D void cta_pair_dense(Ctx &ctx, const ChbSys &S, const double *seg_b, const 
                     }
                 }
             }
+            if (UNI && MODE <= 1) {  // take the self term out of the energy sum
+                if (S.law_kind == 0) {
+                    e -= chb_rsqrt_fast(1.0);
+                } else {
+                    double V, V1, V2;
+                    chb_inter_law(S, 1.0, &V, &V1, &V2);
+                    e += V;
+                }
+            }
             // g_t = -w_i / segm_size * globalmul * sum_s [...] (the factor 2 and W[s][t] are inside the sums)
-            const double f = -wi * inv_size * globalmul;
+            const double wu = UNI ? S.pair_wu : 1.0;
+            const double f = -wi * inv_size * globalmul * wu;
             if (MODE >= 1) sout[i * SP + t] = mk(f * gx, f * gy);
-            esum = fma(-0.5 * wi * inv_size, e, esum);  // ordered pairs count every bin twice; e holds -sum V w
+            esum = fma(-0.5 * wi * inv_size * wu, e, esum);  // ordered pairs count every bin twice; e holds -sum V w
         }
         if (MODE <= 1) red[tid] += esum;
     });
@@ -911,7 +926,7 @@ CHB_HD void chb_tile_eval(int law_kind, const double *law, double w, const cd &x
     }
 }
 
-template <int MODE, class Ctx>
+template <int MODE, bool UNI, class Ctx>
 CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const double *dseg_b, double *out_b, double *pot_out,
                           int tile, double globalmul, int nblk, int ngrp, cd *xs, cd *dxs, cd *accA, cd *accB, double *red) {
     constexpr int SB = CHB_TILE_SB, SBB = (MODE == 2) ? 2 : 4;
@@ -960,7 +975,7 @@ CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const d
 #pragma unroll
                     for (int b = a + 1; b < SB; ++b) {
                         const int sa = A * SB + a, sb = A * SB + b;
-                        const double w = (sa < nS && sb < nS) ? S.pair_w[sa * WSP + sb] : 0.0;
+                        const double w = UNI ? 1.0 : ((sa < nS && sb < nS) ? S.pair_w[sa * WSP + sb] : 0.0);
                         chb_tile_eval<MODE>(S.law_kind, S.law, w, xa[a], xa[b], dxa[a], dxa[b], ga[a], ga[b], e);
                     }
             } else {
@@ -978,7 +993,7 @@ CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const d
 #pragma unroll
                         for (int b = 0; b < SBB; ++b) {
                             const int sa = A * SB + a, sb = B * SB + jb * SBB + b;
-                            const double w = (sa < nS && sb < nS) ? S.pair_w[sa * WSP + sb] : 0.0;
+                            const double w = UNI ? 1.0 : ((sa < nS && sb < nS) ? S.pair_w[sa * WSP + sb] : 0.0);
                             chb_tile_eval<MODE>(S.law_kind, S.law, w, xa[a], xb[b], dxa[a], dxb[b], ga[a], gb[b], e);
                         }
                     if (MODE >= 1) {
@@ -1000,7 +1015,7 @@ CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const d
             if (MODE <= 1) {
                 const int gi = i0 + j;
                 const double wi = (store != S.segm_size && (gi == 0 || gi == store - 1)) ? 0.5 : 1.0;
-                if (j < n) red[tid] += -wi * e / (double)S.segm_size;
+                if (j < n) red[tid] += -wi * (UNI ? S.pair_wu : 1.0) * e / (double)S.segm_size;
             }
         });
     }
@@ -1012,7 +1027,7 @@ CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const d
                 if (j >= n) continue;
                 const int gi = i0 + j;
                 const double wi = (store != S.segm_size && (gi == 0 || gi == store - 1)) ? 0.5 : 1.0;
-                const double f = -wi * inv_size * globalmul;
+                const double f = -wi * inv_size * globalmul * (UNI ? S.pair_wu : 1.0);
                 const cd g = cadd(accA[idx], accB[idx]);
                 ((cd *)out_b)[(long long)s * store + gi] = mk(f * g.x, f * g.y);
             }
