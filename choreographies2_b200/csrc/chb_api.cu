@@ -2362,9 +2362,10 @@ static int arnoldi_launch(chb_plan *p, const char *name, int64_t batch, int64_t 
         CHB_LAUNCH(p, k_arnoldi_reg<16>, batch, CHK_THREADS, 0, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
     else {
         const size_t smem = sizeof(double) * (size_t)n;
-        CHB_REQUIRE(smem <= 200 * 1024, CHB_ERR_UNSUPPORTED,
-                    "chb_arnoldi_step_dev / chb_gmres_step_dev: more than 25600 parameters per state");
-        CHB_LAUNCH(p, k_arnoldi_smem, batch, CHK_THREADS, smem, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
+        if (smem <= 200 * 1024)
+            CHB_LAUNCH(p, k_arnoldi_smem<false>, batch, CHK_THREADS, smem, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
+        else  // rows longer than shared memory: candidate vector in its destination row
+            CHB_LAUNCH(p, k_arnoldi_smem<true>, batch, CHK_THREADS, 0, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
     }
 #else
     (void)st;
@@ -2818,7 +2819,6 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
                 "chb_newton_krylov_dev: need 1 <= restart <= 62, maxiter >= 0");
     const int m = opts->restart;
     const long long n = p->sys.nparams;
-    CHB_REQUIRE(n * 8 <= 200 * 1024, CHB_ERR_UNSUPPORTED, "chb_newton_krylov_dev: more than 25600 parameters per state");
     CHB_REQUIRE(ws && ws_bytes >= nk_ws_bytes(p, batch, m), CHB_ERR_WORKSPACE, "chb_newton_krylov_dev: workspace missing or too small");
     CHB_SET_DEVICE();
     chb_stream_t st = (chb_stream_t)stream;

@@ -442,17 +442,21 @@ k_givens_tail(long long rows, int j, ChkGivens G) {
 }
 
 // larger rows: the candidate vector lives in shared memory (8 n bytes), every basis row is streamed once from HBM for the dot
-// product and once more for the update (an L2 hit: the same CTA just read it)
+// product and once more for the update (an L2 hit: the same CTA just read it).  GMEM: rows longer than shared memory (the deep
+// refinement levels of a search, n > 25600): the candidate lives in its destination row V[j+1] (every thread only ever touches
+// its own elements, so plain loads / stores suffice).
+template <bool GMEM>
 __global__ void __launch_bounds__(CHK_THREADS, 1)
 k_arnoldi_smem(long long rows, long long n, int j, int ldh, double *V, const double *w, const unsigned char *skip, double *h,
                ChkGivens G) {
-    extern __shared__ double chk_acc[];
+    extern __shared__ double chk_acc_s[];
     __shared__ double sred[2][CHK_THREADS / 32];
     __shared__ double sh[64];
     const long long a = blockIdx.x;
     const int tid = threadIdx.x;
     const size_t vs = (size_t)rows * (size_t)n;
     double *vout = V + (size_t)(j + 1) * vs + (size_t)a * n;
+    double *chk_acc = GMEM ? vout : chk_acc_s;
     if (skip && skip[a]) {  // (inside the library's GMRES nobody reads the vectors of a stopped state: no zero fill)
         if (!G.R)
             for (long long e = tid; e < n; e += CHK_THREADS) vout[e] = 0.0;

@@ -498,7 +498,7 @@ class NBodySystB200:
         if not self._direct_ok(V):
             return False
         batch, n = int(w.shape[0]), int(w.shape[1])
-        if n * 8 > 200 * 1024 or j >= 62:
+        if j >= 62:
             return False
         if tuple(V.shape[1:]) != (batch, n) or V.shape[0] < j + 2 or tuple(h.shape[:1]) != (batch,) or h.shape[1] < j + 2:
             raise ValueError("arnoldi_step: inconsistent shapes")
@@ -622,7 +622,7 @@ class NBodySystB200:
             return False
         batch, n = int(w.shape[0]), int(w.shape[1])
         m = int(R.shape[2])
-        if n * 8 > 200 * 1024 or m > 62:
+        if m > 62:
             return False
         want = {"V": (m + 1, batch, n), "R": (batch, m + 1, m), "g": (batch, m + 1), "cs": (batch, m, 2), "target": (batch,),
                 "kdone": (batch,), "done": (batch,)}
