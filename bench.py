@@ -59,6 +59,8 @@ def parse_args():
     ap.add_argument("--newton-reps", type=int, default=5, help="timed repetitions of the solves/hour leg (median reported)")
     ap.add_argument("--newton-ref-seeds", type=int, default=0, help="seeds of the CPU arm of the solves/hour leg (0 = auto)")
     ap.add_argument("--no-configs", dest="configs", action="store_false", help="skip the extra BASELINE configurations")
+    ap.add_argument("--no-pin-numa", dest="pin_numa", action="store_false",
+                    help="do not bind a rank to the CPU set of its GPU (nvidia-smi topo -m) when several ranks share the host")
     return ap.parse_args()
 
 
@@ -70,6 +72,25 @@ def workload_config(args, nparams, world):
         "global_batch": args.batch * world, "parallelism": f"batch-shard x{world} (no collective)",
         "l2": "inputs larger than L2 (params+grad = %.0f MB per step per GPU)" % (2 * args.batch * nparams * 8 / 1e6),
     }
+
+
+def gpu_cpu_affinity(index):
+    """CPU set nvidia-smi reports for a GPU (its NUMA node), or None."""
+    try:
+        out = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout
+        for line in out.splitlines():
+            f = line.split()
+            if f and f[0] == f"GPU{index}":
+                for tok in f[1:]:
+                    if tok[0].isdigit() and ("-" in tok or "," in tok):
+                        cpus = set()
+                        for part in tok.split(","):
+                            a, _, b = part.partition("-")
+                            cpus.update(range(int(a), int(b or a) + 1))
+                        return cpus
+    except Exception:
+        pass
+    return None
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -254,6 +275,11 @@ def run_reference(args):
 
 
 
+# refinement depth of the solves/hour leg, both arms.  The reference's 3C configuration allows 4 doublings of nint; the rare starts
+# that run into a collision then spend minutes per seed in the REFERENCE at nint 24576 / 49152 (1000 Newton iterations per optimiser
+# level, 3 ms per gradient), which no bounded CPU sample can afford.  One doubling keeps the loop, the line search and the six optimiser
+# levels of the configuration; the full-depth comparison is profiles/r02_find_compare_3C_nintfac600_32seeds.txt.
+NEWTON_RECONVERGE = 1
 FP64_PEAK_TFLOPS = 37.0  # measured FMA peak of this pool's B200 (tools/fp64_peak.cu, profiles/r01_fp64_pcie_peaks.json)
 
 
@@ -306,6 +332,7 @@ def _search_cpu_worker(task):
     NBS.nint_fac = fac0
     x0 = ref_find.find_starts(NBS, seeds)
     cfg = {k: v for k, v in ref_find.CONFIG_3C.items() if k not in ("nint_fac_init", "coeff_ampl_o", "k_infl", "k_max", "coeff_ampl_min")}
+    cfg["n_reconverge_it_max"] = NEWTON_RECONVERGE
     t = time.perf_counter()
     outs = [ref_find.reference_find(NBS, x0[i], fac0, **cfg)[0] for i in range(len(seeds))]
     return time.perf_counter() - t, outs
@@ -350,6 +377,7 @@ def newton_leg(args, rank, world, dev, barrier, max_over_ranks):
     starts = refine.find_starts(Tn, nint0, range(rank * Bn, (rank + 1) * Bn), **refine.RANDOM_CONFIG_3C)
     x0n = torch.from_numpy(starts).to(dev)
     kw = dict(refine.SEARCH_CONFIG_3C)
+    kw["n_reconverge_it_max"] = NEWTON_RECONVERGE
     refine.find_batched(make, x0n[:min(Bn, 256)].clone(), nint0, **kw)  # warm-up: plans of the levels, workspaces, allocator
     times, res = [], None
     l0 = sum(p.kernel_launches for p in plans.values())
@@ -367,7 +395,7 @@ def newton_leg(args, rank, world, dev, barrier, max_over_ranks):
            "seconds_median": med, "seconds_min": ts[0], "seconds_max": ts[-1], "repetitions": len(ts), "batch_per_gpu": Bn,
            "system": "3C", "nint0": nint0, "nparams0": int(make(nint0).nparams),
            "settings": "find.py loop with the reference's 3C configuration: GMRES(20), wolfe line search smin 0.1, optimiser levels "
-                       "gradtol 1e-1 .. 1e-11 (2-norm) with maxiter 100/1000/1000/1000/500/500, refinement x2 up to 4 times, "
+                       "gradtol 1e-1 .. 1e-11 (2-norm) with maxiter 100/1000/1000/1000/500/500, refinement x2 once (n_reconverge_it_max 1, see NEWTON_RECONVERGE), "
                        "Newt_err_norm_max 1e-11 / 1e-8; starts x_avg + x_ptp U[0,1) from Make_params_bounds(0.1, 3, 50, 1e-16)",
            "rank0": {"found": int((res.outcome == refine.FOUND).sum()), "approximate": int((res.outcome == refine.APPROX).sum()),
                      "not_converged": int((res.outcome == refine.NOT_CONVERGED).sum()), "collision": int((res.outcome == refine.COLLISION).sum()),
@@ -376,7 +404,7 @@ def newton_leg(args, rank, world, dev, barrier, max_over_ranks):
                      "newton_iterations_mean": float(res.newton_iterations.mean())},
            "note": "a solve = one run of the search loop from one random start to termination (saved, abandoned, escaped ...)"}
     if rank == 0 and world == 1 and not args.no_cpu:
-        n = args.newton_ref_seeds or 48
+        n = args.newton_ref_seeds or 16
         out["cpu_baseline"] = search_cpu_arm(nint0, 1, n)
     return out
 
@@ -390,6 +418,16 @@ def run_b200(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    numa = None
+    if world > 1 and args.pin_numa:
+        # several ranks stream pinned buffers through one host: keep each rank (and the first touch of its buffers) on the
+        # NUMA node of its GPU
+        numa = gpu_cpu_affinity(local)
+        if numa:
+            try:
+                os.sched_setaffinity(0, numa)
+            except Exception:
+                numa = None
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -513,6 +551,7 @@ def run_b200(args):
         dt = max_over_ranks(dt)
         e2e = {"value": world * B * ksteps / dt, "unit": UNIT, "h2d_bytes_per_step": int(B * npar * 8),
                "d2h_bytes_per_step": int(B * (npar + 1) * 8), "steps": ksteps,
+               "numa_pinned_cpus": (len(numa) if numa else None),
                "api": "NBodySystB200.params_to_action_and_grad(pinned numpy in/out) -> chb_run_host(CHB_OP_ACTION_GRAD): "
                       "3-slot stream pipeline of 48 MB slices (H2D, kernels, D2H overlapped)"}
         assert abs(float(a_h.sum()) - checksum) <= 1e-9 * abs(checksum)

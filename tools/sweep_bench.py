@@ -24,7 +24,7 @@ sys.path.insert(0, ROOT)
 
 
 def _cpu_worker(task):
-    seeds, nint0 = task
+    seeds, nint0, reconverge = task
     for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS"):
         os.environ[k] = "1"
     from oracle import ref_loader, ref_find
@@ -34,6 +34,7 @@ def _cpu_worker(task):
     NBS.nint_fac = fac0
     x0 = ref_find.find_starts(NBS, seeds)
     cfg = {k: v for k, v in ref_find.CONFIG_3C.items() if k not in ("nint_fac_init", "coeff_ampl_o", "k_infl", "k_max", "coeff_ampl_min")}
+    cfg["n_reconverge_it_max"] = reconverge
     out = []
     t = time.perf_counter()
     for i, s in enumerate(seeds):
@@ -54,6 +55,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=2048)
     ap.add_argument("--static", action="store_true", help="static contiguous split instead of the dynamic chunk queue (A/B)")
     ap.add_argument("--cpu-seeds", type=int, default=0, help="seeds also run through the reference's loop on the host (rank 0)")
+    ap.add_argument("--reconverge", type=int, default=4, help="n_reconverge_it_max of both arms (the 3C configuration has 4)")
     ap.add_argument("--duplicate-eps", type=float, default=1e-8, help="rtol of TestHashSame (Solver_Checks.duplicate_eps)")
     a = ap.parse_args()
     import torch
@@ -74,6 +76,7 @@ def main():
         return plans[nint]
 
     kw = dict(refine.SEARCH_CONFIG_3C)
+    kw["n_reconverge_it_max"] = a.reconverge
     starts = lambda lo, hi: torch.from_numpy(refine.find_starts(T, a.nint, range(lo, hi), **refine.RANDOM_CONFIG_3C)).to(dev)  # noqa: E731
     refine.find_batched(make, starts(0, 128), a.nint, **kw)  # warm-up: plans of the levels, workspaces
     queue = sweep.ChunkQueue(a.guesses, a.chunk, rank, world) if not a.static else None
@@ -152,7 +155,7 @@ def main():
                    "level": int(merged["level"][i])} for i in distinct]
         line = {
             "metric": "Newton orbit solves/hour (sharded search sweep with refinement, hash and duplicate filter)", "n_gpus": world,
-            "system": a.system, "nint0": a.nint, "guesses": a.guesses, "chunk": a.chunk, "queue": "static split" if a.static else "dynamic (TCPStore counter)",
+            "system": a.system, "nint0": a.nint, "n_reconverge_it_max": a.reconverge, "guesses": a.guesses, "chunk": a.chunk, "queue": "static split" if a.static else "dynamic (TCPStore counter)",
             "seconds": dt, "solves_per_hour": a.guesses / dt * 3600, "balance": balance,
             "found": int((out == refine.FOUND).sum()), "approximate": int((out == refine.APPROX).sum()),
             "not_converged": int((out == refine.NOT_CONVERGED).sum()), "collision": int((out == refine.COLLISION).sum()),
@@ -166,7 +169,7 @@ def main():
             import multiprocessing as mp
             P = min(os.cpu_count() or 1, a.cpu_seeds)
             per = (a.cpu_seeds + P - 1) // P
-            tasks = [(list(range(p * per, min(a.cpu_seeds, (p + 1) * per))), a.nint) for p in range(P)]
+            tasks = [(list(range(p * per, min(a.cpu_seeds, (p + 1) * per))), a.nint, a.reconverge) for p in range(P)]
             tasks = [t for t in tasks if t[0]]
             tc = time.perf_counter()
             with mp.get_context("spawn").Pool(len(tasks)) as pool:
