@@ -66,6 +66,7 @@ SYMBOLS = {
     "chb_plan_query": (C.c_int, [_vp, C.c_int, _p64]),
     "chb_plan_set_chunk": (C.c_int, [_vp, _i64]),
     "chb_plan_set_fused": (C.c_int, [_vp, C.c_int]),
+    "chb_plan_set_split": (C.c_int, [_vp, C.c_int]),
     "chb_workspace_bytes": (C.c_int, [_vp, _i64, C.POINTER(_sz)]),
     "chb_params_to_segmpos_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),
     "chb_segmpos_to_params_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),

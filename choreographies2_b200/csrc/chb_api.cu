@@ -118,8 +118,11 @@ struct chb_plan {
     const long long *d_pos_off = nullptr;  // [nloop + 1] offsets of the loops in position-parameter space (params_changevar)
     long long nparams_incl_o = 0;
     int big_active = 0;     // staged transforms by the parity-split kernels of chb_big.cuh (planar RFFT systems without a fused kernel)
-    ChbBigSys bigsys;
-    size_t big_smem = 0;
+    ChbBigSys bigsys[3];    // residue splits R = 2, 4, 8 (index log2 R - 1); big_ok[i] says which exist at this level
+    size_t big_smem[3] = {0, 0, 0};
+    int big_ok[3] = {0, 0, 0};
+    int big_min_len[3] = {0, 0, 0};  // shortest transform length of each split
+    int big_force_r = 0;    // CHB_BIG_R: A/B knob, use this split whenever it exists
     int fused5_active = 0;  // the level is served by the general fused kernel (chb_fused5.cuh) instead of versions 3 / 4
     Ch5Sys f5;              // passed by value (constant bank) to k_fused5
 };
@@ -817,12 +820,12 @@ static int fused5_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm
 }
 
 // ---- parity-split staged transforms (chb_big.cuh) ----------------------------------------------------
-// returns 1 when k_big_fwd / k_big_adj can serve the level's transforms (and fills p->bigsys), 0 when not, <0 on error
-static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_size, int segm_store) {
+// returns 1 when k_big_fwd<R> / k_big_adj<R> can serve the level's transforms (and fills F, *smem), 0 when not, <0 on error
+static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_size, int segm_store, int R, ChbBigSys &F, size_t *smem) {
     const HostTables &T = p->T;
     if (T.G != 2 || segm_store != segm_size || T.nloop > CHB_BIG_MAX_LOOPS || T.vel) return 0;
-    ChbBigSys &F = p->bigsys;
     memset(&F, 0, sizeof(F));
+    F.R = R;
     F.nloop = T.nloop;
     F.segm_size = segm_size;
     F.nparams = p->sys.nparams;
@@ -832,8 +835,8 @@ static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_si
     for (int il = 0; il < T.nloop; ++il) {
         const ChbLoop &L = loops[il];
         if (L.shortcut != CHB_RFFT || L.nnz != 1 || L.nppl != 4 || L.n_sub_fft != 1 || !L.has_k0) return 0;
-        const int N = 2 * L.npr, Nh = L.npr;
-        if (Nh < 2 || N % segm_size != 0) return 0;
+        const int N = 2 * L.npr, Nh = N / R;
+        if (N % R != 0 || Nh < 2 || N % segm_size != 0) return 0;
         ChfLoop &h = F.loops[il].h;
         h.N = Nh;
         h.npr = L.npr;
@@ -859,8 +862,11 @@ static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_si
             if (v < 0) return 0;
         if (level_upload(p, slot_seg, &F.loops[il].slot_seg)) return -1;
     }
-    int Tg = ((maxNh / 32 + 31) / 32) * 32;
-    Tg = std::max(64, std::min(Tg, CHF_MAX_THREADS));
+    // one radix-16 butterfly per thread and pass when the half length allows it: these kernels are latency-bound (one CTA per SM
+    // because of the buffer), so the warps per SM set their speed; CHB_BIG_T caps the block size (A/B knob, read once)
+    static const int big_t_cap = [] { const char *e = getenv("CHB_BIG_T"); const int v = e ? atoi(e) : 0; return v >= 64 ? std::min(v, CHB_BIG_MAX_THREADS) : CHB_BIG_MAX_THREADS; }();
+    int Tg = ((maxNh / 16 + 31) / 32) * 32;
+    Tg = std::max(64, std::min(Tg, big_t_cap));
     F.T = Tg;
     size_t tw_room = 0;
     {
@@ -882,7 +888,7 @@ static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_si
             continue;
         }
         first_loop_of_N[h.N] = il;
-        const int Nh = h.N, N = 2 * Nh;
+        const int Nh = h.N, N = R * Nh;
         std::vector<int> rev(Nh);
         for (int k = 0; k < Nh; ++k) {
             int kk = k, pos = 0, Lcur = Nh;
@@ -917,7 +923,7 @@ static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_si
             Lcur = Lp;
         }
         max_tw = std::max(max_tw, off);
-        std::vector<cd> thi((size_t)(Nh + 127) / 128 + 1), tlo(128);
+        std::vector<cd> thi((size_t)(N + 127) / 128 + 1), tlo(128);
         for (size_t j = 0; j < thi.size(); ++j) {
             double c, sn;
             exact_root((long long)j * 128, N, &c, &sn);
@@ -931,8 +937,8 @@ static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_si
         if (level_upload(p, thi, &BL.t_hi) || level_upload(p, tlo, &BL.t_lo)) return -1;
     }
     F.tw_smem_len = max_tw;
-    p->big_smem = CHF_RED_BYTES + ((size_t)maxNh + max_tw) * sizeof(cd);
-    return p->big_smem <= p->smem_limit ? 1 : 0;
+    *smem = CHF_RED_BYTES + ((size_t)maxNh + max_tw) * sizeof(cd);
+    return *smem <= p->smem_limit ? 1 : 0;
 }
 
 extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
@@ -1292,10 +1298,17 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
         }
         p->big_active = 0;
         {  // staged path (also the A/B path of fused layouts): parity-split transform kernels where the layout allows them
-            int rcb = big_setup(p, loops, segm_size, segm_store);
-            if (rcb < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: transform setup failed"); }
-            if (getenv("CHB_BIG") && atoi(getenv("CHB_BIG")) == 0) rcb = 0;  // A/B knob
-            p->big_active = rcb;
+            static const int big_on = [] { const char *e = getenv("CHB_BIG"); return e ? atoi(e) : 1; }();    // A/B knobs, read once
+            static const int big_r = [] { const char *e = getenv("CHB_BIG_R"); return e ? atoi(e) : 0; }();
+            if (big_r) p->big_force_r = big_r;
+            for (int i = 0; i < 3; ++i) {
+                int rcb = big_on ? big_setup(p, loops, segm_size, segm_store, 2 << i, p->bigsys[i], &p->big_smem[i]) : 0;
+                if (rcb < 0) { free_level(p); return chb_fail(CHB_ERR_CUDA, "chb_plan_set_nint: transform setup failed"); }
+                p->big_ok[i] = rcb;
+                p->big_min_len[i] = 1 << 30;
+                for (int il = 0; rcb > 0 && il < T.nloop; ++il) p->big_min_len[i] = std::min(p->big_min_len[i], p->bigsys[i].loops[il].h.N);
+                p->big_active |= rcb;
+            }
         }
         p->ready = true;
     }
@@ -1356,7 +1369,7 @@ extern "C" int chb_plan_query(const chb_plan *p, int what, int64_t *v) {
         case CHB_Q_SEGM_STORE: *v = p->sys.segm_store; break;
         case CHB_Q_SEGMPOS_SIZE: *v = p->sys.segsz; break;
         case CHB_Q_NPARAMS_INCL_O: *v = p->nparams_incl_o; break;
-        case CHB_Q_STAGED_TRANSFORM: *v = p->big_active ? 1 : 0; break;
+        case CHB_Q_STAGED_TRANSFORM: *v = p->big_active ? (p->big_ok[0] ? 2 : 0) + (p->big_ok[1] ? 4 : 0) + (p->big_ok[2] ? 8 : 0) : 0; break;
         case CHB_Q_PAIR_KERNEL: *v = p->sys.pair_tilek ? 2 : (p->sys.pair_dense ? 1 : 0); break;
 #ifdef CHB_HOSTSIM
         case CHB_Q_HOST_POINTERS: *v = 1; break;
@@ -1395,6 +1408,13 @@ extern "C" int chb_plan_set_fused(chb_plan *p, int enable) {
 #else
     p->fused_enabled = enable > 0 ? (enable >= 4 ? 4 : 3) : 0;  // the older fused variants (1, 2) are compiled only with -DCHF_KEEP_OLD
 #endif
+    return CHB_OK;
+}
+
+extern "C" int chb_plan_set_split(chb_plan *p, int split) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_split: NULL plan");
+    CHB_REQUIRE(split == 0 || split == 2 || split == 4 || split == 8, CHB_ERR_INVALID_ARGUMENT, "chb_plan_set_split: split must be 0, 2, 4 or 8");
+    p->big_force_r = split;
     return CHB_OK;
 }
 
@@ -1979,32 +1999,39 @@ CHB_KERNEL void CHF_BOUNDS k_fused5(CH5_SYS_PARAM, ChfArgs A) {
     }
 }
 
-// parity-split staged transforms (chb_big.cuh): one CTA per (state, loop, parity)
-CHB_KERNEL void CHF_BOUNDS k_big_fwd(ChbBigSys F, ChbSys S, const double *params, double *segmpos, double *kin_part) {
+// residue-split staged transforms (chb_big.cuh): one CTA per (state, loop, residue modulo R)
+#ifndef CHB_HOSTSIM
+#define CHB_BIG_BOUNDS __launch_bounds__(CHB_BIG_MAX_THREADS, 1)
+#else
+#define CHB_BIG_BOUNDS
+#endif
+template <int R>
+CHB_KERNEL void CHB_BIG_BOUNDS k_big_fwd(ChbBigSys F, ChbSys S, const double *params, double *segmpos, double *kin_part) {
     CHB_CTX_DECL;
     const long long blk = CHB_BLOCK_ID;
-    const int par = (int)(blk & 1);
-    const int il = (int)((blk >> 1) % F.nloop);
-    const long long b = (blk >> 1) / F.nloop;
+    const int q = (int)(blk % R);
+    const int il = (int)((blk / R) % F.nloop);
+    const long long b = (blk / R) / F.nloop;
     const ChbBigLoop &L = F.loops[il];
     double *red = (double *)CHB_SMEM;
     cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
     cd *tw = buf + L.h.N;
     cta_big_prologue(ctx, L.h, tw);
-    cta_big_fwd(ctx, F, S, L, par, params + b * F.nparams, segmpos ? segmpos + b * F.segsz : (double *)0,
-                kin_part ? kin_part + b * F.nloop + il : (double *)0, buf, tw, red);
+    cta_big_fwd<R>(ctx, F, S, L, q, params + b * F.nparams, segmpos ? segmpos + b * F.segsz : (double *)0,
+                   kin_part ? kin_part + b * F.nloop + il : (double *)0, buf, tw, red);
 }
-CHB_KERNEL void CHF_BOUNDS k_big_adj(ChbBigSys F, ChbSys S, const double *seg, double *out, const double *kin_src) {
+template <int R>
+CHB_KERNEL void CHB_BIG_BOUNDS k_big_adj(ChbBigSys F, ChbSys S, const double *seg, double *out, const double *kin_src) {
     CHB_CTX_DECL;
     const long long blk = CHB_BLOCK_ID;
-    const int par = (int)(blk & 1);
-    const int il = (int)((blk >> 1) % F.nloop);
-    const long long b = (blk >> 1) / F.nloop;
+    const int q = (int)(blk % R);
+    const int il = (int)((blk / R) % F.nloop);
+    const long long b = (blk / R) / F.nloop;
     const ChbBigLoop &L = F.loops[il];
     cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
     cd *tw = buf + L.h.N;
     cta_big_prologue(ctx, L.h, tw);
-    cta_big_adj(ctx, F, S, L, par, seg + b * F.segsz, out + b * F.nparams, kin_src ? kin_src + b * F.nparams : (const double *)0, buf, tw);
+    cta_big_adj<R>(ctx, F, S, L, q, seg + b * F.segsz, out + b * F.nparams, kin_src ? kin_src + b * F.nparams : (const double *)0, buf, tw);
 }
 
 #ifndef CHB_HOSTSIM
@@ -2065,11 +2092,33 @@ static unsigned long long smem_mask(const chb_plan *p) {
     } while (0)
 #endif
 
+// which residue split serves a launch of nb states: the smallest that exists when the batch fills the GPU (least folding work),
+// a larger one while the CTAs would not (few live states at the end of a search: parallelism inside the state)
+static int big_pick(const chb_plan *p, int64_t nb) {
+    if (p->big_force_r)
+        for (int i = 0; i < 3; ++i)
+            if ((2 << i) == p->big_force_r && p->big_ok[i]) return i;
+    int best = -1;
+    for (int i = 0; i < 3 && best < 0; ++i)
+        if (p->big_ok[i]) best = i;
+    const long long want = 2LL * p->num_sms;
+    for (int i = best + 1; i < 3; ++i) {
+        if (!p->big_ok[i]) continue;
+        if ((long long)nb * p->sys.nloop * (2 << best) >= want) break;
+        if (p->big_min_len[i] < 512) break;  // shorter transforms do not pay for the folding pass
+        best = i;
+    }
+    return best;
+}
 static int launch_fwd(chb_plan *p, int64_t nb, const double *params, double *segmpos, Workspace &W, bool want_kin,
                       unsigned long long mask, chb_stream_t st) {
     if (p->big_active) {
-        CHB_LAUNCH(p, k_big_fwd, 2 * nb * p->sys.nloop, p->bigsys.T, p->big_smem, st, p->bigsys, p->sys, params, segmpos,
-                   want_kin ? W.kin_part : (double *)0);
+        const int i = big_pick(p, nb);
+        const ChbBigSys &F = p->bigsys[i];
+        double *kp = want_kin ? W.kin_part : (double *)0;
+        if (i == 0) CHB_LAUNCH(p, k_big_fwd<2>, 2 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, params, segmpos, kp);
+        if (i == 1) CHB_LAUNCH(p, k_big_fwd<4>, 4 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, params, segmpos, kp);
+        if (i == 2) CHB_LAUNCH(p, k_big_fwd<8>, 8 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, params, segmpos, kp);
         return CHB_OK;
     }
     CHB_LAUNCH(p, k_fwd, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, p->sys, params, segmpos, W.scratch,
@@ -2079,7 +2128,11 @@ static int launch_fwd(chb_plan *p, int64_t nb, const double *params, double *seg
 static int launch_adj(chb_plan *p, int64_t nb, const double *seg, double *out, const double *kin_src, Workspace &W,
                       int mode, unsigned long long mask, chb_stream_t st) {
     if (p->big_active && mode == 0) {
-        CHB_LAUNCH(p, k_big_adj, 2 * nb * p->sys.nloop, p->bigsys.T, p->big_smem, st, p->bigsys, p->sys, seg, out, kin_src);
+        const int i = big_pick(p, nb);
+        const ChbBigSys &F = p->bigsys[i];
+        if (i == 0) CHB_LAUNCH(p, k_big_adj<2>, 2 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, seg, out, kin_src);
+        if (i == 1) CHB_LAUNCH(p, k_big_adj<4>, 4 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, seg, out, kin_src);
+        if (i == 2) CHB_LAUNCH(p, k_big_adj<8>, 8 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, seg, out, kin_src);
         return CHB_OK;
     }
     CHB_LAUNCH(p, k_adj, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, p->sys, seg, out, kin_src, W.scratch, mode,

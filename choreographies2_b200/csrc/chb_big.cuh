@@ -1,15 +1,22 @@
 // chb_big.cuh -- staged transforms for planar RFFT systems that do not fit the one-CTA-per-state kernels: many loops / segments
-// (20B, 16C, 2C3C5C ...) or loops too long for one CTA's shared memory (64C at nint 16384: 262 KB per state).
+// (20B, 16C, 2C3C5C ...) or loops too long for one CTA's shared memory (64C at nint 16384: 262 KB per state; the deep refinement
+// levels of a search, 3C at nint 49152: 786 KB).
 //
-// One CTA per (state, loop, parity).  A loop of N = 2 npr samples is the complex sequence z[n] = x[n] + i y[n]
-// (chb_fused.cuh); its transform is split by the PARITY of the time index,
-//     z[2m + par] = sum_{k < N/2} (Z[k] + (-1)^par Z[k + N/2]) w^(k par) exp(+2 pi i k m / (N/2)),      w = exp(+2 pi i / N),
-// so each CTA runs a complex FFT of length N/2 in shared memory (the register butterflies of chb_fused.cuh, stage tables in
-// shared memory) and writes every other sample of the loop's segments; both CTAs of a pair read all parameter rows (the second
-// read comes from L2).  The adjoint mirrors it on the spectral side: the CTA of parity par folds the segment gradient
-// g[n] + (-1)^par g[n + N/2], multiplies by conj(w)^(n par), transforms, and owns the result rows k = 2 k' + par -- the
-// Hermitian partner Y[N - k] has the same parity, so the split needs no exchange between the two CTAs.
-// Twiddles w^k come from a two-level table (k = 128 hi + lo), exact entries, one complex product.
+// One CTA per (state, loop, residue q of the time index modulo R), R = 2, 4 or 8.  A loop of N = 2 npr samples is the complex
+// sequence z[n] = x[n] + i y[n] (chb_fused.cuh); with M = N / R, w = exp(+2 pi i / N), omega = exp(+2 pi i / R),
+//     z[R m + q] = sum_{k < M} ( w^(k q) sum_{r < R} Z[k + r M] omega^(r q) ) exp(+2 pi i k m / M),
+// so each CTA folds the spectrum to M terms, runs a complex FFT of length M in shared memory (the register butterflies of
+// chb_fused.cuh, stage tables in shared memory) and writes every R-th sample of the loop's segments; all R CTAs of a loop read
+// all parameter rows (the repeats come from L2).  R is chosen per launch: the smallest that fits when the batch fills the GPU,
+// a larger one when few states are live (tail of a search: parallelism inside the state instead of across states).
+//
+// The adjoint mirrors it on the spectral side: the CTA of residue q folds the segment gradient sum_r g[n + r M] omega^(-q r),
+// multiplies by conj(w)^(n q), transforms, and holds Y[R k' + q].  A result row k needs Y[k] and Y[N - k]: for q = 0 and
+// q = R / 2 the Hermitian partner has the same residue (packed x + i y transform, nothing exchanged).  The other residues come
+// in pairs (q, R - q); there the two CTAs split by COORDINATE instead: CTA q transforms the x components for residue q, CTA
+// R - q the y components for residue q.  A real sequence has Y[N - k] = conj(Y[k]), so one transform serves the rows k = q and
+// k = R - q (mod R) of its coordinate: every row element is written by exactly one CTA (no atomics, deterministic).
+// Twiddles w^j come from a two-level table (j = 128 hi + lo), exact entries, one complex product.
 //
 // Reference restated: params_to_pos_slice (RFFT branch) :5463-5506, pos_slice_to_segmpos :5737-5813, segmpos_to_pos_slice_T
 // :5896-5976, pos_slice_to_params (RFFT branch, direction -1) :5645-5735, changevar_mom_pos(_T) :4489-4573 / :4746-4827,
@@ -18,21 +25,33 @@
 #include "chb_fused.cuh"
 
 #define CHB_BIG_MAX_LOOPS 24
+#define CHB_BIG_MAX_THREADS 512  // CHF_RED_BYTES holds 512 partial sums
 
 struct ChbBigLoop {
-    ChfLoop h;              // FFT plan of the half length Nh = N / 2 = npr (+ mom_off, nco_in, ncm, co0, co2, loopmul of the loop)
-    const cd *t_hi, *t_lo;  // exp(-2 pi i 128 j / N), j < ceil(Nh / 128);  exp(-2 pi i j / N), j < 128
+    ChfLoop h;              // FFT plan of the length M = N / R (+ mom_off, nco_in, ncm, co0, co2, loopmul of the loop)
+    const cd *t_hi, *t_lo;  // exp(-2 pi i 128 j / N), j <= N / 128;  exp(-2 pi i j / N), j < 128
     const int *slot_seg;    // [N / segm_size] generating segment stored in each slot of the slice
 };
 struct ChbBigSys {
-    int nloop, T, segm_size, pad;
+    int nloop, T, segm_size, R;
     int tw_smem_len;        // cd slots of stage tables copied to shared memory (behind the buffer)
+    int pad;
     long long nparams, segsz;
     ChbBigLoop loops[CHB_BIG_MAX_LOOPS];
 };
 
-CHB_HD cd chb_big_root(const ChbBigLoop &L, int k) {  // exp(-2 pi i k / N)
+CHB_HD cd chb_big_root(const ChbBigLoop &L, int k) {  // exp(-2 pi i k / N), 0 <= k < N
     return cmul(L.t_hi[k >> 7], L.t_lo[k & 127]);
+}
+CHB_HD cd chb_root8(int j) {  // exp(+2 pi i j / 8)
+    const double s = 0.70710678118654752440;
+    j &= 7;
+    const double c = (j == 0) ? 1.0 : (j == 4) ? -1.0 : (j == 2 || j == 6) ? 0.0 : (j == 1 || j == 7) ? s : -s;
+    const double sn = (j == 2) ? 1.0 : (j == 6) ? -1.0 : (j == 0 || j == 4) ? 0.0 : (j < 4) ? s : -s;
+    return mk(c, sn);
+}
+CHB_HD cd chb_big_omega(int R, int j) {  // exp(+2 pi i j / R), R in {2, 4, 8}
+    return chb_root8(j * (8 / R));
 }
 
 // row k >= 1 of the loop's parameter array -> Z[k] and its Hermitian mirror Z[N - k]
@@ -43,42 +62,61 @@ CHB_HD void chb_big_row(const double *rows, int k, double sc, cd *Z, cd *Zm, dou
     *Z = mk((p0 - p3) * sc, (p1 + p2) * sc);
     *Zm = mk((p0 + p3) * sc, (p2 - p1) * sc);
 }
+CHB_HD cd chb_cfma(cd acc, cd a, cd b) {  // acc + a * b
+    return mk(acc.x + (a.x * b.x - a.y * b.y), acc.y + (a.x * b.y + a.y * b.x));
+}
 
-template <class Ctx>
-CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbBigLoop &L, int par, const double *vec_b,
+// params -> the samples n = R m + q of the loop's segments (+ kinetic energy of the loop from the CTA of residue 0)
+template <int R, class Ctx>
+CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbBigLoop &L, int q, const double *vec_b,
                         double *segmpos_b, double *kin_out, cd *buf, const cd *twsm, double *red) {
     const ChfLoop &h = L.h;
-    const int Nh = h.N;
-    const double sgn = par ? -1.0 : 1.0;
+    const int M = h.N;
+    cd om[R];  // omega^(r q)
+    for (int r = 0; r < R; ++r) om[r] = chb_big_omega(R, r * q);
     ctx.groups(1, F.T, [&](auto &grp) {
         grp.par([&](int tid, int T) {
             double kin = 0.0;
             const double *rows = vec_b + h.mom_off - h.nco_in;
             const double lm = h.loopmul / (double)h.ncm;
-            for (int q = tid; q <= Nh / 2; q += T) {
-                const int k1 = q, k2 = Nh - q;
-                if (q == 0) {
+            for (int kk = tid; kk <= M / 2; kk += T) {
+                const int k1 = kk, k2 = M - kk;
+                cd Z, Zm;
+                if (kk == 0) {
+                    // Z[0] (zero frequency), Z[r M] for 0 < r < R / 2, the Nyquist term is zero, mirrors above it
                     const double c0 = h.co0 >= 0 ? vec_b[h.mom_off + h.co0] : 0.0;
                     const double c2 = h.co2 >= 0 ? vec_b[h.mom_off + h.co2] : 0.0;
-                    buf[chf_swz(h.rev[0], h.swm)] = mk(c0 * h.loopmul, c2 * h.loopmul);  // Z[0] + (-1)^par Z[N/2], Nyquist row = 0
+                    cd acc = mk(c0 * h.loopmul, c2 * h.loopmul);
+#pragma unroll
+                    for (int r = 1; r < R / 2; ++r) {
+                        chb_big_row(rows, r * M, lm * chf_rcp((double)(r * M)), &Z, &Zm, &kin);
+                        acc = chb_cfma(acc, Z, om[r]);
+                        acc = chb_cfma(acc, Zm, om[R - r]);
+                    }
+                    buf[chf_swz(h.rev[0], h.swm)] = acc;
                     continue;
                 }
-                cd Z1, Zm1, Z2, Zm2;
-                chb_big_row(rows, k1, lm * chf_rcp((double)k1), &Z1, &Zm1, &kin);
+                // A[k] = w^(k q) ( sum_{r < R/2} Z[k + r M] omega^(r q) + sum_{r < R/2} mirror(row (M - k) + r M) omega^((R - 1 - r) q) )
+                cd a1 = mk(0.0, 0.0), a2 = mk(0.0, 0.0);
+#pragma unroll
+                for (int r = 0; r < R / 2; ++r) {
+                    const int r1 = k1 + r * M;
+                    chb_big_row(rows, r1, lm * chf_rcp((double)r1), &Z, &Zm, &kin);
+                    a1 = chb_cfma(a1, Z, om[r]);
+                    if (k2 != k1) {
+                        a2 = chb_cfma(a2, Zm, om[R - 1 - r]);
+                        const int r2 = k2 + r * M;
+                        chb_big_row(rows, r2, lm * chf_rcp((double)r2), &Z, &Zm, &kin);
+                        a2 = chb_cfma(a2, Z, om[r]);
+                    }
+                    a1 = chb_cfma(a1, Zm, om[R - 1 - r]);
+                }
+                if (q) a1 = cmul(a1, cconj(chb_big_root(L, q * k1)));
+                buf[chf_swz(h.rev[k1], h.swm)] = a1;
                 if (k2 != k1) {
-                    chb_big_row(rows, k2, lm * chf_rcp((double)k2), &Z2, &Zm2, &kin);
-                } else {
-                    Z2 = Z1;
-                    Zm2 = Zm1;
+                    if (q) a2 = cmul(a2, cconj(chb_big_root(L, q * k2)));
+                    buf[chf_swz(h.rev[k2], h.swm)] = a2;
                 }
-                // Z[k + Nh] = mirror of row Nh - k
-                cd A1 = mk(Z1.x + sgn * Zm2.x, Z1.y + sgn * Zm2.y), A2 = mk(Z2.x + sgn * Zm1.x, Z2.y + sgn * Zm1.y);
-                if (par) {
-                    A1 = cmul(A1, cconj(chb_big_root(L, k1)));
-                    A2 = cmul(A2, cconj(chb_big_root(L, k2)));
-                }
-                buf[chf_swz(h.rev[k1], h.swm)] = A1;
-                if (k2 != k1) buf[chf_swz(h.rev[k2], h.swm)] = A2;
             }
             red[tid] = 0.5 * kin;
         });
@@ -86,10 +124,10 @@ CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbB
         if (segmpos_b) {
             grp.par([&](int tid, int T) {
                 const int size = F.segm_size;
-                for (int m = tid; m < Nh; m += T) {
-                    const int n = 2 * m + par;
-                    const int q = n / size, i = n - q * size;
-                    const int s = L.slot_seg[q];
+                for (int m = tid; m < M; m += T) {
+                    const int n = R * m + q;
+                    const int qs = n / size, i = n - qs * size;
+                    const int s = L.slot_seg[qs];
                     const ChbSeg &sg = S.segs[s];
                     const cd u = buf[chf_swz(m, h.swm)];
                     const cd v = sg.isid ? u : mk(u.x * sg.rot[0] + u.y * sg.rot[2], u.x * sg.rot[1] + u.y * sg.rot[3]);  // x @ R
@@ -99,7 +137,7 @@ CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbB
             });
         }
     });
-    if (kin_out && par == 0) {
+    if (kin_out && q == 0) {
         cta_reduce(ctx, red);
         ctx.par([&](int tid, int nthr) {
             (void)nthr;
@@ -108,57 +146,86 @@ CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbB
     }
 }
 
-// segment gradient -> result rows k = 2 k' + par of the loop (+ kin_src rows on k > 0: params_to_kin_nrg_grad_daxpy)
-template <class Ctx>
-CHB_D void cta_big_adj(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbBigLoop &L, int par, const double *seg_b,
+// segment gradient -> result rows of the loop (+ kin_src rows on k > 0: params_to_kin_nrg_grad_daxpy).  q = 0, R / 2: packed
+// transform, rows k = q (mod R), all four entries; other q: one coordinate of the rows k = +-rho (mod R), rho = min(q, R - q)
+template <int R, class Ctx>
+CHB_D void cta_big_adj(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbBigLoop &L, int q, const double *seg_b,
                         double *out_b, const double *kin_b, cd *buf, const cd *twsm) {
     const ChfLoop &h = L.h;
-    const int Nh = h.N;
-    const double sgn = par ? -1.0 : 1.0;
+    const int M = h.N, N = R * M;
+    const bool packed = (q == 0) || (2 * q == R);
+    const int rho = packed ? q : (q < R - q ? q : R - q);
+    const int dim = (2 * q > R) ? 1 : 0;  // coordinate of the unpacked CTAs
+    cd omc[R];  // omega^(-rho r)
+    for (int r = 0; r < R; ++r) omc[r] = cconj(chb_big_omega(R, r * rho));
     ctx.groups(1, F.T, [&](auto &grp) {
         grp.par([&](int tid, int T) {
             const int size = F.segm_size;
-            for (int n1 = tid; n1 < Nh; n1 += T) {
-                cd g[2];
-                for (int hh = 0; hh < 2; ++hh) {
-                    const int n = n1 + hh * Nh;
-                    const int q = n / size, i = n - q * size;
-                    const int s = L.slot_seg[q];
+            for (int n1 = tid; n1 < M; n1 += T) {
+                cd acc = mk(0.0, 0.0);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const int n = n1 + r * M;
+                    const int qs = n / size, i = n - qs * size;
+                    const int s = L.slot_seg[qs];
                     const ChbSeg &sg = S.segs[s];
                     const int ii = sg.timerev > 0 ? i : size - 1 - i;
                     const cd u = ((const cd *)seg_b)[(long long)s * size + ii];
-                    g[hh] = sg.isid ? u : mk(sg.rot[0] * u.x + sg.rot[1] * u.y, sg.rot[2] * u.x + sg.rot[3] * u.y);  // R . g
+                    const cd g = sg.isid ? u : mk(sg.rot[0] * u.x + sg.rot[1] * u.y, sg.rot[2] * u.x + sg.rot[3] * u.y);  // R . g
+                    if (packed) {
+                        acc = chb_cfma(acc, g, omc[r]);
+                    } else {
+                        const double gd = dim ? g.y : g.x;
+                        acc = mk(acc.x + gd * omc[r].x, acc.y + gd * omc[r].y);
+                    }
                 }
-                cd Bv = mk(g[0].x + sgn * g[1].x, g[0].y + sgn * g[1].y);
-                if (par) Bv = cmul(Bv, chb_big_root(L, n1));
-                buf[chf_swz(n1, h.swm)] = Bv;
+                if (rho) acc = cmul(acc, chb_big_root(L, rho * n1));
+                buf[chf_swz(n1, h.swm)] = acc;
             }
         });
         chf_fft_time_to_spec(grp, buf, h, false, twsm, 0);
         grp.par([&](int tid, int T) {
             const long long off = h.mom_off - h.nco_in;
             const double lm = h.loopmul / (double)h.ncm;
-            for (int kp = tid; 2 * kp + par < Nh; kp += T) {
-                const int k = 2 * kp + par;
-                const cd A = buf[chf_swz(h.rev[kp], h.swm)];
-                if (k == 0) {
-                    // f = 1, Y_0[0] = Re, the imaginary parts of the zero-frequency term get no gradient
-                    for (int c = 0; c < 4 - h.nco_in; ++c) out_b[h.mom_off + c] = 0.0;
-                    if (h.co0 >= 0) out_b[h.mom_off + h.co0] = A.x * h.loopmul;
-                    if (h.co2 >= 0) out_b[h.mom_off + h.co2] = A.y * h.loopmul;
-                    continue;
+            if (packed) {
+                for (int kp = tid; R * kp + q < N / 2; kp += T) {
+                    const int k = R * kp + q;
+                    const cd A = buf[chf_swz(h.rev[kp], h.swm)];
+                    if (k == 0) {
+                        // f = 1, Y_0[0] = Re, the imaginary parts of the zero-frequency term get no gradient
+                        for (int c = 0; c < 4 - h.nco_in; ++c) out_b[h.mom_off + c] = 0.0;
+                        if (h.co0 >= 0) out_b[h.mom_off + h.co0] = A.x * h.loopmul;
+                        if (h.co2 >= 0) out_b[h.mom_off + h.co2] = A.y * h.loopmul;
+                        continue;
+                    }
+                    const int kq = q ? M - 1 - kp : M - kp;  // Y[N - k] = Y'[kq]
+                    const cd Bm = buf[chf_swz(h.rev[kq], h.swm)];
+                    const double sc = lm * chf_rcp((double)k);
+                    // Y_0 = (A + conj(Bm)) / 2, Y_1 = (A - conj(Bm)) / (2i); the adjoint carries a factor 2 for k > 0
+                    double v[4] = {(A.x + Bm.x) * sc, (A.y - Bm.y) * sc, (A.y + Bm.y) * sc, (Bm.x - A.x) * sc};
+                    if (kin_b) {
+                        const double *p = kin_b + off + 4LL * k;
+                        v[0] += p[0]; v[1] += p[1]; v[2] += p[2]; v[3] += p[3];
+                    }
+                    double *o = out_b + off + 4LL * k;
+                    o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
                 }
-                const int kq = par ? Nh - 1 - kp : Nh - kp;  // Y[N - k] = Y'[kq]
-                const cd Bm = buf[chf_swz(h.rev[kq], h.swm)];
-                const double sc = lm * chf_rcp((double)k);
-                // Y_0 = (A + conj(Bm)) / 2, Y_1 = (A - conj(Bm)) / (2i); the adjoint carries a factor 2 for k > 0
-                double v[4] = {(A.x + Bm.x) * sc, (A.y - Bm.y) * sc, (A.y + Bm.y) * sc, (Bm.x - A.x) * sc};
-                if (kin_b) {
-                    const double *p = kin_b + off + 4LL * k;
-                    v[0] += p[0]; v[1] += p[1]; v[2] += p[2]; v[3] += p[3];
+            } else {
+                for (int kp = tid; kp < M; kp += T) {
+                    const int k = R * kp + rho;  // never 0 or N / 2
+                    const cd A = buf[chf_swz(h.rev[kp], h.swm)];
+                    const int row = k < N / 2 ? k : N - k;           // Y_d[N - k] = conj(Y_d[k]) for the real sequence of coordinate d
+                    const double im = k < N / 2 ? A.y : -A.y;
+                    const double sc = 2.0 * lm * chf_rcp((double)row);
+                    double v0 = A.x * sc, v1 = im * sc;
+                    const long long at = off + 4LL * row + 2 * dim;
+                    if (kin_b) {
+                        v0 += kin_b[at];
+                        v1 += kin_b[at + 1];
+                    }
+                    out_b[at] = v0;
+                    out_b[at + 1] = v1;
                 }
-                double *o = out_b + off + 4LL * k;
-                o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
             }
         });
     });

@@ -117,7 +117,8 @@ class NBodySystB200:
 
     @property
     def staged_kernels(self):
-        """(transform kind, pair kernel) of the staged path: (0 generic | 1 parity-split, 0 colour rounds | 1 dense | 2 tiled)."""
+        """(transform kind, pair kernel) of the staged path: (0 generic | sum of the available residue splits R of
+        ``chb_big.cuh``, e.g. 14 = 2 + 4 + 8; 0 colour rounds | 1 dense | 2 tiled)."""
         return self._q(L.Q_STAGED_TRANSFORM), self._q(L.Q_PAIR_KERNEL)
 
     def set_chunk(self, chunk: int) -> None:
@@ -129,6 +130,10 @@ class NBodySystB200:
         load/store phases (kept for A/B measurements)."""
         level = 4 if enable is True else int(enable)
         L.check(self._lib, self._lib.chb_plan_set_fused(self._plan, level))
+
+    def set_transform_split(self, split: int) -> None:
+        """0: residue split of the staged transforms chosen per launch (default); 2, 4, 8: that split whenever the level has it."""
+        L.check(self._lib, self._lib.chb_plan_set_split(self._plan, int(split)))
 
     # ------------------------------------------------------------------ plumbing
     def _check(self, arr, last_shape, what: str):

@@ -96,6 +96,10 @@ class _XP:
     def to_numpy(self, a):
         return a.detach().cpu().numpy() if self.torch else np.asarray(a)
 
+    def sync(self):
+        if self.torch and self.dev.type == "cuda":
+            self.t.cuda.synchronize(self.dev)
+
 
 @dataclass
 class NewtonResult:

@@ -14,6 +14,7 @@ duplicate search is ``group_duplicates`` / ``DuplicateStore`` below (hash + ``Te
 """
 from __future__ import annotations
 
+import time
 from dataclasses import dataclass
 from typing import Any, Callable, Dict, List, Optional, Sequence
 
@@ -71,7 +72,7 @@ def find_batched(make_nbs: Callable[[int], Any], x0, nint0: int, *, gradtol: flo
                  n_reconverge_it_max: int = 4, Newt_err_norm_max: float = 1e-10, Newt_err_norm_max_save: float = 1e-7,
                  mul_coarse_to_fine: float = 3.0, max_norm_on_entry: float = 1e20, linesearch_smin: float = 1e-2,
                  line_search: Optional[str] = "armijo", restart: int = 20, Check_Escape: bool = True,
-                 recenter: bool = True) -> RefineResult:
+                 recenter: bool = True, trace: Optional[list] = None) -> RefineResult:
     """``make_nbs(nint)`` returns the evaluator of one level (called once per level); ``x0`` ``[B, nparams(nint0)]`` NumPy
     array or torch CUDA tensor.  Keyword names and defaults follow the reference's ``Find_Choreo`` arguments.
 
@@ -82,7 +83,8 @@ def find_batched(make_nbs: Callable[[int], Any], x0, nint0: int, *, gradtol: flo
     exactly as the reference decides; states that share (refinement level, optimiser level) are solved together.
     ``krylov_method``: the reference wires ``inner_maxiter_list`` into the linear solver only for ``'lgmres'``
     (find.py:246-249); with ``'gmres'`` scipy's ``KrylovJacobian`` default restart (20, ``restart`` here) is used at every
-    level.  ``'lgmres'`` is not built on the device and is rejected."""
+    level.  ``'lgmres'`` is not built on the device and is rejected.  ``trace``: a list that receives one record per solved
+    (refinement level, optimiser level) group: states, nint, seconds (device-synchronised), Newton iterations."""
     if krylov_method != "gmres":
         raise ValueError(f"krylov_method {krylov_method!r}: the batched driver implements 'gmres' (scipy KrylovJacobian's default "
                          "for the reference's configurations); 'lgmres' is not built")
@@ -136,11 +138,19 @@ def find_batched(make_nbs: Callable[[int], Any], x0, nint0: int, *, gradtol: flo
         x = cat([p[1] for p in parts])
         nint = int(nint0) * 2 ** lvl
         nbs = nbs_at(nint)
+        if trace is not None:
+            xp.sync()
+            t_key = time.perf_counter()
         res = newton_krylov_batched(nbs, x, f_tol=gradtols[iopt], maxiter=maxiters[iopt], restart=restart, smin=linesearch_smin,
                                     line_search=line_search, tol_norm="l2", track_best=True)
         n_grad += res.n_grad_evals
         n_hess += res.n_hess_evals
         nit_tot[ids] += res.nit
+        if trace is not None:
+            xp.sync()
+            trace.append(dict(level=int(lvl), optim_level=int(iopt), nint=nint, states=int(ids.size), seconds=time.perf_counter() - t_key,
+                              nit_max=int(np.max(res.nit)), nit_sum=int(np.sum(res.nit)), grad_evals=int(res.n_grad_evals),
+                              hess_evals=int(res.n_hess_evals)))
         best_x = res.best_x
         fn = xp.to_numpy(res.best_fnorm)
         # the best iterate at twice the resolution (find.py:312-320)

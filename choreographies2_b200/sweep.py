@@ -12,6 +12,7 @@ torch.distributed is plumbing here; nothing in this module touches the numerics.
 from __future__ import annotations
 
 import os
+import threading
 from typing import Callable, Dict, Optional, Sequence, Tuple
 
 import numpy as np
@@ -50,6 +51,7 @@ class ChunkQueue:
         self.n, self.chunk, self.key = int(n), int(chunk), key
         self.nchunks = (self.n + self.chunk - 1) // self.chunk
         self._local = 0
+        self._lock = threading.Lock()  # several worker threads of one rank may share the queue
         self.store = None
         if world > 1:
             from torch.distributed import TCPStore
@@ -59,11 +61,12 @@ class ChunkQueue:
 
     def next(self) -> Optional[Tuple[int, int]]:
         """Claim the next unclaimed chunk: ``(lo, hi)`` seed bounds, or None when the queue is empty."""
-        if self.store is None:
-            c = self._local
-            self._local += 1
-        else:
-            c = int(self.store.add(self.key, 1)) - 1
+        with self._lock:
+            if self.store is None:
+                c = self._local
+                self._local += 1
+            else:
+                c = int(self.store.add(self.key, 1)) - 1
         if c >= self.nchunks:
             return None
         lo = c * self.chunk

@@ -149,6 +149,11 @@ int chb_plan_set_chunk(chb_plan *plan, int64_t chunk);
  * (A/B measurements).  Layouts versions 3 / 4 do not serve (GENERAL_SYM loops, segm_store = segm_size + 1, rotated or
  * time-reversed segments) run the general fused kernel (CHB_Q_FUSED reports 5) for any non-zero value. */
 int chb_plan_set_fused(chb_plan *plan, int enable);
+/* Staged transforms of planar RFFT systems (one CTA per (state, loop, residue of the time index modulo R), chb_big.cuh):
+ * 0 (default) = R chosen per launch from the number of states (the smallest split that fits when the batch fills the GPU, a
+ * larger one for the few live states at the end of a search); 2, 4, 8 = use that split whenever the level has it
+ * (CHB_Q_STAGED_TRANSFORM reports the sum of the available R, 0 = generic kernels).  A/B measurements and tests. */
+int chb_plan_set_split(chb_plan *plan, int split);
 
 /* bytes of device workspace any *_dev operator below needs for `batch` states */
 int chb_workspace_bytes(const chb_plan *plan, int64_t batch, size_t *bytes_out);

@@ -15,6 +15,7 @@ import argparse
 import json
 import os
 import sys
+import threading
 import time
 
 import numpy as np
@@ -57,6 +58,8 @@ def main():
     ap.add_argument("--cpu-seeds", type=int, default=0, help="seeds also run through the reference's loop on the host (rank 0)")
     ap.add_argument("--reconverge", type=int, default=4, help="n_reconverge_it_max of both arms (the 3C configuration has 4)")
     ap.add_argument("--duplicate-eps", type=float, default=1e-8, help="rtol of TestHashSame (Solver_Checks.duplicate_eps)")
+    ap.add_argument("--workers", type=int, default=1, help="chunks in flight per GPU (threads, one stream and one set of plans each)")
+    ap.add_argument("--trace", default=None, help="write one line per solved (refinement level, optimiser level) group of rank 0 to this file")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -68,25 +71,33 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", f"{a.system}.npz"))
-    plans = {}
+    W = max(1, a.workers)
+    plans = [dict() for _ in range(W)]  # one set of plans per worker: a plan serves one stream at a time
 
-    def make(nint):
-        if nint not in plans:
-            plans[nint] = NBodySystB200(T, nint, device=local)
-        return plans[nint]
+    def maker(w):
+        def make(nint):
+            if nint not in plans[w]:
+                plans[w][nint] = NBodySystB200(T, nint, device=local)
+            return plans[w][nint]
+        return make
 
+    make = maker(0)
     kw = dict(refine.SEARCH_CONFIG_3C)
     kw["n_reconverge_it_max"] = a.reconverge
     starts = lambda lo, hi: torch.from_numpy(refine.find_starts(T, a.nint, range(lo, hi), **refine.RANDOM_CONFIG_3C)).to(dev)  # noqa: E731
-    refine.find_batched(make, starts(0, 128), a.nint, **kw)  # warm-up: plans of the levels, workspaces
+    for w in range(W):
+        refine.find_batched(maker(w), starts(0, 128), a.nint, **kw)  # warm-up: plans of the levels, workspaces
+    if a.static and W > 1:
+        raise SystemExit("--static runs one worker per rank")
     queue = sweep.ChunkQueue(a.guesses, a.chunk, rank, world) if not a.static else None
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     rec = {"seed": [], "outcome": [], "level": [], "gradnorm": [], "action": [], "hash": [], "dup_of_seed": []}
-    nU1 = nU2 = nchunks = 0
-    t_starts = 0.0
+    count = {"U1": 0, "U2": 0, "chunks": 0, "starts_s": 0.0}
+    trace = [] if (a.trace and rank == 0) else None
+    lock = threading.Lock()
 
     def chunks():
         if queue is not None:
@@ -100,33 +111,66 @@ def main():
             for s0 in range(lo, hi, a.chunk):
                 yield s0, min(hi, s0 + a.chunk)
 
-    for lo, hi in chunks():
-        ts = time.perf_counter()
-        x0 = starts(lo, hi)
-        t_starts += time.perf_counter() - ts
-        res = refine.find_batched(make, x0, a.nint, **kw)
-        nU1 += res.n_grad_evals
-        nU2 += res.n_hess_evals
-        nchunks += 1
-        n = hi - lo
-        H = np.full((n, 9), np.nan)
-        act = np.full(n, np.nan)
-        saved = np.nonzero((res.outcome == refine.FOUND) | (res.outcome == refine.APPROX))[0]
-        for lvl in np.unique(res.level[saved]):  # one plan per refinement level
-            ids = saved[res.level[saved] == lvl]
-            nbs = make(a.nint * 2 ** int(lvl))
-            xs = torch.stack([res.params[int(i)] for i in ids])
-            seg = nbs.params_to_segmpos(xs)
-            H[ids] = nbs.segmpos_to_hash(seg).cpu().numpy()
-            act[ids] = nbs.params_to_action(xs).cpu().numpy()
-        dup = np.full(n, -1, dtype=np.int64)
-        if saved.size:  # duplicates inside the chunk (Check_Duplicates against the orbits found earlier in the chunk)
-            rep = refine.group_duplicates(make(a.nint), H[saved], a.duplicate_eps)
-            dup[saved] = lo + saved[rep]
-        rec["seed"].append(np.arange(lo, hi)); rec["outcome"].append(res.outcome); rec["level"].append(res.level)
-        rec["gradnorm"].append(res.f_norm); rec["action"].append(act); rec["hash"].append(H); rec["dup_of_seed"].append(dup)
+    def work(w):
+        mk = maker(w)
+        for lo, hi in chunks():
+            ts = time.perf_counter()
+            x0 = starts(lo, hi)
+            t_st = time.perf_counter() - ts
+            res = refine.find_batched(mk, x0, a.nint, trace=trace if w == 0 else None, **kw)
+            if trace is not None and w == 0:
+                trace.append(dict(chunk=[lo, hi], seconds_since_start=time.perf_counter() - t0))
+            n = hi - lo
+            H = np.full((n, 9), np.nan)
+            act = np.full(n, np.nan)
+            saved = np.nonzero((res.outcome == refine.FOUND) | (res.outcome == refine.APPROX))[0]
+            for lvl in np.unique(res.level[saved]):  # one plan per refinement level
+                ids = saved[res.level[saved] == lvl]
+                nbs = mk(a.nint * 2 ** int(lvl))
+                xs = torch.stack([res.params[int(i)] for i in ids])
+                seg = nbs.params_to_segmpos(xs)
+                H[ids] = nbs.segmpos_to_hash(seg).cpu().numpy()
+                act[ids] = nbs.params_to_action(xs).cpu().numpy()
+            dup = np.full(n, -1, dtype=np.int64)
+            if saved.size:  # duplicates inside the chunk (Check_Duplicates against the orbits found earlier in the chunk)
+                rep = refine.group_duplicates(mk(a.nint), H[saved], a.duplicate_eps)
+                dup[saved] = lo + saved[rep]
+            with lock:
+                count["U1"] += res.n_grad_evals
+                count["U2"] += res.n_hess_evals
+                count["chunks"] += 1
+                count["starts_s"] += t_st
+                rec["seed"].append(np.arange(lo, hi)); rec["outcome"].append(res.outcome); rec["level"].append(res.level)
+                rec["gradnorm"].append(res.f_norm); rec["action"].append(act); rec["hash"].append(H); rec["dup_of_seed"].append(dup)
+
+    if W == 1:
+        work(0)
+    else:  # several chunks in flight per GPU, one stream each: the few-state tails of one chunk run under the bulk of the others
+        errors = []
+
+        def run(w):
+            try:
+                torch.cuda.set_device(local)
+                with torch.cuda.stream(torch.cuda.Stream(device=dev)):
+                    work(w)
+                    torch.cuda.current_stream().synchronize()
+            except BaseException as e:  # noqa: BLE001
+                errors.append(e)
+
+        threads = [threading.Thread(target=run, args=(w,)) for w in range(W)]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        if errors:
+            raise errors[0]
+    nU1, nU2, nchunks, t_starts = count["U1"], count["U2"], count["chunks"], count["starts_s"]
     torch.cuda.synchronize()
     dt_local = time.perf_counter() - t0
+    if trace is not None:
+        with open(a.trace, "w") as fh:
+            for r in trace:
+                fh.write(json.dumps(r) + "\n")
     dt = dt_local
     if world > 1:
         t = torch.tensor([dt_local, float(nU1), float(nU2), float(nchunks)], dtype=torch.float64, device=dev)
@@ -155,7 +199,7 @@ def main():
                    "level": int(merged["level"][i])} for i in distinct]
         line = {
             "metric": "Newton orbit solves/hour (sharded search sweep with refinement, hash and duplicate filter)", "n_gpus": world,
-            "system": a.system, "nint0": a.nint, "n_reconverge_it_max": a.reconverge, "guesses": a.guesses, "chunk": a.chunk, "queue": "static split" if a.static else "dynamic (TCPStore counter)",
+            "system": a.system, "nint0": a.nint, "n_reconverge_it_max": a.reconverge, "guesses": a.guesses, "chunk": a.chunk, "workers_per_gpu": W, "queue": "static split" if a.static else "dynamic (TCPStore counter)",
             "seconds": dt, "solves_per_hour": a.guesses / dt * 3600, "balance": balance,
             "found": int((out == refine.FOUND).sum()), "approximate": int((out == refine.APPROX).sum()),
             "not_converged": int((out == refine.NOT_CONVERGED).sum()), "collision": int((out == refine.COLLISION).sum()),
