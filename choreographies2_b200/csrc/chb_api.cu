@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <string>
@@ -122,6 +123,8 @@ struct chb_plan {
     size_t big_smem[3] = {0, 0, 0};
     int big_ok[3] = {0, 0, 0};
     int big_min_len[3] = {0, 0, 0};  // shortest transform length of each split
+    const unsigned char *stage_skip = nullptr;  // set by the Newton driver around staged launches: byte mask of states to leave out
+    int64_t stage_c0 = 0;                       // first state of the chunk being launched (offset into stage_skip)
     int big_force_r = 0;    // CHB_BIG_R: A/B knob, use this split whenever it exists
     int fused5_active = 0;  // the level is served by the general fused kernel (chb_fused5.cuh) instead of versions 3 / 4
     Ch5Sys f5;              // passed by value (constant bank) to k_fused5
@@ -1743,6 +1746,7 @@ CHB_KERNEL void k_fwd(ChbSys S, const double *params, double *segmpos, cd *scrat
     const long long blk = CHB_BLOCK_ID;
     const int il = (int)(blk % S.nloop);
     const long long b = blk / S.nloop;
+    if (S.skip && S.skip[b]) return;
     const ChbLoop &L = S.loops[il];
     double *red = (double *)CHB_SMEM;
     cd *buf = ((smem_mask >> il) & 1ULL) ? (cd *)(CHB_SMEM + sizeof(double) * 1024)
@@ -1758,6 +1762,7 @@ CHB_KERNEL void k_adj(ChbSys S, const double *seg, double *out, const double *ki
     const long long blk = CHB_BLOCK_ID;
     const int il = (int)(blk % S.nloop);
     const long long b = blk / S.nloop;
+    if (S.skip && S.skip[b]) return;
     const ChbLoop &L = S.loops[il];
     cd *buf = ((smem_mask >> il) & 1ULL) ? (cd *)(CHB_SMEM + sizeof(double) * 1024)
                                          : scratch + b * S.scratch_per_state + L.scratch_off;
@@ -1771,6 +1776,7 @@ CHB_KERNEL void k_pair(ChbSys S, const double *seg, const double *dseg, double *
     const long long blk = CHB_BLOCK_ID;
     const int tile = (int)(blk % S.pair_ntiles);
     const long long b = blk / S.pair_ntiles;
+    if (S.skip && S.skip[b]) return;
     double *red = (double *)CHB_SMEM;
     const size_t arr = (size_t)S.nsegm * S.G * S.pair_tile;
     double *spos = red + 1024;
@@ -1787,6 +1793,7 @@ CHB_KERNEL void k_pair_dense(ChbSys S, const double *seg, const double *dseg, do
     const long long blk = CHB_BLOCK_ID;
     const int tile = (int)(blk % S.pair_ntiles);
     const long long b = blk / S.pair_ntiles;
+    if (S.skip && S.skip[b]) return;
     double *red = (double *)CHB_SMEM;
     double *sw = red + 1024;
     cd *spos = (cd *)(sw + (UNI ? (size_t)0 : (size_t)S.nsegm * S.pair_spad));
@@ -1807,6 +1814,7 @@ k_pair_tile(ChbSys S, const double *seg, const double *dseg, double *out, double
     const long long blk = CHB_BLOCK_ID;
     const int tile = (int)(blk % S.pair_ntiles);
     const long long b = blk / S.pair_ntiles;
+    if (S.skip && S.skip[b]) return;
     double *red = (double *)CHB_SMEM;
     const size_t arr = (size_t)S.tile_nblk * CHB_TILE_SB * 32 * S.tile_ngrp;
     cd *xs = (cd *)(red + 1024);
@@ -2012,6 +2020,7 @@ CHB_KERNEL void CHB_BIG_BOUNDS k_big_fwd(ChbBigSys F, ChbSys S, const double *pa
     const int q = (int)(blk % R);
     const int il = (int)((blk / R) % F.nloop);
     const long long b = (blk / R) / F.nloop;
+    if (S.skip && S.skip[b]) return;
     const ChbBigLoop &L = F.loops[il];
     double *red = (double *)CHB_SMEM;
     cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
@@ -2027,6 +2036,7 @@ CHB_KERNEL void CHB_BIG_BOUNDS k_big_adj(ChbBigSys F, ChbSys S, const double *se
     const int q = (int)(blk % R);
     const int il = (int)((blk / R) % F.nloop);
     const long long b = (blk / R) / F.nloop;
+    if (S.skip && S.skip[b]) return;
     const ChbBigLoop &L = F.loops[il];
     cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
     cd *tw = buf + L.h.N;
@@ -2035,10 +2045,24 @@ CHB_KERNEL void CHB_BIG_BOUNDS k_big_adj(ChbBigSys F, ChbSys S, const double *se
 }
 
 #ifndef CHB_HOSTSIM
+// Opt-in to large dynamic shared memory: once per launch site and device, to the device maximum minus the kernel's static shared
+// memory (a constant, so host threads that launch the same kernel with different sizes do not race on the attribute).
+template <class K>
+static cudaError_t chb_smem_opt_in(K kern, size_t limit) {
+    cudaFuncAttributes fa;
+    cudaError_t e = cudaFuncGetAttributes(&fa, kern);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)limit - (int)fa.sharedSizeBytes);
+}
 #define CHB_LAUNCH(p, kern, grid, block, smem, stream, ...)                                                  \
     do {                                                                                                     \
         if ((smem) > 32 * 1024) { /* static shared memory counts towards the 48 KB default limit too */    \
-            CHB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); \
+            static std::atomic<unsigned long long> opted_{0};                                                \
+            const unsigned long long bit_ = 1ULL << ((p)->device & 63);                                      \
+            if (!(opted_.load(std::memory_order_acquire) & bit_)) {                                          \
+                CHB_CUDA(chb_smem_opt_in(kern, (p)->smem_limit));                                            \
+                opted_.fetch_or(bit_, std::memory_order_release);                                            \
+            }                                                                                                \
         }                                                                                                    \
         kern<<<(unsigned)(grid), (unsigned)(block), (smem), (stream)>>>(__VA_ARGS__);                       \
         CHB_CUDA(cudaGetLastError());                                                                        \
@@ -2092,6 +2116,12 @@ static unsigned long long smem_mask(const chb_plan *p) {
     } while (0)
 #endif
 
+// the system descriptor of a staged launch: inside the Newton driver it carries the byte mask of the states to leave out
+static ChbSys stage_sys(const chb_plan *p, const ChbSys &S) {
+    ChbSys Sy = S;
+    Sy.skip = p->stage_skip ? p->stage_skip + p->stage_c0 : nullptr;
+    return Sy;
+}
 // which residue split serves a launch of nb states: the smallest that exists when the batch fills the GPU (least folding work),
 // a larger one while the CTAs would not (few live states at the end of a search: parallelism inside the state)
 static int big_pick(const chb_plan *p, int64_t nb) {
@@ -2112,30 +2142,32 @@ static int big_pick(const chb_plan *p, int64_t nb) {
 }
 static int launch_fwd(chb_plan *p, int64_t nb, const double *params, double *segmpos, Workspace &W, bool want_kin,
                       unsigned long long mask, chb_stream_t st) {
+    const ChbSys Sy = stage_sys(p, p->sys);
     if (p->big_active) {
         const int i = big_pick(p, nb);
         const ChbBigSys &F = p->bigsys[i];
         double *kp = want_kin ? W.kin_part : (double *)0;
-        if (i == 0) CHB_LAUNCH(p, k_big_fwd<2>, 2 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, params, segmpos, kp);
-        if (i == 1) CHB_LAUNCH(p, k_big_fwd<4>, 4 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, params, segmpos, kp);
-        if (i == 2) CHB_LAUNCH(p, k_big_fwd<8>, 8 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, params, segmpos, kp);
+        if (i == 0) CHB_LAUNCH(p, k_big_fwd<2>, 2 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, Sy, params, segmpos, kp);
+        if (i == 1) CHB_LAUNCH(p, k_big_fwd<4>, 4 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, Sy, params, segmpos, kp);
+        if (i == 2) CHB_LAUNCH(p, k_big_fwd<8>, 8 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, Sy, params, segmpos, kp);
         return CHB_OK;
     }
-    CHB_LAUNCH(p, k_fwd, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, p->sys, params, segmpos, W.scratch,
+    CHB_LAUNCH(p, k_fwd, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, Sy, params, segmpos, W.scratch,
                want_kin ? W.kin_part : (double *)0, mask);
     return CHB_OK;
 }
 static int launch_adj(chb_plan *p, int64_t nb, const double *seg, double *out, const double *kin_src, Workspace &W,
                       int mode, unsigned long long mask, chb_stream_t st) {
+    const ChbSys Sy = stage_sys(p, p->sys);
     if (p->big_active && mode == 0) {
         const int i = big_pick(p, nb);
         const ChbBigSys &F = p->bigsys[i];
-        if (i == 0) CHB_LAUNCH(p, k_big_adj<2>, 2 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, seg, out, kin_src);
-        if (i == 1) CHB_LAUNCH(p, k_big_adj<4>, 4 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, seg, out, kin_src);
-        if (i == 2) CHB_LAUNCH(p, k_big_adj<8>, 8 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, p->sys, seg, out, kin_src);
+        if (i == 0) CHB_LAUNCH(p, k_big_adj<2>, 2 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, Sy, seg, out, kin_src);
+        if (i == 1) CHB_LAUNCH(p, k_big_adj<4>, 4 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, Sy, seg, out, kin_src);
+        if (i == 2) CHB_LAUNCH(p, k_big_adj<8>, 8 * nb * p->sys.nloop, F.T, p->big_smem[i], st, F, Sy, seg, out, kin_src);
         return CHB_OK;
     }
-    CHB_LAUNCH(p, k_adj, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, p->sys, seg, out, kin_src, W.scratch, mode,
+    CHB_LAUNCH(p, k_adj, nb * p->sys.nloop, p->fft_threads, p->fft_smem, st, Sy, seg, out, kin_src, W.scratch, mode,
                mask);
     return CHB_OK;
 }
@@ -2146,8 +2178,9 @@ static int launch_pair(chb_plan *p, int mode, int64_t nb, const double *seg, con
     return launch_pair_sys(p, p->sys, mode, nb, seg, dseg, out, pot_part, globalmul, st);
 }
 // Sy: the plan's system, possibly with another interaction law (the hash sums of chb_segmpos_to_hash_dev)
-static int launch_pair_sys(chb_plan *p, const ChbSys &Sy, int mode, int64_t nb, const double *seg, const double *dseg,
+static int launch_pair_sys(chb_plan *p, const ChbSys &Sy_in, int mode, int64_t nb, const double *seg, const double *dseg,
                            double *out, double *pot_part, double globalmul, chb_stream_t st) {
+    const ChbSys Sy = stage_sys(p, Sy_in);
     const long long grid = nb * p->sys.pair_ntiles;
     // uniform-weight variants only for the plan's own law and weights (the hash sums reuse the same weights)
     const bool uni = p->sys.pair_uniform != 0;
@@ -2300,6 +2333,7 @@ extern "C" int chb_params_to_segmpos_dev(chb_plan *p, int64_t batch, const doubl
     CHB_SET_DEVICE();
     if (use_fused(p)) return launch_fused(p, 3, batch, chf_args(params, nullptr, nullptr, segmpos, nullptr, nullptr, 0), st);
     for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        p->stage_c0 = c0;
         int64_t nb = std::min(chunk, batch - c0);
         CHB_TRY(launch_fwd(p, nb, params + c0 * S.nparams, segmpos + c0 * S.segsz, W, false, mask, st));
     }
@@ -2415,9 +2449,14 @@ static int arnoldi_launch(chb_plan *p, const char *name, int64_t batch, int64_t 
         CHB_LAUNCH(p, k_arnoldi_reg<16>, batch, CHK_THREADS, 0, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
     else {
         const size_t smem = sizeof(double) * (size_t)n;
+        static const bool cluster_on = [] { const char *e = getenv("CHB_ARNOLDI_CLUSTER"); return !(e && atoi(e) == 0); }();  // A/B knob
+        const long long len = ((n + CHK_CL - 1) / CHK_CL + 1) & ~1LL;  // elements per CTA of a cluster (even: 16-byte slices)
         if (smem <= 200 * 1024)
             CHB_LAUNCH(p, k_arnoldi_smem<false>, batch, CHK_THREADS, smem, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
-        else  // rows longer than shared memory: candidate vector in its destination row
+        else if (cluster_on && sizeof(double) * (size_t)len <= 200 * 1024)  // candidate vector distributed over a cluster's shared memory
+            CHB_LAUNCH(p, k_arnoldi_cluster, batch * CHK_CL, CHK_THREADS, sizeof(double) * (size_t)len, st, (long long)batch, (long long)n, len, j,
+                       ldh, V, w, skip, h, G);
+        else  // longer still: candidate vector in its destination row
             CHB_LAUNCH(p, k_arnoldi_smem<true>, batch, CHK_THREADS, 0, st, (long long)batch, (long long)n, j, ldh, V, w, skip, h, G);
     }
 #else
@@ -2498,6 +2537,7 @@ extern "C" int chb_params_to_action_grad_dev(chb_plan *p, int64_t batch, const d
     if (use_fused(p))
         return launch_fused(p, 1, batch, chf_args(params, params, nullptr, segmpos_out, grad, action, action ? 1 : 0), st);
     for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        p->stage_c0 = c0;
         int64_t nb = std::min(chunk, batch - c0);
         double *seg = segmpos_out ? segmpos_out + c0 * S.segsz : W.segA;
         CHB_TRY(launch_fwd(p, nb, params + c0 * S.nparams, seg, W, action != nullptr, mask, st));
@@ -2577,7 +2617,13 @@ static int hess_common(chb_plan *p, int64_t batch, const double *segmpos, const 
         A.live_list = live_list; A.live_count = live_count;
         return launch_fused(p, 2, batch, A, st);
     }
-    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {  // staged kernels: the mask is not used, every state is computed
+    struct SkipGuard {  // staged kernels: CTAs of masked states return at once; the mask never outlives this call
+        chb_plan *pl;
+        ~SkipGuard() { pl->stage_skip = nullptr; pl->stage_c0 = 0; }
+    } guard{p};
+    p->stage_skip = skip;
+    for (int64_t c0 = 0; c0 < batch; c0 += chunk) {
+        p->stage_c0 = c0;
         int64_t nb = std::min(chunk, batch - c0);
         CHB_TRY(launch_fwd(p, nb, dparams + c0 * S.nparams, W.segB, W, false, mask, st));
         CHB_TRY(launch_pair(p, 2, nb, segmpos + c0 * S.segsz, W.segB, W.segC, nullptr, -1.0, st));
@@ -2758,17 +2804,19 @@ CHB_KERNEL void k_nk_finish(long long B, const double *ns, int32_t *status, int3
 // op 2: a += s_final * d, c = e  (accept: x, F)               rows with NK_LIVE
 // op 3: out = a                (best iterate)                 rows whose mask byte is 0
 CHB_KERNEL void k_nk_rows(long long n, int op, const double *ns, const unsigned char *mask, double *out, double *a, const double *d,
-                          double *c, const double *e) {
-    const long long b = CHB_BLOCK_ID;
+                          double *c, const double *e, int nchunk) {
+    const long long b = CHB_BLOCK_ID / nchunk;  // grid = states x nchunk: long rows are shared by several CTAs
+    const long long ck = CHB_BLOCK_ID % nchunk;
     const double *st = ns + b * NK_STRIDE;
     if ((op == 0 || op == 2) && st[NK_LIVE] == 0.0) return;
     if ((op == 1 || op == 3) && mask[b]) return;
     const double s = op == 0 ? 1.0 / st[NK_FNORM] : (op == 1 ? st[NK_S_EVAL] : st[NK_S_FINAL]);
     const size_t o = (size_t)b * n;
+    const long long per = (n + nchunk - 1) / nchunk, i0 = ck * per, i1 = i0 + per < n ? i0 + per : n;
 #ifndef CHB_HOSTSIM
-    for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+    for (long long i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
 #else
-    for (long long i = 0; i < n; ++i) {
+    for (long long i = i0; i < i1; ++i) {
 #endif
         if (op == 0) out[o + i] = a[o + i] * s;
         else if (op == 1) out[o + i] = fma(s, d[o + i], a[o + i]);
@@ -2837,7 +2885,11 @@ static int nk_grad(chb_plan *p, int64_t B, const double *x, double *grad, const 
         a.skip = mask;
         return launch_fused(p, 1, B, a, st);
     }
-    return chb_params_to_action_grad_dev(p, B, x, nullptr, grad, nullptr, A.opws, A.opws_bytes, (void *)st);
+    p->stage_skip = mask;
+    const int rc = chb_params_to_action_grad_dev(p, B, x, nullptr, grad, nullptr, A.opws, A.opws_bytes, (void *)st);
+    p->stage_skip = nullptr;
+    p->stage_c0 = 0;
+    return rc;
 }
 static int nk_segmpos(chb_plan *p, int64_t B, const double *x, double *seg, const unsigned char *mask, NkArrays &A, chb_stream_t st) {
     if (use_fused(p)) {
@@ -2845,7 +2897,11 @@ static int nk_segmpos(chb_plan *p, int64_t B, const double *x, double *seg, cons
         a.skip = mask;
         return launch_fused(p, 3, B, a, st);
     }
-    return chb_params_to_segmpos_dev(p, B, x, seg, A.opws, A.opws_bytes, (void *)st);
+    p->stage_skip = mask;
+    const int rc = chb_params_to_segmpos_dev(p, B, x, seg, A.opws, A.opws_bytes, (void *)st);
+    p->stage_skip = nullptr;
+    p->stage_c0 = 0;
+    return rc;
 }
 
 extern "C" int chb_newton_workspace_bytes(const chb_plan *p, int64_t batch, int restart, size_t *bytes) {
@@ -2894,10 +2950,11 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
     CHB_TRY(nk_grad(p, B, x, A.F, nullptr, A, st));
     n_u1 += B;
     CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, A.F, (const unsigned char *)nullptr, A.phi_t, A.fmax_t);
+    const int nkc = (int)std::max<int64_t>(1, std::min<int64_t>(64, n / 8192));  // CTAs per row of the element-wise row kernels
     CHB_LAUNCH(p, k_nk_init, gs, 128, 0, st, B, A.ns, A.phi_t, A.fmax_t);
     if (best_x) {
         CHB_TRY(nk_zero(A.mask, (size_t)B, st));
-        CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr);
+        CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr, nkc);
     }
     for (int it = 0; it < opts->maxiter; ++it) {
         CHB_TRY(nk_zero(A.counts, sizeof(int) * (size_t)(m + 8), st));
@@ -2908,7 +2965,7 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
         ++n_it;
         // jacobian.setup / update (:2013-2019): segment positions of the current iterate; first Krylov vector F / |F|
         CHB_TRY(nk_segmpos(p, B, x, A.seg, A.mask, A, st));
-        CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 0, A.ns, A.mask, A.V, A.F, (const double *)nullptr, (double *)nullptr, (const double *)nullptr);
+        CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 0, A.ns, A.mask, A.V, A.F, (const double *)nullptr, (double *)nullptr, (const double *)nullptr, nkc);
         // GMRES(m), one cycle, zero initial guess: per inner iteration one Hessian-vector launch over the running states and one
         // step launch (Arnoldi + Givens + stopping test + the list of the next iteration)
         for (int j = 0; j < m; ++j) {
@@ -2916,7 +2973,7 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
                 CHB_TRY(nk_read_counts(p, A.counts + j, 1, hc, st));
                 if (hc[0] == 0) break;
             }
-            CHB_TRY(hess_common(p, B, A.seg, A.V + (size_t)j * B * n, nullptr, A.lists + (size_t)(j & 1) * B, A.counts + j, A.w, A.opws,
+            CHB_TRY(hess_common(p, B, A.seg, A.V + (size_t)j * B * n, use_fused(p) ? nullptr : A.done, A.lists + (size_t)(j & 1) * B, A.counts + j, A.w, A.opws,
                                 A.opws_bytes, (void *)st));
             CHB_TRY(chb_gmres_step_dev(p, B, n, j, m, A.V, A.w, A.done, A.R, A.g, A.cs, A.target, (int64_t *)A.kdone,
                                        A.lists + (size_t)((j + 1) & 1) * B, A.counts + j + 1, (void *)st));
@@ -2939,7 +2996,7 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
             const int use_kind = hc[1] > 0 ? 2 : 1;  // probes first: a state alternates probe / stored evaluations
             double *Fout = use_kind == 1 ? A.Ft : A.Fd;
             CHB_LAUNCH(p, k_nk_mask, gs, 128, 0, st, B, A.ns, use_kind, A.mask);
-            CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 1, A.ns, A.mask, A.xt, x, (const double *)A.dx, (double *)nullptr, (const double *)nullptr);
+            CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 1, A.ns, A.mask, A.xt, x, (const double *)A.dx, (double *)nullptr, (const double *)nullptr, nkc);
             CHB_TRY(nk_grad(p, B, A.xt, Fout, A.mask, A, st));
             n_u1 += use_kind == 1 ? hc[0] : hc[1];
             CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, (const double *)Fout, (const unsigned char *)A.mask, A.phi_t, A.fmax_t);
@@ -2948,10 +3005,10 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
             CHB_TRY(nk_read_counts(p, A.counts + m + 2, 2, hc, st));
         }
         // accept: x += s dx, F = F(x + s dx) (the stored evaluation), forcing terms, best iterate
-        CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 2, A.ns, A.mask, (double *)nullptr, x, (const double *)A.dx, A.F, (const double *)A.Ft);
+        CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 2, A.ns, A.mask, (double *)nullptr, x, (const double *)A.dx, A.F, (const double *)A.Ft, nkc);
         CHB_LAUNCH(p, k_nk_end, gs, 128, 0, st, B, A.ns, O, A.mask);
         if (best_x)
-            CHB_LAUNCH(p, k_nk_rows, B, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr);
+            CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr, nkc);
     }
     CHB_LAUNCH(p, k_nk_finish, gs, 128, 0, st, B, A.ns, status, nit, fnorm_max, fnorm_2, best_fnorm);
     {
@@ -2998,7 +3055,8 @@ extern "C" int chb_gmres_solution_dev(chb_plan *p, int64_t batch, int64_t n, int
     CHB_SET_DEVICE();
     chb_stream_t st = (chb_stream_t)stream;
 #ifndef CHB_HOSTSIM
-    CHB_LAUNCH(p, k_gmres_solution, batch, 256, 0, st, (long long)batch, (long long)n, m, V, R, g, (const long long *)kdone, scale, sol);
+    const int nchunk = (int)std::max<int64_t>(1, std::min<int64_t>(64, n / 8192));  // long rows: several CTAs per state
+    CHB_LAUNCH(p, k_gmres_solution, batch * nchunk, 256, 0, st, (long long)batch, (long long)n, m, V, R, g, (const long long *)kdone, scale, sol, nchunk);
 #else
     (void)st;
     chk_solution_host(batch, n, m, V, R, g, (const long long *)kdone, scale, sol);

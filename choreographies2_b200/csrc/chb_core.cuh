@@ -121,6 +121,7 @@ struct ChbSys {
     double pair_wu;
     int pair_tilek, tile_nblk, tile_ngrp;  // cta_pair_tile serves the level: segment blocks of 8, groups of 32 samples per CTA
     long long scratch_per_state;  // cd slots
+    const unsigned char *skip;    // staged kernels inside the Newton driver: states whose byte is non-zero are left out (NULL: all run)
 };
 
 // ------------------------------------------------------------------------------------------------

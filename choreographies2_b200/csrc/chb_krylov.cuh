@@ -9,6 +9,9 @@
 // shared memory; modified Gram-Schmidt: the dot product with v_i uses the vector already purged of v_0..v_(i-1)).
 // Algorithmic bytes per state and step: 8 n (j + 3)  [v_0..v_j and w read, v_(j+1) written].
 #pragma once
+#ifndef CHB_HOSTSIM
+#include <cooperative_groups.h>
+#endif
 #include <cmath>
 #include <cstdint>
 
@@ -513,18 +516,110 @@ k_arnoldi_smem(long long rows, long long n, int j, int ldh, double *V, const dou
     }
 }
 
+// Rows longer than one CTA's shared memory (the deep refinement levels of a search: 3C at nint 49152 has n = 98302) and few states:
+// a thread-block CLUSTER of CHK_CL CTAs per state.  The candidate vector is distributed over the cluster's shared memory (CTA r
+// holds the elements [r len, (r + 1) len)), every CTA streams its slice of the basis rows, and the inner products are completed
+// through distributed shared memory: each CTA writes its partial sum into slot r of every CTA of the cluster, one cluster barrier,
+// then all add the CHK_CL partial sums in the same order (deterministic, identical on every CTA).  Same modified Gram-Schmidt
+// recurrence as k_arnoldi_smem.
+#define CHK_CL 8
+__device__ __forceinline__ double chk_cluster_sum(double v, double (*sred)[CHK_THREADS / 32], int &ph, double (*cpart)[CHK_CL], int &cph,
+                                                  cooperative_groups::cluster_group &cl, unsigned rank) {
+    const double s = chk_block_sum(v, sred, ph);
+    if (threadIdx.x < CHK_CL) *cl.map_shared_rank(&cpart[cph][rank], threadIdx.x) = s;
+    cl.sync();
+    double t = 0.0;
+#pragma unroll
+    for (int r = 0; r < CHK_CL; ++r) t += cpart[cph][r];
+    cph ^= 1;  // the buffer of two sums ago is free: every CTA of the cluster passed a cluster barrier after reading it
+    return t;
+}
+__global__ void __cluster_dims__(CHK_CL, 1, 1) __launch_bounds__(CHK_THREADS, 1)
+k_arnoldi_cluster(long long rows, long long n, long long len, int j, int ldh, double *V, const double *w, const unsigned char *skip,
+                  double *h, ChkGivens G) {
+    extern __shared__ double chk_acc[];
+    __shared__ double sred[2][CHK_THREADS / 32];
+    __shared__ double cpart[2][CHK_CL];
+    __shared__ double sh[64];
+    cooperative_groups::cluster_group cl = cooperative_groups::this_cluster();
+    const unsigned rank = cl.block_rank();
+    const long long a = blockIdx.x / CHK_CL;
+    const int tid = threadIdx.x;
+    const size_t vs = (size_t)rows * (size_t)n;
+    const long long lo = (long long)rank * len;
+    const long long cnt = lo < n ? (n - lo < len ? n - lo : len) : 0;  // elements of this CTA
+    double *vout = V + (size_t)(j + 1) * vs + (size_t)a * n + lo;
+    if (skip && skip[a]) {  // the whole cluster leaves together
+        if (!G.R)
+            for (long long e = tid; e < cnt; e += CHK_THREADS) vout[e] = 0.0;
+        if (rank == 0 && h && tid <= j + 1) h[(size_t)a * ldh + tid] = 0.0;
+        return;
+    }
+    if (tid < 64) sh[tid] = 0.0;
+    int ph = 0, cph = 0;
+    const double *vj = V + (size_t)j * vs + (size_t)a * n + lo;
+    const double *wr = w + (size_t)a * n + lo;
+    double part = 0.0;
+#pragma unroll 4
+    for (long long e = tid; e < cnt; e += CHK_THREADS) {
+        const double d = wr[e] - vj[e];
+        chk_acc[e] = d;
+        part = fma(d, d, part);
+    }
+    const double n0 = sqrt(chk_cluster_sum(part, sred, ph, cpart, cph, cl, rank));
+    double hn = 0.0;
+    for (int pass = 0; pass < 2; ++pass) {
+        for (int t = 0; t <= j; ++t) {
+            const int i = t == 0 ? j : t - 1;
+            const double *vr = V + (size_t)i * vs + (size_t)a * n + lo;
+            part = 0.0;
+#pragma unroll 8
+            for (long long e = tid; e < cnt; e += CHK_THREADS) part = fma(vr[e], chk_acc[e], part);
+            const double hi = chk_cluster_sum(part, sred, ph, cpart, cph, cl, rank);
+#pragma unroll 8
+            for (long long e = tid; e < cnt; e += CHK_THREADS) chk_acc[e] = fma(-hi, vr[e], chk_acc[e]);
+            if (tid == 0) sh[i] += hi;
+        }
+        part = 0.0;
+#pragma unroll 4
+        for (long long e = tid; e < cnt; e += CHK_THREADS) part = fma(chk_acc[e], chk_acc[e], part);
+        hn = sqrt(chk_cluster_sum(part, sred, ph, cpart, cph, cl, rank));
+        if (pass == 0 && hn < 0.1 * n0) continue;
+        break;
+    }
+    const double inv = hn > 0.0 ? 1.0 / hn : 1.0;
+    for (long long e = tid; e < cnt; e += CHK_THREADS) vout[e] = chk_acc[e] * inv;
+    if (rank == 0 && tid == 0) {
+        sh[j] += 1.0;
+        sh[j + 1] = hn;
+        if (h)
+            for (int i = 0; i <= j + 1; ++i) h[(size_t)a * ldh + i] = sh[i];
+        if (G.R) {
+            if (G.split) {
+                double *Rc = G.R + (size_t)a * (G.m + 1) * G.m + j;
+                for (int i = 0; i <= j + 1; ++i) Rc[(size_t)i * G.m] = sh[i];
+            } else {
+                chk_givens_update(G, a, j, sh);
+            }
+        }
+    }
+}
+
+// solution of the least-squares problem: grid = rows x nchunk CTAs, every CTA repeats the (tiny) back substitution of its row
 __global__ void __launch_bounds__(256)
 k_gmres_solution(long long rows, long long n, int m, const double *V, const double *R, const double *g, const long long *kdone,
-                 double scale, double *sol) {
+                 double scale, double *sol, int nchunk) {
     __shared__ double y[64];
-    const long long a = blockIdx.x;
+    const long long a = blockIdx.x / nchunk;
+    const int c = (int)(blockIdx.x % nchunk);
     int k = (int)kdone[a];
     k = k < 0 ? 0 : (k > m ? m : k);
     if (threadIdx.x == 0) chk_back_subst(R + (size_t)a * (m + 1) * m, g + (size_t)a * (m + 1), m, k, y);
     __syncthreads();
     const size_t vs = (size_t)rows * (size_t)n;
     const double *va = V + (size_t)a * n;
-    for (long long e = threadIdx.x; e < n; e += 256) {
+    const long long per = (n + nchunk - 1) / nchunk, e0 = c * per, e1 = e0 + per < n ? e0 + per : n;
+    for (long long e = e0 + threadIdx.x; e < e1; e += 256) {
         double s = 0.0;
 #pragma unroll 4
         for (int j = 0; j < k; ++j) s = fma(y[j], va[(size_t)j * vs + e], s);

@@ -41,6 +41,8 @@ def _case(A, n, j, m, seed, with_skip, noise=1e-2):
     # (noise 1e-4: what is left after the first Gram-Schmidt pass is < 0.1 of the vector -> the second pass runs)
     w = V[j] + noise * rng.standard_normal((A, n)) + 0.3 * V[0]
     skip = (rng.random(A) < 0.3) if with_skip else None
+    if skip is not None:
+        skip[0] = False  # at least one running state
     return V, w, skip
 
 
@@ -92,6 +94,20 @@ def test_arnoldi_step_gpu(n, j, with_skip):
            7, n, j, 20, 5 + n, with_skip)
     _check(nbs, lambda a: torch.as_tensor(np.ascontiguousarray(a), device=dev), lambda t: t.cpu().numpy(),
            150, n, j, 20, 6 + n, with_skip, noise=1e-4)  # second Gram-Schmidt pass, more states than SMs
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,j,with_skip", [(25601, 3, True), (30001, 6, False), (98302, 5, True), (204801, 2, False)])
+def test_arnoldi_step_gpu_long_rows(n, j, with_skip):
+    """Rows longer than one CTA's shared memory: the candidate vector distributed over a cluster of 8 CTAs (inner products through
+    distributed shared memory), and beyond the cluster's capacity the global-memory variant."""
+    import torch
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nbs = NBodySystB200(T, 96)
+    dev = torch.device("cuda:0")
+    to_dev, from_dev = (lambda a: torch.as_tensor(np.ascontiguousarray(a), device=dev)), (lambda t: t.cpu().numpy())
+    _check(nbs, to_dev, from_dev, 5, n, j, 8, 5 + n, with_skip)
+    _check(nbs, to_dev, from_dev, 3, n, j, 8, 6 + n, with_skip, noise=1e-4)  # second Gram-Schmidt pass
 
 
 def _masked_case(nbs, B, seed, forced):

@@ -195,3 +195,38 @@ def test_line_search_argument_is_validated(sim):
         nbs.newton_krylov(xs[None, :].copy(), 1e-9, 5, line_search="strong")
     res = newton_krylov_batched(nbs, xs[None, :] + 1e-3, f_tol=1e-11, maxiter=30, line_search="wolfe", smin=0.1, tol_norm="l2")
     assert res.status[0] == 1
+
+
+@pytest.mark.parametrize("split", [0, 8])
+def test_library_driver_staged_path_equals_fused(split, backend):
+    """The library Newton driver on the staged kernels (residue-split transforms, CTAs of stopped states return at once: byte masks
+    of the driver) against the same solve on the fused kernel: same iteration counts, same iterates to rounding.  States stop at
+    different iterations, so the masks are exercised."""
+    import os
+    from conftest import ROOT, make_nbs
+    from choreographies2_b200 import PlanTables, refine
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nint = 768
+    x0 = refine.find_starts(T, nint, range(6), **refine.RANDOM_CONFIG_3C)
+    out = []
+    for fused in (True, False):
+        nbs = make_nbs(T, nint, backend)
+        nbs.set_fused(fused)
+        if not fused:
+            assert nbs.staged_kernels[0] & 8
+            nbs.set_transform_split(split)
+        if backend is None:
+            import torch
+            x = torch.from_numpy(x0).cuda()
+        else:
+            x = x0.copy()
+        r = nbs.newton_krylov(x, 1e-3, 12, 20, 0.1, "wolfe", "l2", True)
+        get = (lambda t: t.cpu().numpy()) if backend is None else (lambda t: np.asarray(t))
+        out.append((get(x), get(r["nit"]), get(r["status"]), get(r["best_x"])))
+    (xf, nf, sf, bf), (xs, ns, ss, bs) = out
+    assert len(set(nf.tolist())) > 1, "the starts should stop at different iterations"
+    assert np.array_equal(nf, ns) and np.array_equal(sf, ss)
+    # the wolfe search differentiates phi by a forward difference (step ~1e-8): rounding differences between the two kernel sets
+    # are amplified by every line search, as in test_library_driver_tracks_reference_iterations
+    assert np.abs(xf - xs).max() < 1e-3 * max(1.0, np.abs(xf).max())
+    assert np.abs(bf - bs).max() < 1e-3 * max(1.0, np.abs(bf).max())
