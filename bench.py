@@ -56,6 +56,8 @@ def parse_args():
     ap.add_argument("--stages", action="store_true", help="also time the staged operators separately")
     ap.add_argument("--no-newton", action="store_true", help="skip the Newton orbit solves/hour leg")
     ap.add_argument("--newton-batch", type=int, default=8192, help="random starts per GPU in the solves/hour leg")
+    ap.add_argument("--newton-workers", type=int, default=4, help="chunks of starts in flight per GPU in the solves/hour leg (threads, one stream each)")
+    ap.add_argument("--newton-chunk", type=int, default=1024, help="starts per chunk in the solves/hour leg")
     ap.add_argument("--newton-reps", type=int, default=5, help="timed repetitions of the solves/hour leg (median reported)")
     ap.add_argument("--newton-ref-seeds", type=int, default=0, help="seeds of the CPU arm of the solves/hour leg (0 = auto)")
     ap.add_argument("--no-configs", dest="configs", action="store_false", help="skip the extra BASELINE configurations")
@@ -363,45 +365,48 @@ def search_cpu_arm(nint0, nproc, seeds_per_proc):
 
 def newton_leg(args, rank, world, dev, barrier, max_over_ranks):
     import torch
-    from choreographies2_b200 import NBodySystB200, PlanTables
-    from choreographies2_b200 import refine
+    from choreographies2_b200 import PlanTables
+    from choreographies2_b200 import refine, sweep
     Tn = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
     nint0, Bn = 3072, int(args.newton_batch)
-    plans = {}
-
-    def make(nint):
-        if nint not in plans:
-            plans[nint] = NBodySystB200(Tn, nint, device=dev.index)
-        return plans[nint]
-
-    starts = refine.find_starts(Tn, nint0, range(rank * Bn, (rank + 1) * Bn), **refine.RANDOM_CONFIG_3C)
-    x0n = torch.from_numpy(starts).to(dev)
+    W, chunk = max(1, int(args.newton_workers)), max(1, int(args.newton_chunk))
     kw = dict(refine.SEARCH_CONFIG_3C)
     kw["n_reconverge_it_max"] = NEWTON_RECONVERGE
-    refine.find_batched(make, x0n[:min(Bn, 256)].clone(), nint0, **kw)  # warm-up: plans of the levels, workspaces, allocator
-    times, res = [], None
-    l0 = sum(p.kernel_launches for p in plans.values())
+    # warm-up: plans of the levels, workspaces, allocator (every worker thread has its own set of plans)
+    warm = sweep.run_search(Tn, nint0, 128 * W, device=dev.index, chunk=128, workers=W, config=kw, seed_offset=rank * Bn)
+    plans = warm["plans"]
+    nlaunch = lambda: sum(int(pl.kernel_launches) for d in plans for pl in d.values())  # noqa: E731
+    times, out_s = [], None
+    l0 = nlaunch()
     for _ in range(max(1, args.newton_reps)):
         barrier()
         t0 = time.perf_counter()
-        res = refine.find_batched(make, x0n, nint0, **kw)
+        out_s = sweep.run_search(Tn, nint0, Bn, device=dev.index, chunk=chunk, workers=W, config=kw, seed_offset=rank * Bn, plans=plans)
         torch.cuda.synchronize()
         times.append(max_over_ranks(time.perf_counter() - t0))
-    launches = (sum(p.kernel_launches for p in plans.values()) - l0) // max(1, args.newton_reps)
+    rec = out_s["records"]
+
+    class res:  # the fields the summary below reads
+        outcome, level = rec["outcome"], rec["level"]
+        n_grad_evals, n_hess_evals = out_s["U1"], out_s["U2"]
+    distinct = int(np.unique(rec["dup_of_seed"][rec["dup_of_seed"] >= 0]).size)
+    launches = (nlaunch() - l0) // max(1, args.newton_reps)
     ts = sorted(times)
     med = ts[len(ts) // 2]
     saved = int(((res.outcome == refine.FOUND) | (res.outcome == refine.APPROX)).sum())
     out = {"solves_per_hour": world * Bn / med * 3600.0, "saved_orbits_per_hour": world * saved / med * 3600.0,
            "seconds_median": med, "seconds_min": ts[0], "seconds_max": ts[-1], "repetitions": len(ts), "batch_per_gpu": Bn,
-           "system": "3C", "nint0": nint0, "nparams0": int(make(nint0).nparams),
+           "chunk": chunk, "chunks_in_flight_per_gpu": W,
+           "system": "3C", "nint0": nint0, "nparams0": int(plans[0][nint0].nparams),
            "settings": "find.py loop with the reference's 3C configuration: GMRES(20), wolfe line search smin 0.1, optimiser levels "
                        "gradtol 1e-1 .. 1e-11 (2-norm) with maxiter 100/1000/1000/1000/500/500, refinement x2 once (n_reconverge_it_max 1, see NEWTON_RECONVERGE), "
-                       "Newt_err_norm_max 1e-11 / 1e-8; starts x_avg + x_ptp U[0,1) from Make_params_bounds(0.1, 3, 50, 1e-16)",
+                       "Newt_err_norm_max 1e-11 / 1e-8; starts x_avg + x_ptp U[0,1) from Make_params_bounds(0.1, 3, 50, 1e-16); sweep.run_search: chunks of seeds "
+                       "through refine.find_batched, several chunks in flight (one stream each), saved orbits hashed and duplicate-filtered per chunk inside the timed region",
            "rank0": {"found": int((res.outcome == refine.FOUND).sum()), "approximate": int((res.outcome == refine.APPROX).sum()),
                      "not_converged": int((res.outcome == refine.NOT_CONVERGED).sum()), "collision": int((res.outcome == refine.COLLISION).sum()),
                      "escaped": int((res.outcome == refine.ESCAPED).sum()), "refined_at_least_once": int((res.level > 0).sum()),
                      "U1_evals": int(res.n_grad_evals), "U2_evals": int(res.n_hess_evals), "gpu_launches": int(launches),
-                     "newton_iterations_mean": float(res.newton_iterations.mean())},
+                     "chunk_representatives_after_duplicate_filter": distinct},
            "note": "a solve = one run of the search loop from one random start to termination (saved, abandoned, escaped ...)"}
     if rank == 0 and world == 1 and not args.no_cpu:
         n = args.newton_ref_seeds or 16

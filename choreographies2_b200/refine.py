@@ -39,8 +39,8 @@ def find_starts(tables, nint: int, seeds, coeff_ampl_o=0.1, k_infl=3, k_max=50, 
     x_avg, x_ptp = (x_min + x_min) / 2, x_max - x_min
     out = np.empty((len(seeds), x_min.shape[0]))
     for r, s in enumerate(seeds):
-        np.random.seed(int(s))
-        out[r] = x_avg + x_ptp * np.random.random(x_min.shape[0])
+        # the stream of np.random.seed(s); np.random.random(n), drawn from a private generator: safe from several threads
+        out[r] = x_avg + x_ptp * np.random.RandomState(int(s)).random_sample(x_min.shape[0])
     return out
 
 

@@ -184,3 +184,52 @@ def test_find_full_schedule_identical_orbits(backend):
             assert row["hash_same"] and row["hash_rel"] < 1e-9, row
             assert abs(row["action_ref"] - row["action_b200"]) < 1e-11 * abs(row["action_ref"]), row
     assert abs(rows[3]["action_b200"] - 10.4830237879556) < 1e-9
+
+
+def test_run_search_is_independent_of_chunks_and_workers(sim):
+    """sweep.run_search (the per-rank body of a search sweep): the records do not depend on the chunk size or on the number of
+    chunks in flight (worker threads, one set of plans each), and equal a direct refine.find_batched call on the same seeds."""
+    from choreographies2_b200 import sweep
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nint0, n = 96, 10
+    cfg = dict(refine.SEARCH_CONFIG_3C)
+    cfg["n_reconverge_it_max"] = 1
+    mk = lambda nint: NBodySystB200(T, nint, _lib_handle=sim)  # noqa: E731
+    a = sweep.run_search(T, nint0, n, device=None, chunk=n, workers=1, config=cfg, make_plan=mk)
+    b = sweep.run_search(T, nint0, n, device=None, chunk=3, workers=2, config=cfg, make_plan=mk)
+    ra, rb = a["records"], b["records"]
+    assert ra["seed"].tolist() == list(range(n)) == rb["seed"].tolist()
+    assert a["chunks"] == 1 and b["chunks"] == 4
+    assert np.array_equal(ra["outcome"], rb["outcome"]) and np.array_equal(ra["level"], rb["level"])
+    saved = (ra["outcome"] == refine.FOUND) | (ra["outcome"] == refine.APPROX)
+    assert saved.sum() >= n // 2
+    assert np.allclose(ra["action"][saved], rb["action"][saved], rtol=1e-12, atol=0)
+    assert np.allclose(ra["hash"][saved], rb["hash"][saved], rtol=1e-10, atol=0)
+    assert np.all(ra["dup_of_seed"][~saved] == -1) and np.all(ra["dup_of_seed"][saved] >= 0)
+    # the same seeds through find_batched directly
+    plans = {}
+    x0 = refine.find_starts(T, nint0, range(n), **refine.RANDOM_CONFIG_3C)
+    res = refine.find_batched(lambda nint: plans.setdefault(nint, mk(nint)), x0, nint0, **cfg)
+    assert np.array_equal(res.outcome, ra["outcome"]) and np.array_equal(res.level, ra["level"])
+    # a seed offset selects other seeds: run_search(offset 4, 3 guesses) == records 4..6
+    c = sweep.run_search(T, nint0, 3, device=None, chunk=2, workers=1, config=cfg, make_plan=mk, seed_offset=4)["records"]
+    assert c["seed"].tolist() == [4, 5, 6] and np.array_equal(c["outcome"], ra["outcome"][4:7])
+
+
+@pytest.mark.gpu
+def test_run_search_gpu_threads_do_not_change_results():
+    """Four chunks in flight on four CUDA streams (host threads, one set of plans each) against one chunk on one stream."""
+    from choreographies2_b200 import sweep
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    nint0, n = 768, 96
+    cfg = dict(refine.SEARCH_CONFIG_3C)
+    cfg["n_reconverge_it_max"] = 2
+    a = sweep.run_search(T, nint0, n, device=0, chunk=n, workers=1, config=cfg)
+    b = sweep.run_search(T, nint0, n, device=0, chunk=8, workers=4, config=cfg)
+    ra, rb = a["records"], b["records"]
+    assert ra["seed"].tolist() == list(range(n)) == rb["seed"].tolist() and b["chunks"] == 12
+    assert np.array_equal(ra["outcome"], rb["outcome"]) and np.array_equal(ra["level"], rb["level"])
+    saved = (ra["outcome"] == refine.FOUND) | (ra["outcome"] == refine.APPROX)
+    assert saved.sum() >= n // 2 and (ra["level"] > 0).any()
+    assert np.allclose(ra["action"][saved], rb["action"][saved], rtol=1e-12, atol=0)
+    assert np.allclose(ra["hash"][saved], rb["hash"][saved], rtol=1e-10, atol=0)

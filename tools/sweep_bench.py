@@ -15,7 +15,6 @@ import argparse
 import json
 import os
 import sys
-import threading
 import time
 
 import numpy as np
@@ -72,99 +71,31 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", f"{a.system}.npz"))
     W = max(1, a.workers)
-    plans = [dict() for _ in range(W)]  # one set of plans per worker: a plan serves one stream at a time
-
-    def maker(w):
-        def make(nint):
-            if nint not in plans[w]:
-                plans[w][nint] = NBodySystB200(T, nint, device=local)
-            return plans[w][nint]
-        return make
-
-    make = maker(0)
     kw = dict(refine.SEARCH_CONFIG_3C)
     kw["n_reconverge_it_max"] = a.reconverge
-    starts = lambda lo, hi: torch.from_numpy(refine.find_starts(T, a.nint, range(lo, hi), **refine.RANDOM_CONFIG_3C)).to(dev)  # noqa: E731
-    for w in range(W):
-        refine.find_batched(maker(w), starts(0, 128), a.nint, **kw)  # warm-up: plans of the levels, workspaces
-    if a.static and W > 1:
-        raise SystemExit("--static runs one worker per rank")
-    queue = sweep.ChunkQueue(a.guesses, a.chunk, rank, world) if not a.static else None
+    # warm-up: plans of the levels, workspaces (a private queue: the shared counter is for the timed sweep)
+    warm = sweep.run_search(T, a.nint, 128 * W, device=local, chunk=128, workers=W, config=kw, queue=sweep.ChunkQueue(128 * W, 128))
+    plans = warm["plans"]
+
+    def make(nint):  # plans of worker 0, for the merge on rank 0
+        if nint not in plans[0]:
+            plans[0][nint] = NBodySystB200(T, nint, device=local)
+        return plans[0][nint]
+
+    if a.static:
+        lo_s, hi_s = sweep.shard_bounds(a.guesses, rank, world)
+        queue, off, nmine = sweep.ChunkQueue(hi_s - lo_s, a.chunk), lo_s, hi_s - lo_s  # this rank's contiguous share, claimed locally
+    else:
+        queue, off, nmine = sweep.ChunkQueue(a.guesses, a.chunk, rank, world), 0, a.guesses
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    rec = {"seed": [], "outcome": [], "level": [], "gradnorm": [], "action": [], "hash": [], "dup_of_seed": []}
-    count = {"U1": 0, "U2": 0, "chunks": 0, "starts_s": 0.0}
     trace = [] if (a.trace and rank == 0) else None
-    lock = threading.Lock()
-
-    def chunks():
-        if queue is not None:
-            while True:
-                c = queue.next()
-                if c is None:
-                    return
-                yield c
-        else:
-            lo, hi = sweep.shard_bounds(a.guesses, rank, world)
-            for s0 in range(lo, hi, a.chunk):
-                yield s0, min(hi, s0 + a.chunk)
-
-    def work(w):
-        mk = maker(w)
-        for lo, hi in chunks():
-            ts = time.perf_counter()
-            x0 = starts(lo, hi)
-            t_st = time.perf_counter() - ts
-            res = refine.find_batched(mk, x0, a.nint, trace=trace if w == 0 else None, **kw)
-            if trace is not None and w == 0:
-                trace.append(dict(chunk=[lo, hi], seconds_since_start=time.perf_counter() - t0))
-            n = hi - lo
-            H = np.full((n, 9), np.nan)
-            act = np.full(n, np.nan)
-            saved = np.nonzero((res.outcome == refine.FOUND) | (res.outcome == refine.APPROX))[0]
-            for lvl in np.unique(res.level[saved]):  # one plan per refinement level
-                ids = saved[res.level[saved] == lvl]
-                nbs = mk(a.nint * 2 ** int(lvl))
-                xs = torch.stack([res.params[int(i)] for i in ids])
-                seg = nbs.params_to_segmpos(xs)
-                H[ids] = nbs.segmpos_to_hash(seg).cpu().numpy()
-                act[ids] = nbs.params_to_action(xs).cpu().numpy()
-            dup = np.full(n, -1, dtype=np.int64)
-            if saved.size:  # duplicates inside the chunk (Check_Duplicates against the orbits found earlier in the chunk)
-                rep = refine.group_duplicates(mk(a.nint), H[saved], a.duplicate_eps)
-                dup[saved] = lo + saved[rep]
-            with lock:
-                count["U1"] += res.n_grad_evals
-                count["U2"] += res.n_hess_evals
-                count["chunks"] += 1
-                count["starts_s"] += t_st
-                rec["seed"].append(np.arange(lo, hi)); rec["outcome"].append(res.outcome); rec["level"].append(res.level)
-                rec["gradnorm"].append(res.f_norm); rec["action"].append(act); rec["hash"].append(H); rec["dup_of_seed"].append(dup)
-
-    if W == 1:
-        work(0)
-    else:  # several chunks in flight per GPU, one stream each: the few-state tails of one chunk run under the bulk of the others
-        errors = []
-
-        def run(w):
-            try:
-                torch.cuda.set_device(local)
-                with torch.cuda.stream(torch.cuda.Stream(device=dev)):
-                    work(w)
-                    torch.cuda.current_stream().synchronize()
-            except BaseException as e:  # noqa: BLE001
-                errors.append(e)
-
-        threads = [threading.Thread(target=run, args=(w,)) for w in range(W)]
-        for th in threads:
-            th.start()
-        for th in threads:
-            th.join()
-        if errors:
-            raise errors[0]
-    nU1, nU2, nchunks, t_starts = count["U1"], count["U2"], count["chunks"], count["starts_s"]
+    t0 = time.perf_counter()
+    out_s = sweep.run_search(T, a.nint, nmine, device=local, chunk=a.chunk, workers=W, config=kw, queue=queue, seed_offset=off,
+                             duplicate_eps=a.duplicate_eps, trace=trace, plans=plans)
+    rec = out_s["records"]
+    nU1, nU2, nchunks, t_starts = out_s["U1"], out_s["U2"], out_s["chunks"], out_s["starts_seconds"]
     torch.cuda.synchronize()
     dt_local = time.perf_counter() - t0
     if trace is not None:
@@ -182,10 +113,8 @@ def main():
         balance = {"seconds_min_rank": float(tmin[0]), "seconds_max_rank": float(tmax[0]), "chunks_min": int(tmin[3]), "chunks_max": int(tmax[3])}
     else:
         balance = {"seconds_min_rank": dt, "seconds_max_rank": dt, "chunks_min": nchunks, "chunks_max": nchunks}
-    cat = lambda k, w: np.concatenate(rec[k]) if rec[k] else np.zeros((0,) + w)  # noqa: E731
-    local_rec = {"outcome": cat("outcome", ()), "level": cat("level", ()), "gradnorm": cat("gradnorm", ()), "action": cat("action", ()),
-                 "hash": cat("hash", (9,)), "dup_of_seed": cat("dup_of_seed", ())}
-    merged = sweep.gather_records(local_rec, cat("seed", ()).astype(np.int64))
+    local_rec = {k: rec[k] for k in ("outcome", "level", "gradnorm", "action", "hash", "dup_of_seed")}
+    merged = sweep.gather_records(local_rec, rec["seed"])
     if rank == 0:
         out = merged["outcome"]
         saved = np.nonzero((out == refine.FOUND) | (out == refine.APPROX))[0]
