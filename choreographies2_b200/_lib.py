@@ -88,6 +88,8 @@ SYMBOLS = {
     "chb_params_to_action_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _sz, _vp]),
     "chb_params_to_action_grad_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "chb_params_to_action_hess_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _sz, _vp]),
+    "chb_noalloc_scratch_bytes": (C.c_int, [C.POINTER(C.c_size_t)]),
+    "chb_params_to_action_hess_noalloc_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp]),
     "chb_segmpos_params_to_action_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _sz, _vp]),
     "chb_segmpos_params_to_action_grad_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "chb_segmpos_dparams_to_action_hess_dev": (C.c_int, _dev_op + [_vp, _vp, _vp, _vp, _sz, _vp]),

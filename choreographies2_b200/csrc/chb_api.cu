@@ -3501,3 +3501,67 @@ extern "C" int chb_run_host(chb_plan *p, int op, int64_t batch, const double *in
 #endif
     return rc;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Hessian-vector product without any allocation by the caller or the library (no counterpart in the reference):
+// the operator's scratch (segment positions of both arguments and of the result, partial sums)
+// lives in ONE file-scope device array per GPU that loads the library, CHB_NOALLOC_SCRATCH_BYTES long, held until exit.
+// Every call on a device shares it and finds the last call's contents there: nothing in it has to start at zero (every kernel of
+// the operator writes what the next one reads), and two calls that overlap on the GPU (different streams, different plans on one
+// device) race on it -- callers serialise them.
+// ------------------------------------------------------------------------------------------------
+#ifndef CHB_HOSTSIM
+static __device__ __align__(256) unsigned char chb_noalloc_scratch[CHB_NOALLOC_SCRATCH_BYTES];
+#else
+alignas(256) static unsigned char chb_noalloc_scratch[CHB_NOALLOC_SCRATCH_BYTES];
+#endif
+#define CHB_NOALLOC_MAX_DEVICES 64
+static void *g_noalloc_ptr[CHB_NOALLOC_MAX_DEVICES];  // device address of the array on each device (host code cannot use its name)
+static std::mutex g_noalloc_mutex;
+
+// set-up, once per device, with that device current: the device address of the scratch array
+static int noalloc_scratch_address(chb_plan *p, void **out) {
+    CHB_REQUIRE(p->device >= 0 && p->device < CHB_NOALLOC_MAX_DEVICES, CHB_ERR_UNSUPPORTED,
+                "chb_params_to_action_hess_noalloc_dev: device index beyond the per-device table");
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[p->device]) {
+#ifndef CHB_HOSTSIM
+        CHB_CUDA(cudaSetDevice(p->device));
+        void *ptr = nullptr;
+        CHB_CUDA(cudaGetSymbolAddress((void **)&ptr, chb_noalloc_scratch));
+        CHB_REQUIRE(ptr != nullptr, CHB_ERR_CUDA, "chb_params_to_action_hess_noalloc_dev: cudaGetSymbolAddress returned NULL");
+        g_noalloc_ptr[p->device] = ptr;
+#else
+        g_noalloc_ptr[p->device] = (void *)chb_noalloc_scratch;
+#endif
+    }
+    *out = g_noalloc_ptr[p->device];
+    return CHB_OK;
+}
+
+extern "C" int chb_noalloc_scratch_bytes(size_t *bytes_out) {
+    CHB_REQUIRE(bytes_out, CHB_ERR_INVALID_ARGUMENT, "chb_noalloc_scratch_bytes: NULL argument");
+    *bytes_out = (size_t)CHB_NOALLOC_SCRATCH_BYTES;
+    return CHB_OK;
+}
+
+extern "C" int chb_params_to_action_hess_noalloc_dev(chb_plan *p, int64_t batch, const double *params, const double *dparams,
+                                                     double *hess, void *stream) {
+    CHB_REQUIRE(p, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_action_hess_noalloc_dev: NULL plan");
+    CHB_REQUIRE(p->ready, CHB_ERR_NOT_READY, "chb_params_to_action_hess_noalloc_dev: call chb_plan_set_nint first");
+    CHB_REQUIRE(batch >= 0, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_action_hess_noalloc_dev: negative batch");
+    if (batch == 0) return CHB_OK;
+    CHB_REQUIRE(params && dparams && hess, CHB_ERR_INVALID_ARGUMENT, "chb_params_to_action_hess_noalloc_dev: NULL array");
+    // what chb_workspace_bytes asks the caller of the workspace variant for (the operator works in chunks of states: the need
+    // follows the chunk, chb_plan_set_chunk lowers it)
+    const size_t need = ws_bytes_for(p, plan_chunk(p, batch)) + 256;
+    if (need > (size_t)CHB_NOALLOC_SCRATCH_BYTES)
+        return chb_fail(CHB_ERR_WORKSPACE, "chb_params_to_action_hess_noalloc_dev: " + std::to_string(batch) + " states of this level need " +
+                                               std::to_string(need) + " bytes of scratch, the built-in array holds " +
+                                               std::to_string((size_t)CHB_NOALLOC_SCRATCH_BYTES) +
+                                               " (CHB_NOALLOC_SCRATCH_BYTES): lower the batch or chb_plan_set_chunk, or use "
+                                               "chb_params_to_action_hess_dev with a workspace of your own");
+    void *scratch = nullptr;
+    CHB_TRY(noalloc_scratch_address(p, &scratch));
+    return chb_params_to_action_hess_dev(p, batch, params, dparams, hess, scratch, (size_t)CHB_NOALLOC_SCRATCH_BYTES, stream);
+}

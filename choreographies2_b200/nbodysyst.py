@@ -880,6 +880,27 @@ class NBodySystB200:
         return self._host(L.OP_ACTION_HESS, params_mom_buf, (self.nparams,), dparams_mom_buf, (self.nparams,),
                           out0_shape=(self.nparams,))[0]
 
+    NOALLOC_SCRATCH_BYTES = 32 << 20  # CHB_NOALLOC_SCRATCH_BYTES of include/choreo_b200.h
+
+    def params_to_action_hess_noalloc(self, params_mom_buf, dparams_mom_buf, out) -> None:
+        """``out[...] = params_to_action_hess(params, dparams)`` for callers that cannot allocate device memory (CUDA graph capture,
+        serving loops): no counterpart in the reference.  All three arguments are
+        contiguous float64 CUDA tensors of shape ``[batch, nparams]`` (or ``[nparams]``) on the plan's device; nothing is allocated
+        here or in the library (``chb_params_to_action_hess_noalloc_dev``: the scratch is a 32 MiB device array built into the
+        library, shared by every call on the device; a batch that needs more raises ``ChoreoB200Error`` CHB_ERR_WORKSPACE;
+        calls that overlap on the GPU race on it)."""
+        import torch
+        for name, t in (("params", params_mom_buf), ("dparams", dparams_mom_buf), ("out", out)):
+            if not (_is_torch(t) and t.is_cuda and t.dtype == torch.float64 and t.is_contiguous()):
+                raise ValueError(f"params_to_action_hess_noalloc: {name} must be a contiguous float64 CUDA tensor")
+            if t.shape[-1] != self.nparams or t.shape != params_mom_buf.shape:
+                raise ValueError(f"params_to_action_hess_noalloc: {name} has shape {tuple(t.shape)}, expected [batch, {self.nparams}]")
+        b = 1 if params_mom_buf.dim() == 1 else int(params_mom_buf.numel() // self.nparams)
+        stream = torch.cuda.current_stream(params_mom_buf.device).cuda_stream
+        L.check(self._lib, self._lib.chb_params_to_action_hess_noalloc_dev(
+            self._plan, b, C.c_void_p(params_mom_buf.data_ptr()), C.c_void_p(dparams_mom_buf.data_ptr()), C.c_void_p(out.data_ptr()),
+            C.c_void_p(stream)))
+
     def segmpos_params_to_action(self, segmpos, params_mom_buf):
         """_NBodySyst.pyx:2968-2991."""
         if _is_torch(segmpos):

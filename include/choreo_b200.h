@@ -227,6 +227,19 @@ int chb_params_to_action_grad_dev(chb_plan *plan, int64_t batch, const double *p
 /* params_to_action_hess, :2876-2965 */
 int chb_params_to_action_hess_dev(chb_plan *plan, int64_t batch, const double *params, const double *dparams,
                                   double *hess, void *workspace, size_t workspace_bytes, void *stream);
+/* No counterpart in the reference.  The same Hessian-vector product for callers that
+ * cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): no
+ * workspace argument, and neither this call nor anything it runs allocates or frees memory.  The operator's scratch is a device
+ * array built into the library, CHB_NOALLOC_SCRATCH_BYTES long (chb_noalloc_scratch_bytes reports it), that every GPU which loads
+ * the library holds until exit.  Limit: the call fails with CHB_ERR_WORKSPACE, before anything is launched, when the batch needs
+ * more than that (the need is what chb_workspace_bytes reports for the batch; chb_plan_set_chunk lowers it).  All calls on a
+ * device share the array and find the previous call's contents in it (nothing in it has to start at zero); calls that overlap on
+ * the GPU -- other streams, other plans on the same device -- race on it and must be serialised by the caller.  The first call
+ * on a device looks up the array's device address (cudaGetSymbolAddress): make it once before capturing a graph. */
+#define CHB_NOALLOC_SCRATCH_BYTES (32u << 20)
+int chb_noalloc_scratch_bytes(size_t *bytes_out);
+int chb_params_to_action_hess_noalloc_dev(chb_plan *plan, int64_t batch, const double *params, const double *dparams,
+                                          double *hess, void *stream);
 /* segmpos_params_to_action, :2968-2991 */
 int chb_segmpos_params_to_action_dev(chb_plan *plan, int64_t batch, const double *segmpos, const double *params,
                                      double *action, void *workspace, size_t workspace_bytes, void *stream);
