@@ -871,9 +871,13 @@ static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_si
     int Tg = ((maxNh / 16 + 31) / 32) * 32;
     Tg = std::max(64, std::min(Tg, big_t_cap));
     F.T = Tg;
+    int max_slots = 0;
+    for (int il = 0; il < T.nloop; ++il) max_slots = std::max(max_slots, (R * F.loops[il].h.N) / segm_size);
+    F.max_slots = max_slots;
+    const size_t slot_bytes = (size_t)max_slots * sizeof(ChbBigSlot);
     size_t tw_room = 0;
     {
-        const size_t base = CHF_RED_BYTES + (size_t)maxNh * sizeof(cd);
+        const size_t base = CHF_RED_BYTES + (size_t)maxNh * sizeof(cd) + slot_bytes;
         if (base + 1024 > p->smem_limit) return 0;
         tw_room = (p->smem_limit - base - 1024) / sizeof(cd);
     }
@@ -940,7 +944,7 @@ static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_si
         if (level_upload(p, thi, &BL.t_hi) || level_upload(p, tlo, &BL.t_lo)) return -1;
     }
     F.tw_smem_len = max_tw;
-    *smem = CHF_RED_BYTES + ((size_t)maxNh + max_tw) * sizeof(cd);
+    *smem = CHF_RED_BYTES + ((size_t)maxNh + max_tw) * sizeof(cd) + slot_bytes;
     return *smem <= p->smem_limit ? 1 : 0;
 }
 
@@ -1787,7 +1791,7 @@ CHB_KERNEL void k_pair(ChbSys S, const double *seg, const double *dseg, double *
                    globalmul, spos, sdpos, sout, red);
 }
 
-template <int MODE, bool UNI>
+template <int MODE, bool UNI, bool LAW0>
 CHB_KERNEL void k_pair_dense(ChbSys S, const double *seg, const double *dseg, double *out, double *pot_part, double globalmul) {
     CHB_CTX_DECL;
     const long long blk = CHB_BLOCK_ID;
@@ -1799,12 +1803,12 @@ CHB_KERNEL void k_pair_dense(ChbSys S, const double *seg, const double *dseg, do
     cd *spos = (cd *)(sw + (UNI ? (size_t)0 : (size_t)S.nsegm * S.pair_spad));
     cd *sout = spos + (size_t)S.pair_tile * S.pair_spad;
     cd *sdpos = sout + (size_t)S.pair_tile * S.pair_spad;
-    cta_pair_dense<MODE, UNI>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
+    cta_pair_dense<MODE, UNI, LAW0>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
                          out ? out + b * S.segsz : (double *)0, pot_part ? pot_part + b * S.pair_ntiles + tile : (double *)0, tile,
                          globalmul, CHB_NTHREADS, spos, sdpos, sout, sw, red);
 }
 
-template <int MODE, bool UNI>
+template <int MODE, bool UNI, bool LAW0>
 CHB_KERNEL void
 #ifndef CHB_HOSTSIM
 __launch_bounds__(256, 2)
@@ -1819,7 +1823,7 @@ k_pair_tile(ChbSys S, const double *seg, const double *dseg, double *out, double
     const size_t arr = (size_t)S.tile_nblk * CHB_TILE_SB * 32 * S.tile_ngrp;
     cd *xs = (cd *)(red + 1024);
     cd *accA = xs + arr, *accB = accA + arr, *dxs = accB + arr;
-    cta_pair_tile<MODE, UNI>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
+    cta_pair_tile<MODE, UNI, LAW0>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
                         out ? out + b * S.segsz : (double *)0, pot_part ? pot_part + b * S.pair_ntiles + tile : (double *)0, tile,
                         globalmul, S.tile_nblk, S.tile_ngrp, xs, dxs, accA, accB, red);
 }
@@ -2025,9 +2029,10 @@ CHB_KERNEL void CHB_BIG_BOUNDS k_big_fwd(ChbBigSys F, ChbSys S, const double *pa
     double *red = (double *)CHB_SMEM;
     cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
     cd *tw = buf + L.h.N;
-    cta_big_prologue(ctx, L.h, tw);
-    cta_big_fwd<R>(ctx, F, S, L, q, params + b * F.nparams, segmpos ? segmpos + b * F.segsz : (double *)0,
-                   kin_part ? kin_part + b * F.nloop + il : (double *)0, buf, tw, red);
+    ChbBigSlot *slots = (ChbBigSlot *)(tw + F.tw_smem_len);
+    cta_big_prologue(ctx, F, S, L, tw, slots);
+    cta_big_fwd<R>(ctx, F, L, q, params + b * F.nparams, segmpos ? segmpos + b * F.segsz : (double *)0,
+                   kin_part ? kin_part + b * F.nloop + il : (double *)0, buf, tw, slots, red);
 }
 template <int R>
 CHB_KERNEL void CHB_BIG_BOUNDS k_big_adj(ChbBigSys F, ChbSys S, const double *seg, double *out, const double *kin_src) {
@@ -2040,8 +2045,9 @@ CHB_KERNEL void CHB_BIG_BOUNDS k_big_adj(ChbBigSys F, ChbSys S, const double *se
     const ChbBigLoop &L = F.loops[il];
     cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
     cd *tw = buf + L.h.N;
-    cta_big_prologue(ctx, L.h, tw);
-    cta_big_adj<R>(ctx, F, S, L, q, seg + b * F.segsz, out + b * F.nparams, kin_src ? kin_src + b * F.nparams : (const double *)0, buf, tw);
+    ChbBigSlot *slots = (ChbBigSlot *)(tw + F.tw_smem_len);
+    cta_big_prologue(ctx, F, S, L, tw, slots);
+    cta_big_adj<R>(ctx, F, L, q, seg + b * F.segsz, out + b * F.nparams, kin_src ? kin_src + b * F.nparams : (const double *)0, buf, tw, slots);
 }
 
 #ifndef CHB_HOSTSIM
@@ -2184,21 +2190,26 @@ static int launch_pair_sys(chb_plan *p, const ChbSys &Sy_in, int mode, int64_t n
     const long long grid = nb * p->sys.pair_ntiles;
     // uniform-weight variants only for the plan's own law and weights (the hash sums reuse the same weights)
     const bool uni = p->sys.pair_uniform != 0;
+    const bool law0 = Sy.law_kind == 0;  // of THIS launch (the hash sums run other laws through the same kernels)
     if (p->sys.pair_tilek) {
         const bool tu = uni && (p->sys.nsegm % CHB_TILE_SB == 0);
-#define CHB_TILE_LAUNCH(M, U) CHB_LAUNCH(p, (k_pair_tile<M, U>), grid, p->tile_threads, p->tile_smem[M == 0 ? 0 : M], st, Sy, seg, dseg, out, pot_part, globalmul)
+#define CHB_TILE_LAUNCH2(M, U, W) CHB_LAUNCH(p, (k_pair_tile<M, U, W>), grid, p->tile_threads, p->tile_smem[M == 0 ? 0 : M], st, Sy, seg, dseg, out, pot_part, globalmul)
+#define CHB_TILE_LAUNCH(M, U) do { if (law0) CHB_TILE_LAUNCH2(M, U, true); else CHB_TILE_LAUNCH2(M, U, false); } while (0)
         if (mode == 0) { if (tu) CHB_TILE_LAUNCH(0, true); else CHB_TILE_LAUNCH(0, false); }
         else if (mode == 1) { if (tu) CHB_TILE_LAUNCH(1, true); else CHB_TILE_LAUNCH(1, false); }
         else { if (tu) CHB_TILE_LAUNCH(2, true); else CHB_TILE_LAUNCH(2, false); }
+#undef CHB_TILE_LAUNCH2
 #undef CHB_TILE_LAUNCH
         return CHB_OK;
     }
     if (p->sys.pair_dense) {
         const size_t wb = uni ? (size_t)p->sys.nsegm * p->sys.pair_spad * sizeof(double) : 0;  // no weight matrix in shared memory
-#define CHB_DENSE_LAUNCH(M, U, SM) CHB_LAUNCH(p, (k_pair_dense<M, U>), grid, p->dense_threads, (SM) - wb, st, Sy, seg, dseg, out, pot_part, globalmul)
+#define CHB_DENSE_LAUNCH2(M, U, W, SM) CHB_LAUNCH(p, (k_pair_dense<M, U, W>), grid, p->dense_threads, (SM) - wb, st, Sy, seg, dseg, out, pot_part, globalmul)
+#define CHB_DENSE_LAUNCH(M, U, SM) do { if (law0) CHB_DENSE_LAUNCH2(M, U, true, SM); else CHB_DENSE_LAUNCH2(M, U, false, SM); } while (0)
         if (mode == 0) { if (uni) CHB_DENSE_LAUNCH(0, true, p->dense_smem[1]); else CHB_DENSE_LAUNCH(0, false, p->dense_smem[1]); }
         else if (mode == 1) { if (uni) CHB_DENSE_LAUNCH(1, true, p->dense_smem[1]); else CHB_DENSE_LAUNCH(1, false, p->dense_smem[1]); }
         else { if (uni) CHB_DENSE_LAUNCH(2, true, p->dense_smem[2]); else CHB_DENSE_LAUNCH(2, false, p->dense_smem[2]); }
+#undef CHB_DENSE_LAUNCH2
 #undef CHB_DENSE_LAUNCH
         return CHB_OK;
     }

@@ -32,10 +32,14 @@ struct ChbBigLoop {
     const cd *t_hi, *t_lo;  // exp(-2 pi i 128 j / N), j <= N / 128;  exp(-2 pi i j / N), j < 128
     const int *slot_seg;    // [N / segm_size] generating segment stored in each slot of the slice
 };
+struct ChbBigSlot {         // one slot of a loop's slice, staged in shared memory by the prologue (the loops below then have no
+    int s, timerev, isid, pad;  // dependent global loads: slot -> segment -> flags / rotation)
+    double rot[4];
+};
 struct ChbBigSys {
     int nloop, T, segm_size, R;
     int tw_smem_len;        // cd slots of stage tables copied to shared memory (behind the buffer)
-    int pad;
+    int max_slots;          // ChbBigSlot entries behind the stage tables
     long long nparams, segsz;
     ChbBigLoop loops[CHB_BIG_MAX_LOOPS];
 };
@@ -66,12 +70,40 @@ CHB_HD cd chb_cfma(cd acc, cd a, cd b) {  // acc + a * b
     return mk(acc.x + (a.x * b.x - a.y * b.y), acc.y + (a.x * b.y + a.y * b.x));
 }
 
+// (quotient, remainder) of n / size kept incrementally: n advances by a fixed step whose quotient / remainder are dq / dr
+struct ChbDivStep {
+    int q, r;
+};
+CHB_HD void chb_div_advance(ChbDivStep &d, int dq, int dr, int size) {
+    d.q += dq;
+    d.r += dr;
+    if (d.r >= size) {
+        d.r -= size;
+        ++d.q;
+    }
+}
+
+// row (already in registers) -> Z[k] and its Hermitian mirror Z[N - k]
+CHB_HD void chb_big_row_regs(const double *p, double sc, cd *Z, cd *Zm, double *kin) {
+    *kin += (p[0] * p[0] + p[1] * p[1]) + (p[2] * p[2] + p[3] * p[3]);
+    *Z = mk((p[0] - p[3]) * sc, (p[1] + p[2]) * sc);
+    *Zm = mk((p[0] + p[3]) * sc, (p[2] - p[1]) * sc);
+}
+
+// The loops below have a handful of iterations per thread and one CTA per SM, so the latency of their global loads is what they
+// cost (profiles/r02_big_transforms_ncu_summary.md: half of all stall samples were long-scoreboard waits).  Each loop therefore
+// works in batches of CHB_BIG_U(R) independent iterations: all global loads of a batch are issued first, into registers, then
+// the arithmetic and the shared-memory traffic follow (written out by hand: buf and the global arrays are generic pointers, the
+// compiler may not move the loads of one iteration above the shared-memory stores of the previous one).
+#define CHB_BIG_U(R) ((R) == 2 ? 4 : ((R) == 4 ? 2 : 1))
+
 // params -> the samples n = R m + q of the loop's segments (+ kinetic energy of the loop from the CTA of residue 0)
 template <int R, class Ctx>
-CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbBigLoop &L, int q, const double *vec_b,
-                        double *segmpos_b, double *kin_out, cd *buf, const cd *twsm, double *red) {
+CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbBigLoop &L, int q, const double *vec_b, double *segmpos_b,
+                        double *kin_out, cd *buf, const cd *twsm, const ChbBigSlot *slots, double *red) {
     const ChfLoop &h = L.h;
     const int M = h.N;
+    constexpr int H = R / 2, U = CHB_BIG_U(R);
     cd om[R];  // omega^(r q)
     for (int r = 0; r < R; ++r) om[r] = chb_big_omega(R, r * q);
     ctx.groups(1, F.T, [&](auto &grp) {
@@ -79,43 +111,63 @@ CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbB
             double kin = 0.0;
             const double *rows = vec_b + h.mom_off - h.nco_in;
             const double lm = h.loopmul / (double)h.ncm;
-            for (int kk = tid; kk <= M / 2; kk += T) {
-                const int k1 = kk, k2 = M - kk;
-                cd Z, Zm;
-                if (kk == 0) {
-                    // Z[0] (zero frequency), Z[r M] for 0 < r < R / 2, the Nyquist term is zero, mirrors above it
-                    const double c0 = h.co0 >= 0 ? vec_b[h.mom_off + h.co0] : 0.0;
-                    const double c2 = h.co2 >= 0 ? vec_b[h.mom_off + h.co2] : 0.0;
-                    cd acc = mk(c0 * h.loopmul, c2 * h.loopmul);
+            if (tid == 0) {
+                // k = 0: Z[0] (zero frequency), Z[r M] for 0 < r < R / 2, the Nyquist term is zero, mirrors above it
+                const double c0 = h.co0 >= 0 ? vec_b[h.mom_off + h.co0] : 0.0;
+                const double c2 = h.co2 >= 0 ? vec_b[h.mom_off + h.co2] : 0.0;
+                cd acc = mk(c0 * h.loopmul, c2 * h.loopmul), Z, Zm;
 #pragma unroll
-                    for (int r = 1; r < R / 2; ++r) {
-                        chb_big_row(rows, r * M, lm * chf_rcp((double)(r * M)), &Z, &Zm, &kin);
-                        acc = chb_cfma(acc, Z, om[r]);
-                        acc = chb_cfma(acc, Zm, om[R - r]);
-                    }
-                    buf[chf_swz(h.rev[0], h.swm)] = acc;
-                    continue;
+                for (int r = 1; r < H; ++r) {
+                    chb_big_row(rows, r * M, lm * chf_rcp((double)(r * M)), &Z, &Zm, &kin);
+                    acc = chb_cfma(acc, Z, om[r]);
+                    acc = chb_cfma(acc, Zm, om[R - r]);
                 }
-                // A[k] = w^(k q) ( sum_{r < R/2} Z[k + r M] omega^(r q) + sum_{r < R/2} mirror(row (M - k) + r M) omega^((R - 1 - r) q) )
-                cd a1 = mk(0.0, 0.0), a2 = mk(0.0, 0.0);
+                buf[chf_swz(h.rev[0], h.swm)] = acc;
+            }
+            for (int kk0 = tid; kk0 <= M / 2; kk0 += U * T) {
+                double pr[U][2 * H][4];
+                int rv[U][2];
 #pragma unroll
-                for (int r = 0; r < R / 2; ++r) {
-                    const int r1 = k1 + r * M;
-                    chb_big_row(rows, r1, lm * chf_rcp((double)r1), &Z, &Zm, &kin);
-                    a1 = chb_cfma(a1, Z, om[r]);
+                for (int u = 0; u < U; ++u) {  // loads of the batch
+                    const int kk = kk0 + u * T;
+                    const bool on = kk >= 1 && kk <= M / 2;
+                    const int k1 = on ? kk : 1, k2 = on ? M - kk : 1;
+                    rv[u][0] = h.rev[k1];
+                    rv[u][1] = h.rev[k2];
+#pragma unroll
+                    for (int r = 0; r < H; ++r) {
+                        const double *p1 = rows + 4LL * (k1 + r * M), *p2 = rows + 4LL * (k2 + r * M);
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            pr[u][2 * r][c] = p1[c];
+                            pr[u][2 * r + 1][c] = p2[c];
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int kk = kk0 + u * T;
+                    if (kk < 1 || kk > M / 2) continue;
+                    const int k1 = kk, k2 = M - kk;
+                    // A[k] = w^(k q) ( sum_{r < R/2} Z[k + r M] omega^(r q) + sum_{r < R/2} mirror(row (M - k) + r M) omega^((R - 1 - r) q) )
+                    cd a1 = mk(0.0, 0.0), a2 = mk(0.0, 0.0), Z, Zm;
+#pragma unroll
+                    for (int r = 0; r < H; ++r) {
+                        chb_big_row_regs(pr[u][2 * r], lm * chf_rcp((double)(k1 + r * M)), &Z, &Zm, &kin);
+                        a1 = chb_cfma(a1, Z, om[r]);
+                        if (k2 != k1) {
+                            a2 = chb_cfma(a2, Zm, om[R - 1 - r]);
+                            chb_big_row_regs(pr[u][2 * r + 1], lm * chf_rcp((double)(k2 + r * M)), &Z, &Zm, &kin);
+                            a2 = chb_cfma(a2, Z, om[r]);
+                        }
+                        a1 = chb_cfma(a1, Zm, om[R - 1 - r]);
+                    }
+                    if (q) a1 = cmul(a1, cconj(chb_big_root(L, q * k1)));
+                    buf[chf_swz(rv[u][0], h.swm)] = a1;
                     if (k2 != k1) {
-                        a2 = chb_cfma(a2, Zm, om[R - 1 - r]);
-                        const int r2 = k2 + r * M;
-                        chb_big_row(rows, r2, lm * chf_rcp((double)r2), &Z, &Zm, &kin);
-                        a2 = chb_cfma(a2, Z, om[r]);
+                        if (q) a2 = cmul(a2, cconj(chb_big_root(L, q * k2)));
+                        buf[chf_swz(rv[u][1], h.swm)] = a2;
                     }
-                    a1 = chb_cfma(a1, Zm, om[R - 1 - r]);
-                }
-                if (q) a1 = cmul(a1, cconj(chb_big_root(L, q * k1)));
-                buf[chf_swz(h.rev[k1], h.swm)] = a1;
-                if (k2 != k1) {
-                    if (q) a2 = cmul(a2, cconj(chb_big_root(L, q * k2)));
-                    buf[chf_swz(h.rev[k2], h.swm)] = a2;
                 }
             }
             red[tid] = 0.5 * kin;
@@ -123,16 +175,17 @@ CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbB
         chf_fft_spec_to_time(grp, buf, h, false, twsm, 0);
         if (segmpos_b) {
             grp.par([&](int tid, int T) {
-                const int size = F.segm_size;
+                const int size = F.segm_size, step = R * T;
+                const int dq = step / size, dr = step - dq * size;
+                const int n0 = R * tid + q;
+                ChbDivStep d = {n0 / size, n0 % size};
                 for (int m = tid; m < M; m += T) {
-                    const int n = R * m + q;
-                    const int qs = n / size, i = n - qs * size;
-                    const int s = L.slot_seg[qs];
-                    const ChbSeg &sg = S.segs[s];
+                    const ChbBigSlot &sl = slots[d.q];
                     const cd u = buf[chf_swz(m, h.swm)];
-                    const cd v = sg.isid ? u : mk(u.x * sg.rot[0] + u.y * sg.rot[2], u.x * sg.rot[1] + u.y * sg.rot[3]);  // x @ R
-                    const int ii = sg.timerev > 0 ? i : size - 1 - i;
-                    ((cd *)segmpos_b)[(long long)s * size + ii] = v;
+                    const cd v = sl.isid ? u : mk(u.x * sl.rot[0] + u.y * sl.rot[2], u.x * sl.rot[1] + u.y * sl.rot[3]);  // x @ R
+                    const int ii = sl.timerev > 0 ? d.r : size - 1 - d.r;
+                    ((cd *)segmpos_b)[(long long)sl.s * size + ii] = v;
+                    chb_div_advance(d, dq, dr, size);
                 }
             });
         }
@@ -149,10 +202,11 @@ CHB_D void cta_big_fwd(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbB
 // segment gradient -> result rows of the loop (+ kin_src rows on k > 0: params_to_kin_nrg_grad_daxpy).  q = 0, R / 2: packed
 // transform, rows k = q (mod R), all four entries; other q: one coordinate of the rows k = +-rho (mod R), rho = min(q, R - q)
 template <int R, class Ctx>
-CHB_D void cta_big_adj(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbBigLoop &L, int q, const double *seg_b,
-                        double *out_b, const double *kin_b, cd *buf, const cd *twsm) {
+CHB_D void cta_big_adj(Ctx &ctx, const ChbBigSys &F, const ChbBigLoop &L, int q, const double *seg_b, double *out_b,
+                        const double *kin_b, cd *buf, const cd *twsm, const ChbBigSlot *slots) {
     const ChfLoop &h = L.h;
     const int M = h.N, N = R * M;
+    constexpr int U = CHB_BIG_U(R), UO = 4;
     const bool packed = (q == 0) || (2 * q == R);
     const int rho = packed ? q : (q < R - q ? q : R - q);
     const int dim = (2 * q > R) ? 1 : 0;  // coordinate of the unpacked CTAs
@@ -161,26 +215,46 @@ CHB_D void cta_big_adj(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbB
     ctx.groups(1, F.T, [&](auto &grp) {
         grp.par([&](int tid, int T) {
             const int size = F.segm_size;
-            for (int n1 = tid; n1 < M; n1 += T) {
-                cd acc = mk(0.0, 0.0);
+            const int Tq = T / size, Tr = T - Tq * size, Mq = M / size, Mr = M - Mq * size;
+            ChbDivStep d0 = {tid / size, tid % size};  // of n1, advanced by T per iteration
+            for (int n10 = tid; n10 < M; n10 += U * T) {
+                cd g[U][R];
+                int sq[U][R];
 #pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    const int n = n1 + r * M;
-                    const int qs = n / size, i = n - qs * size;
-                    const int s = L.slot_seg[qs];
-                    const ChbSeg &sg = S.segs[s];
-                    const int ii = sg.timerev > 0 ? i : size - 1 - i;
-                    const cd u = ((const cd *)seg_b)[(long long)s * size + ii];
-                    const cd g = sg.isid ? u : mk(sg.rot[0] * u.x + sg.rot[1] * u.y, sg.rot[2] * u.x + sg.rot[3] * u.y);  // R . g
-                    if (packed) {
-                        acc = chb_cfma(acc, g, omc[r]);
-                    } else {
-                        const double gd = dim ? g.y : g.x;
-                        acc = mk(acc.x + gd * omc[r].x, acc.y + gd * omc[r].y);
+                for (int u = 0; u < U; ++u) {  // loads of the batch
+                    const bool on = n10 + u * T < M;
+                    ChbDivStep d = d0;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {  // n = n1 + r M
+                        const int qs = on ? d.q : 0;
+                        const ChbBigSlot &sl = slots[qs];
+                        const int ii = sl.timerev > 0 ? d.r : size - 1 - d.r;
+                        sq[u][r] = qs;
+                        g[u][r] = ((const cd *)seg_b)[(long long)sl.s * size + (on ? ii : 0)];
+                        chb_div_advance(d, Mq, Mr, size);
                     }
+                    chb_div_advance(d0, Tq, Tr, size);
                 }
-                if (rho) acc = cmul(acc, chb_big_root(L, rho * n1));
-                buf[chf_swz(n1, h.swm)] = acc;
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int n1 = n10 + u * T;
+                    if (n1 >= M) continue;
+                    cd acc = mk(0.0, 0.0);
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const ChbBigSlot &sl = slots[sq[u][r]];
+                        const cd w = g[u][r];
+                        const cd gg = sl.isid ? w : mk(sl.rot[0] * w.x + sl.rot[1] * w.y, sl.rot[2] * w.x + sl.rot[3] * w.y);  // R . g
+                        if (packed) {
+                            acc = chb_cfma(acc, gg, omc[r]);
+                        } else {
+                            const double gd = dim ? gg.y : gg.x;
+                            acc = mk(acc.x + gd * omc[r].x, acc.y + gd * omc[r].y);
+                        }
+                    }
+                    if (rho) acc = cmul(acc, chb_big_root(L, rho * n1));
+                    buf[chf_swz(n1, h.swm)] = acc;
+                }
             }
         });
         chf_fft_time_to_spec(grp, buf, h, false, twsm, 0);
@@ -188,56 +262,95 @@ CHB_D void cta_big_adj(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbB
             const long long off = h.mom_off - h.nco_in;
             const double lm = h.loopmul / (double)h.ncm;
             if (packed) {
-                for (int kp = tid; R * kp + q < N / 2; kp += T) {
-                    const int k = R * kp + q;
-                    const cd A = buf[chf_swz(h.rev[kp], h.swm)];
-                    if (k == 0) {
-                        // f = 1, Y_0[0] = Re, the imaginary parts of the zero-frequency term get no gradient
-                        for (int c = 0; c < 4 - h.nco_in; ++c) out_b[h.mom_off + c] = 0.0;
-                        if (h.co0 >= 0) out_b[h.mom_off + h.co0] = A.x * h.loopmul;
-                        if (h.co2 >= 0) out_b[h.mom_off + h.co2] = A.y * h.loopmul;
-                        continue;
+                for (int kp0 = tid; R * kp0 + q < N / 2; kp0 += UO * T) {
+                    int ra[UO], rb[UO];
+                    double kn[UO][4];
+#pragma unroll
+                    for (int u = 0; u < UO; ++u) {  // loads of the batch
+                        const int kp = kp0 + u * T, k = R * kp + q;
+                        const bool on = k < N / 2, row = on && k > 0;
+                        ra[u] = h.rev[on ? kp : 0];
+                        rb[u] = h.rev[row ? (q ? M - 1 - kp : M - kp) : 0];  // Y[N - k] = Y'[kq]
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) kn[u][c] = (kin_b && row) ? kin_b[off + 4LL * k + c] : 0.0;
                     }
-                    const int kq = q ? M - 1 - kp : M - kp;  // Y[N - k] = Y'[kq]
-                    const cd Bm = buf[chf_swz(h.rev[kq], h.swm)];
-                    const double sc = lm * chf_rcp((double)k);
-                    // Y_0 = (A + conj(Bm)) / 2, Y_1 = (A - conj(Bm)) / (2i); the adjoint carries a factor 2 for k > 0
-                    double v[4] = {(A.x + Bm.x) * sc, (A.y - Bm.y) * sc, (A.y + Bm.y) * sc, (Bm.x - A.x) * sc};
-                    if (kin_b) {
-                        const double *p = kin_b + off + 4LL * k;
-                        v[0] += p[0]; v[1] += p[1]; v[2] += p[2]; v[3] += p[3];
+#pragma unroll
+                    for (int u = 0; u < UO; ++u) {
+                        const int kp = kp0 + u * T, k = R * kp + q;
+                        if (k >= N / 2) continue;
+                        const cd A = buf[chf_swz(ra[u], h.swm)];
+                        if (k == 0) {
+                            // f = 1, Y_0[0] = Re, the imaginary parts of the zero-frequency term get no gradient
+                            for (int c = 0; c < 4 - h.nco_in; ++c) out_b[h.mom_off + c] = 0.0;
+                            if (h.co0 >= 0) out_b[h.mom_off + h.co0] = A.x * h.loopmul;
+                            if (h.co2 >= 0) out_b[h.mom_off + h.co2] = A.y * h.loopmul;
+                            continue;
+                        }
+                        const cd Bm = buf[chf_swz(rb[u], h.swm)];
+                        const double sc = lm * chf_rcp((double)k);
+                        // Y_0 = (A + conj(Bm)) / 2, Y_1 = (A - conj(Bm)) / (2i); the adjoint carries a factor 2 for k > 0
+                        double *o = out_b + off + 4LL * k;
+                        o[0] = (A.x + Bm.x) * sc + kn[u][0];
+                        o[1] = (A.y - Bm.y) * sc + kn[u][1];
+                        o[2] = (A.y + Bm.y) * sc + kn[u][2];
+                        o[3] = (Bm.x - A.x) * sc + kn[u][3];
                     }
-                    double *o = out_b + off + 4LL * k;
-                    o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
                 }
             } else {
-                for (int kp = tid; kp < M; kp += T) {
-                    const int k = R * kp + rho;  // never 0 or N / 2
-                    const cd A = buf[chf_swz(h.rev[kp], h.swm)];
-                    const int row = k < N / 2 ? k : N - k;           // Y_d[N - k] = conj(Y_d[k]) for the real sequence of coordinate d
-                    const double im = k < N / 2 ? A.y : -A.y;
-                    const double sc = 2.0 * lm * chf_rcp((double)row);
-                    double v0 = A.x * sc, v1 = im * sc;
-                    const long long at = off + 4LL * row + 2 * dim;
-                    if (kin_b) {
-                        v0 += kin_b[at];
-                        v1 += kin_b[at + 1];
+                for (int kp0 = tid; kp0 < M; kp0 += UO * T) {
+                    int ra[UO];
+                    double kn[UO][2];
+#pragma unroll
+                    for (int u = 0; u < UO; ++u) {  // loads of the batch
+                        const int kp = kp0 + u * T;
+                        const bool on = kp < M;
+                        const int k = R * (on ? kp : 0) + rho;  // never 0 or N / 2
+                        const int row = k < N / 2 ? k : N - k;
+                        ra[u] = h.rev[on ? kp : 0];
+                        const long long at = off + 4LL * row + 2 * dim;
+                        kn[u][0] = (kin_b && on) ? kin_b[at] : 0.0;
+                        kn[u][1] = (kin_b && on) ? kin_b[at + 1] : 0.0;
                     }
-                    out_b[at] = v0;
-                    out_b[at + 1] = v1;
+#pragma unroll
+                    for (int u = 0; u < UO; ++u) {
+                        const int kp = kp0 + u * T;
+                        if (kp >= M) continue;
+                        const int k = R * kp + rho;
+                        const cd A = buf[chf_swz(ra[u], h.swm)];
+                        const int row = k < N / 2 ? k : N - k;           // Y_d[N - k] = conj(Y_d[k]) for the real sequence of coordinate d
+                        const double im = k < N / 2 ? A.y : -A.y;
+                        const double sc = 2.0 * lm * chf_rcp((double)row);
+                        const long long at = off + 4LL * row + 2 * dim;
+                        out_b[at] = A.x * sc + kn[u][0];
+                        out_b[at + 1] = im * sc + kn[u][1];
+                    }
                 }
             }
         });
     });
 }
 
+// stage tables of the FFT and the slot table of the loop's slice -> shared memory
 template <class Ctx>
-CHB_D void cta_big_prologue(Ctx &ctx, const ChfLoop &h, cd *twsm_dst) {
+CHB_D void cta_big_prologue(Ctx &ctx, const ChbBigSys &F, const ChbSys &S, const ChbBigLoop &L, cd *twsm_dst, ChbBigSlot *slots) {
+    const ChfLoop &h = L.h;
     ctx.par([&](int tid, int nthr) {
         for (int s = 0; s < h.nfac; ++s) {
             if (h.tw_soff[s] < 0) continue;
             cd *dst = twsm_dst + h.tw_soff[s];
             for (int i = tid; i < h.tw_len[s]; i += nthr) dst[i] = h.tw[s][i];
+        }
+        const int nslot = (F.R * h.N) / F.segm_size;
+        for (int j = tid; j < nslot; j += nthr) {
+            const int s = L.slot_seg[j];
+            const ChbSeg &sg = S.segs[s];
+            ChbBigSlot sl;
+            sl.s = s;
+            sl.timerev = sg.timerev;
+            sl.isid = sg.isid;
+            sl.pad = 0;
+            for (int c = 0; c < 4; ++c) sl.rot[c] = sg.rot[c];
+            slots[j] = sl;
         }
     });
 }

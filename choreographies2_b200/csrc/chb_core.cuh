@@ -769,7 +769,10 @@ CHB_HD double chb_rsqrt_fast(double d) {
 
 // UNI: every interacting pair has the same weight S.pair_wu (equal masses and charges -- every nC / nB test system): no weight
 // matrix in shared memory (more resident CTAs), no weight loads or multiplies inside the loop
-template <int MODE, bool UNI, class Ctx>
+// LAW0: the plan's law is the fast power law (law_kind 0, V = -1/r): a compile-time fact inside the kernel, so the unrolled pair
+// evaluations are straight-line code the compiler can interleave (with the run-time branch every evaluation was a basic block of
+// its own, and the generic branch's pow() made the tiled kernel 15 k instructions long)
+template <int MODE, bool UNI, bool LAW0, class Ctx>
 CHB_D void cta_pair_dense(Ctx &ctx, const ChbSys &S, const double *seg_b, const double *dseg_b, double *out_b,
                            double *pot_out, int tile, double globalmul, int nthreads, cd *spos, cd *sdpos, cd *sout,
                            double *sw, double *red) {
@@ -810,7 +813,7 @@ CHB_D void cta_pair_dense(Ctx &ctx, const ChbSys &S, const double *seg_b, const 
                 const double dx = xs.x - xt.x, dy = xs.y - xt.y;
                 double xsq = fma(dx, dx, dy * dy);
                 xsq = (s == t) ? 1.0 : xsq;  // W[t][t] = 0: the term vanishes, keep it finite
-                if (S.law_kind == 0) {
+                if (LAW0 || S.law_kind == 0) {
                     const double r = chb_rsqrt_fast(xsq);
                     const double r2 = r * r;
                     const double c = w * (r2 * r);    // 2 V' w
@@ -843,7 +846,7 @@ CHB_D void cta_pair_dense(Ctx &ctx, const ChbSys &S, const double *seg_b, const 
                 }
             }
             if (UNI && MODE <= 1) {  // take the self term out of the energy sum
-                if (S.law_kind == 0) {
+                if (LAW0 || S.law_kind == 0) {
                     e -= chb_rsqrt_fast(1.0);
                 } else {
                     double V, V1, V2;
@@ -888,12 +891,12 @@ CHB_D void cta_pair_dense(Ctx &ctx, const ChbSys &S, const double *seg_b, const 
 // Layout: xs / dxs / accA / accB [SP][TS] cd (SP = nsegm padded to a multiple of 8, TS = samples per CTA = 32 * groups).
 // ------------------------------------------------------------------------------------------------
 #define CHB_TILE_SB 8
-template <int MODE>
+template <int MODE, bool LAW0>
 CHB_HD void chb_tile_eval(int law_kind, const double *law, double w, const cd &xa, const cd &xb, const cd &dxa, const cd &dxb, cd &ga,
                           cd &gb, double &e) {
     const double dx = xa.x - xb.x, dy = xa.y - xb.y;
     const double xsq = fma(dx, dx, dy * dy);
-    if (law_kind == 0) {
+    if (LAW0 || law_kind == 0) {
         const double r = chb_rsqrt_fast(xsq);
         const double r2 = r * r;
         const double c = w * (r2 * r);  // 2 V' w
@@ -927,7 +930,7 @@ CHB_HD void chb_tile_eval(int law_kind, const double *law, double w, const cd &x
     }
 }
 
-template <int MODE, bool UNI, class Ctx>
+template <int MODE, bool UNI, bool LAW0, class Ctx>
 CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const double *dseg_b, double *out_b, double *pot_out,
                           int tile, double globalmul, int nblk, int ngrp, cd *xs, cd *dxs, cd *accA, cd *accB, double *red) {
     constexpr int SB = CHB_TILE_SB, SBB = (MODE == 2) ? 2 : 4;
@@ -977,7 +980,7 @@ CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const d
                     for (int b = a + 1; b < SB; ++b) {
                         const int sa = A * SB + a, sb = A * SB + b;
                         const double w = UNI ? 1.0 : ((sa < nS && sb < nS) ? S.pair_w[sa * WSP + sb] : 0.0);
-                        chb_tile_eval<MODE>(S.law_kind, S.law, w, xa[a], xa[b], dxa[a], dxa[b], ga[a], ga[b], e);
+                        chb_tile_eval<MODE, LAW0>(S.law_kind, S.law, w, xa[a], xa[b], dxa[a], dxa[b], ga[a], ga[b], e);
                     }
             } else {
 #pragma unroll 1
@@ -995,7 +998,7 @@ CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const d
                         for (int b = 0; b < SBB; ++b) {
                             const int sa = A * SB + a, sb = B * SB + jb * SBB + b;
                             const double w = UNI ? 1.0 : ((sa < nS && sb < nS) ? S.pair_w[sa * WSP + sb] : 0.0);
-                            chb_tile_eval<MODE>(S.law_kind, S.law, w, xa[a], xb[b], dxa[a], dxb[b], ga[a], gb[b], e);
+                            chb_tile_eval<MODE, LAW0>(S.law_kind, S.law, w, xa[a], xb[b], dxa[a], dxb[b], ga[a], gb[b], e);
                         }
                     if (MODE >= 1) {
 #pragma unroll
