@@ -1264,12 +1264,14 @@ extern "C" int chb_plan_set_nint(chb_plan *p, int64_t nint) {
             S.pair_dense = p->dense_smem[2] <= p->smem_limit ? 1 : 0;
         }
         if (getenv("CHB_PAIR_DENSE") && atoi(getenv("CHB_PAIR_DENSE")) == 0) S.pair_dense = 0;
-        // tiled one-sided kernel (cta_pair_tile) on the same conditions, up to 64 segments.  Measured on B200 (profiles/
-        // r02_configs.txt): 17 FP64 instructions per unordered pair instead of 30, but only 22 % FP64 pipe utilisation (two
-        // 8-warp CTAs per SM, weight loads and predicates per pair) against 62 % for cta_pair_dense: 0.78 ms vs 0.36 ms per 256
-        // states of 64C.  Kept as an opt-in A/B path (CHB_PAIR_TILE=1); the dense kernel is the default.
+        // tiled one-sided kernel (cta_pair_tile) on the same conditions, up to 64 segments: every unordered pair once, 17 FP64
+        // instructions per unordered pair instead of 30.  Its first version lost to the dense kernel (22 % FP64 pipe utilisation:
+        // the run-time law branch made every pair evaluation a basic block of its own and pulled pow() into the unrolled tile);
+        // with the law as a template parameter it wins (profiles/r02_pair_tile_law0_ab.txt: 64C 0.592 -> 0.493 ms per 256 states,
+        // 16C 0.465 -> 0.358 ms per 1024 states) and is the default; CHB_PAIR_TILE=0 selects the dense kernel (A/B).
         S.pair_tilek = 0;
-        if (S.pair_dense && T.nsegm <= 64 && getenv("CHB_PAIR_TILE") && atoi(getenv("CHB_PAIR_TILE")) == 1) {
+        static const int tile_on = [] { const char *e = getenv("CHB_PAIR_TILE"); return e ? atoi(e) : 1; }();
+        if (S.pair_dense && T.nsegm <= 64 && tile_on == 1) {
             const int nblk = (T.nsegm + CHB_TILE_SB - 1) / CHB_TILE_SB, ngrp = std::max(1, 8 / nblk);
             const int TS = 32 * ngrp, SP = nblk * CHB_TILE_SB;
             const size_t arrt = (size_t)SP * TS * sizeof(cd);
