@@ -954,35 +954,61 @@ CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const d
         }
         red[tid] = 0.0;
     });
-    const int nround = nblk / 2 + 1;
-    for (int r = 0; r < nround; ++r) {
+    // Rounds.  Every unordered block pair {A, B} once: warp A takes B = (A + r) mod nblk in round r.  For an even number of blocks
+    // the middle round r = nblk / 2 needs only half of the warps (each pair would come up twice); the other half does the work of
+    // the "diagonal round" there instead -- the pairs inside its own block and inside block A - nblk / 2, whose B-side accumulator
+    // nobody else writes in that round -- so there is no separate diagonal round and no idle half: nblk / 2 rounds of (almost)
+    // equal work per warp instead of nblk / 2 + 1 unequal ones (the round barrier was 19 % of the stall samples,
+    // profiles/r02_pair_tile_ncu_summary.md).  Odd nblk: a diagonal round (r = 0) and (nblk - 1) / 2 full rounds.
+    const bool even = (nblk % 2) == 0;
+    for (int r = even ? 1 : 0; r <= nblk / 2; ++r) {
         ctx.par([&](int tid, int nthr) {
             (void)nthr;
             const int warp = tid >> 5, lane = tid & 31;
             const int grp = warp / nblk, A = warp - grp * nblk;
             if (grp >= ngrp) return;
-            if (r > 0 && 2 * r == nblk && A >= nblk / 2) return;  // the middle round pairs every block once
-            const int B = (A + r) % nblk;
-            if (r > 0 && B == A) return;
             const int j = grp * 32 + lane;
-            cd xa[SB], dxa[SB], ga[SB];
-#pragma unroll
-            for (int a = 0; a < SB; ++a) {
-                xa[a] = xs[(A * SB + a) * TS + j];
-                dxa[a] = (MODE == 2) ? dxs[(A * SB + a) * TS + j] : mk(0.0, 0.0);
-                ga[a] = mk(0.0, 0.0);
-            }
             double e = 0.0;
-            if (r == 0) {
+            // the pairs inside block D, sums added to acc (accA of the block's own warp, or the free accB of the middle round)
+            auto diagonal = [&](int D, cd *acc) {
+                cd xd[SB], dxd[SB], gd[SB];
+#pragma unroll
+                for (int a = 0; a < SB; ++a) {
+                    xd[a] = xs[(D * SB + a) * TS + j];
+                    dxd[a] = (MODE == 2) ? dxs[(D * SB + a) * TS + j] : mk(0.0, 0.0);
+                    gd[a] = mk(0.0, 0.0);
+                }
 #pragma unroll
                 for (int a = 0; a < SB; ++a)
 #pragma unroll
                     for (int b = a + 1; b < SB; ++b) {
-                        const int sa = A * SB + a, sb = A * SB + b;
+                        const int sa = D * SB + a, sb = D * SB + b;
                         const double w = UNI ? 1.0 : ((sa < nS && sb < nS) ? S.pair_w[sa * WSP + sb] : 0.0);
-                        chb_tile_eval<MODE, LAW0>(S.law_kind, S.law, w, xa[a], xa[b], dxa[a], dxa[b], ga[a], ga[b], e);
+                        chb_tile_eval<MODE, LAW0>(S.law_kind, S.law, w, xd[a], xd[b], dxd[a], dxd[b], gd[a], gd[b], e);
                     }
+                if (MODE >= 1) {
+#pragma unroll
+                    for (int a = 0; a < SB; ++a) {
+                        const int o = (D * SB + a) * TS + j;
+                        acc[o] = cadd(acc[o], gd[a]);
+                    }
+                }
+            };
+            const bool middle = even && 2 * r == nblk;
+            if (r == 0) {
+                diagonal(A, accA);
+            } else if (middle && A >= nblk / 2) {
+                diagonal(A, accA);
+                diagonal(A - nblk / 2, accB);
             } else {
+                const int B = (A + r) % nblk;
+                cd xa[SB], dxa[SB], ga[SB];
+#pragma unroll
+                for (int a = 0; a < SB; ++a) {
+                    xa[a] = xs[(A * SB + a) * TS + j];
+                    dxa[a] = (MODE == 2) ? dxs[(A * SB + a) * TS + j] : mk(0.0, 0.0);
+                    ga[a] = mk(0.0, 0.0);
+                }
 #pragma unroll 1
                 for (int jb = 0; jb < SB / SBB; ++jb) {
                     cd xb[SBB], dxb[SBB], gb[SBB];
@@ -1008,12 +1034,12 @@ CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const d
                         }
                     }
                 }
-            }
-            if (MODE >= 1) {
+                if (MODE >= 1) {
 #pragma unroll
-                for (int a = 0; a < SB; ++a) {
-                    const int o = (A * SB + a) * TS + j;
-                    accA[o] = cadd(accA[o], ga[a]);
+                    for (int a = 0; a < SB; ++a) {
+                        const int o = (A * SB + a) * TS + j;
+                        accA[o] = cadd(accA[o], ga[a]);
+                    }
                 }
             }
             if (MODE <= 1) {
