@@ -125,6 +125,7 @@ struct chb_plan {
     int big_min_len[3] = {0, 0, 0};  // shortest transform length of each split
     const unsigned char *stage_skip = nullptr;  // set by the Newton driver around staged launches: byte mask of states to leave out
     int64_t stage_c0 = 0;                       // first state of the chunk being launched (offset into stage_skip)
+    int gmres_split_hint = 1;  // 0: the Newton driver has few live states -> Givens tail inside the Arnoldi launch (one launch less per inner iteration)
     int big_force_r = 0;    // CHB_BIG_R: A/B knob, use this split whenever it exists
     int fused5_active = 0;  // the level is served by the general fused kernel (chb_fused5.cuh) instead of versions 3 / 4
     Ch5Sys f5;              // passed by value (constant bank) to k_fused5
@@ -874,6 +875,9 @@ static int big_setup(chb_plan *p, const std::vector<ChbLoop> &loops, int segm_si
     int max_slots = 0;
     for (int il = 0; il < T.nloop; ++il) max_slots = std::max(max_slots, (R * F.loops[il].h.N) / segm_size);
     F.max_slots = max_slots;
+    static const int stagger_ns = [] { const char *e = getenv("CHB_BIG_STAGGER_NS"); return e ? atoi(e) : 0; }();  // A/B knob, read once
+    F.stagger_ns = stagger_ns;
+    F.first_wave = p->num_sms;
     const size_t slot_bytes = (size_t)max_slots * sizeof(ChbBigSlot);
     size_t tw_room = 0;
     {
@@ -2019,6 +2023,22 @@ CHB_KERNEL void CHF_BOUNDS k_fused5(CH5_SYS_PARAM, ChfArgs A) {
 #else
 #define CHB_BIG_BOUNDS
 #endif
+// With one CTA per SM all CTAs of a wave run their phases in lock-step: every SM reads parameter rows at the same time (an HBM
+// burst), then every SM computes.  A start offset for the first-wave CTAs on odd SMs shifts half of the chip by about one phase, so
+// that the memory phase of one half overlaps the FFT phase of the other; later CTAs inherit the shift (knob CHB_BIG_STAGGER_NS).
+CHB_D void chb_big_stagger(const ChbBigSys &F, long long blk) {
+#ifndef CHB_HOSTSIM
+    if (F.stagger_ns > 0 && blk < F.first_wave) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        if (smid & 1u) {
+            for (int left = F.stagger_ns; left > 0; left -= 4000) __nanosleep(left < 4000 ? left : 4000);
+        }
+    }
+#else
+    (void)F; (void)blk;
+#endif
+}
 template <int R>
 CHB_KERNEL void CHB_BIG_BOUNDS k_big_fwd(ChbBigSys F, ChbSys S, const double *params, double *segmpos, double *kin_part) {
     CHB_CTX_DECL;
@@ -2032,6 +2052,7 @@ CHB_KERNEL void CHB_BIG_BOUNDS k_big_fwd(ChbBigSys F, ChbSys S, const double *pa
     cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
     cd *tw = buf + L.h.N;
     ChbBigSlot *slots = (ChbBigSlot *)(tw + F.tw_smem_len);
+    chb_big_stagger(F, blk);
     cta_big_prologue(ctx, F, S, L, tw, slots);
     cta_big_fwd<R>(ctx, F, L, q, params + b * F.nparams, segmpos ? segmpos + b * F.segsz : (double *)0,
                    kin_part ? kin_part + b * F.nloop + il : (double *)0, buf, tw, slots, red);
@@ -2048,6 +2069,7 @@ CHB_KERNEL void CHB_BIG_BOUNDS k_big_adj(ChbBigSys F, ChbSys S, const double *se
     cd *buf = (cd *)(CHB_SMEM + CHF_RED_BYTES);
     cd *tw = buf + L.h.N;
     ChbBigSlot *slots = (ChbBigSlot *)(tw + F.tw_smem_len);
+    chb_big_stagger(F, blk);
     cta_big_prologue(ctx, F, S, L, tw, slots);
     cta_big_adj<R>(ctx, F, L, q, seg + b * F.segsz, out + b * F.nparams, kin_src ? kin_src + b * F.nparams : (const double *)0, buf, tw, slots);
 }
@@ -2494,7 +2516,8 @@ extern "C" int chb_gmres_step_dev(chb_plan *p, int64_t batch, int64_t n, int j, 
     CHB_REQUIRE(done && R && g && cs && target && kdone && j < m, CHB_ERR_INVALID_ARGUMENT,
                 "chb_gmres_step_dev: NULL array or j >= m");
     static const bool split_on = [] { const char *e = getenv("CHB_GMRES_TAIL_SPLIT"); return !(e && atoi(e) == 0); }();
-    ChkGivens G = {R, g, cs, target, (long long *)kdone, done, m, live_list_next, live_count_next, split_on ? 1 : 0};
+    // split tail (one thread per state in a second launch) pays at large batches; with few live states the launch itself is the cost
+    ChkGivens G = {R, g, cs, target, (long long *)kdone, done, m, live_list_next, live_count_next, (split_on && p && p->gmres_split_hint) ? 1 : 0};
     CHB_TRY(arnoldi_launch(p, "chb_gmres_step_dev", batch, n, j, 0, V, w, done, nullptr, G, stream));
 #ifndef CHB_HOSTSIM
     if (G.split && batch > 0) CHB_LAUNCH(p, k_givens_tail, (batch + 127) / 128, 128, 0, (chb_stream_t)stream, (long long)batch, j, G);
@@ -2773,9 +2796,6 @@ CHB_KERNEL void k_nk_ls_start(long long B, double *ns, NkOpts O, const double *x
     }
 }
 // mask[b] = 0 for the states that want an evaluation of this kind
-CHB_KERNEL void k_nk_mask(long long B, const double *ns, int kind, unsigned char *mask) {
-    NK_FOR_STATE(b, B) { mask[b] = ((int)ns[b * NK_STRIDE + NK_LS_TASK] == kind) ? 0 : 1; }
-}
 CHB_KERNEL void k_nk_ls_update(long long B, double *ns, NkOpts O, int kind, const double *phi_t, const double *fmax_t, int *counts, int m) {
     NK_FOR_STATE(b, B) {
         double *st = ns + b * NK_STRIDE;
@@ -2816,14 +2836,30 @@ CHB_KERNEL void k_nk_finish(long long B, const double *ns, int32_t *status, int3
 // op 1: out = a + s_eval * d   (trial point)                  rows whose mask byte is 0
 // op 2: a += s_final * d, c = e  (accept: x, F)               rows with NK_LIVE
 // op 3: out = a                (best iterate)                 rows whose mask byte is 0
-CHB_KERNEL void k_nk_rows(long long n, int op, const double *ns, const unsigned char *mask, double *out, double *a, const double *d,
-                          double *c, const double *e, int nchunk) {
+CHB_KERNEL void k_nk_rows(long long n, int op, const double *ns, unsigned char *mask, double *out, double *a, const double *d,
+                          double *c, const double *e, int nchunk, int kind, int *zero2) {
     const long long b = CHB_BLOCK_ID / nchunk;  // grid = states x nchunk: long rows are shared by several CTAs
     const long long ck = CHB_BLOCK_ID % nchunk;
     const double *st = ns + b * NK_STRIDE;
+    if (op == 4) {
+        // op 1 for the states whose pending line-search evaluation is of `kind` (what k_nk_mask + op 1 did in two launches): every
+        // CTA of the row derives the predicate from the state, the first one records it in the mask for the kernels that follow;
+        // the first CTA of the grid also clears the two "pending evaluations" counters that k_nk_ls_update will count into (the
+        // host has read them: nk_read_counts synchronises the stream before this launch)
+        const bool off = ((int)st[NK_LS_TASK] != kind);
+#ifndef CHB_HOSTSIM
+        if (threadIdx.x == 0) {
+#else
+        {
+#endif
+            if (ck == 0) mask[b] = off ? 1 : 0;
+            if (CHB_BLOCK_ID == 0 && zero2) { zero2[0] = 0; zero2[1] = 0; }
+        }
+        if (off) return;
+    }
     if ((op == 0 || op == 2) && st[NK_LIVE] == 0.0) return;
     if ((op == 1 || op == 3) && mask[b]) return;
-    const double s = op == 0 ? 1.0 / st[NK_FNORM] : (op == 1 ? st[NK_S_EVAL] : st[NK_S_FINAL]);
+    const double s = op == 0 ? 1.0 / st[NK_FNORM] : ((op == 1 || op == 4) ? st[NK_S_EVAL] : st[NK_S_FINAL]);
     const size_t o = (size_t)b * n;
     const long long per = (n + nchunk - 1) / nchunk, i0 = ck * per, i1 = i0 + per < n ? i0 + per : n;
 #ifndef CHB_HOSTSIM
@@ -2832,14 +2868,22 @@ CHB_KERNEL void k_nk_rows(long long n, int op, const double *ns, const unsigned 
     for (long long i = i0; i < i1; ++i) {
 #endif
         if (op == 0) out[o + i] = a[o + i] * s;
-        else if (op == 1) out[o + i] = fma(s, d[o + i], a[o + i]);
+        else if (op == 1 || op == 4) out[o + i] = fma(s, d[o + i], a[o + i]);
         else if (op == 2) { a[o + i] = fma(s, d[o + i], a[o + i]); c[o + i] = e[o + i]; }
         else out[o + i] = a[o + i];
     }
 }
 // per-row sum of squares (non-finite when the row has a non-finite entry) and max |.| of the rows whose mask byte is 0 (NULL: all)
-CHB_KERNEL void k_nk_row_stats(long long n, const double *a, const unsigned char *mask, double *sumsq, double *maxabs) {
-    const long long b = CHB_BLOCK_ID;
+CHB_KERNEL void k_nk_row_stats(long long n, const double *a, const unsigned char *mask, double *sumsq, double *maxabs,
+                               long long B2, const double *a2, double *sumsq2) {
+    // grid = B2 blocks for one array, 2 * B2 for two (a2 / sumsq2: the second array shares the mask; no max for it)
+    long long b = CHB_BLOCK_ID;
+    if (a2 && b >= B2) {
+        b -= B2;
+        a = a2;
+        sumsq = sumsq2;
+        maxabs = (double *)0;
+    }
     if (mask && mask[b]) return;
     const double *r = a + (size_t)b * n;
 #ifndef CHB_HOSTSIM
@@ -2962,12 +3006,16 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
     // F(x0), norms, per-state scalars
     CHB_TRY(nk_grad(p, B, x, A.F, nullptr, A, st));
     n_u1 += B;
-    CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, A.F, (const unsigned char *)nullptr, A.phi_t, A.fmax_t);
+    CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, (const double *)A.F, (const unsigned char *)nullptr, A.phi_t, A.fmax_t, (long long)B, (const double *)nullptr, (double *)nullptr);
     const int nkc = (int)std::max<int64_t>(1, std::min<int64_t>(64, n / 8192));  // CTAs per row of the element-wise row kernels
+    struct HintGuard {  // the hint is the driver's: other callers of chb_gmres_step_dev get the default back on every exit path
+        chb_plan *pl;
+        ~HintGuard() { pl->gmres_split_hint = 1; }
+    } hint_guard{p};
     CHB_LAUNCH(p, k_nk_init, gs, 128, 0, st, B, A.ns, A.phi_t, A.fmax_t);
     if (best_x) {
         CHB_TRY(nk_zero(A.mask, (size_t)B, st));
-        CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr, nkc);
+        CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr, nkc, 0, (int *)nullptr);
     }
     for (int it = 0; it < opts->maxiter; ++it) {
         CHB_TRY(nk_zero(A.counts, sizeof(int) * (size_t)(m + 8), st));
@@ -2976,9 +3024,10 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
         const int nlive = hc[0];
         if (nlive == 0) break;
         ++n_it;
+        p->gmres_split_hint = nlive >= 512 ? 1 : 0;
         // jacobian.setup / update (:2013-2019): segment positions of the current iterate; first Krylov vector F / |F|
         CHB_TRY(nk_segmpos(p, B, x, A.seg, A.mask, A, st));
-        CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 0, A.ns, A.mask, A.V, A.F, (const double *)nullptr, (double *)nullptr, (const double *)nullptr, nkc);
+        CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 0, A.ns, A.mask, A.V, A.F, (const double *)nullptr, (double *)nullptr, (const double *)nullptr, nkc, 0, (int *)nullptr);
         // GMRES(m), one cycle, zero initial guess: per inner iteration one Hessian-vector launch over the running states and one
         // step launch (Arnoldi + Givens + stopping test + the list of the next iteration)
         for (int j = 0; j < m; ++j) {
@@ -2993,8 +3042,8 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
         }
         CHB_TRY(chb_gmres_solution_dev(p, B, n, m, A.V, A.R, A.g, (const int64_t *)A.kdone, -1.0, A.dx, (void *)st));  // dx = -J^-1 F
         // line search on phi(s) = |F(x + s dx)|^2
-        CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, (const double *)x, (const unsigned char *)A.mask, A.xn2, (double *)nullptr);
-        CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, (const double *)A.dx, (const unsigned char *)A.mask, A.dxn2, (double *)nullptr);
+        CHB_LAUNCH(p, k_nk_row_stats, 2 * B, 256, 0, st, n, (const double *)x, (const unsigned char *)A.mask, A.xn2, (double *)nullptr, (long long)B,
+                   (const double *)A.dx, A.dxn2);
         CHB_TRY(nk_zero(A.counts + m + 2, 2 * sizeof(int), st));
         CHB_LAUNCH(p, k_nk_ls_start, gs, 128, 0, st, B, A.ns, O, A.xn2, A.dxn2, A.counts, m);
         {   // one read: the live counts of the GMRES iterations (Hessian-vector evaluations) and the pending evaluations
@@ -3008,20 +3057,19 @@ extern "C" int chb_newton_krylov_dev(chb_plan *p, int64_t batch, double *x, cons
         while ((hc[0] > 0 || hc[1] > 0) && guard++ < 400) {
             const int use_kind = hc[1] > 0 ? 2 : 1;  // probes first: a state alternates probe / stored evaluations
             double *Fout = use_kind == 1 ? A.Ft : A.Fd;
-            CHB_LAUNCH(p, k_nk_mask, gs, 128, 0, st, B, A.ns, use_kind, A.mask);
-            CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 1, A.ns, A.mask, A.xt, x, (const double *)A.dx, (double *)nullptr, (const double *)nullptr, nkc);
+            CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 4, A.ns, A.mask, A.xt, x, (const double *)A.dx, (double *)nullptr, (const double *)nullptr, nkc, use_kind,
+                       A.counts + m + 2);
             CHB_TRY(nk_grad(p, B, A.xt, Fout, A.mask, A, st));
             n_u1 += use_kind == 1 ? hc[0] : hc[1];
-            CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, (const double *)Fout, (const unsigned char *)A.mask, A.phi_t, A.fmax_t);
-            CHB_TRY(nk_zero(A.counts + m + 2, 2 * sizeof(int), st));
+            CHB_LAUNCH(p, k_nk_row_stats, B, 256, 0, st, n, (const double *)Fout, (const unsigned char *)A.mask, A.phi_t, A.fmax_t, (long long)B, (const double *)nullptr, (double *)nullptr);
             CHB_LAUNCH(p, k_nk_ls_update, gs, 128, 0, st, B, A.ns, O, use_kind, A.phi_t, A.fmax_t, A.counts, m);
             CHB_TRY(nk_read_counts(p, A.counts + m + 2, 2, hc, st));
         }
         // accept: x += s dx, F = F(x + s dx) (the stored evaluation), forcing terms, best iterate
-        CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 2, A.ns, A.mask, (double *)nullptr, x, (const double *)A.dx, A.F, (const double *)A.Ft, nkc);
+        CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 2, A.ns, A.mask, (double *)nullptr, x, (const double *)A.dx, A.F, (const double *)A.Ft, nkc, 0, (int *)nullptr);
         CHB_LAUNCH(p, k_nk_end, gs, 128, 0, st, B, A.ns, O, A.mask);
         if (best_x)
-            CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr, nkc);
+            CHB_LAUNCH(p, k_nk_rows, B * nkc, 256, 0, st, n, 3, A.ns, A.mask, best_x, x, (const double *)nullptr, (double *)nullptr, (const double *)nullptr, nkc, 0, (int *)nullptr);
     }
     CHB_LAUNCH(p, k_nk_finish, gs, 128, 0, st, B, A.ns, status, nit, fnorm_max, fnorm_2, best_fnorm);
     {

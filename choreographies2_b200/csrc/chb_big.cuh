@@ -40,6 +40,7 @@ struct ChbBigSys {
     int nloop, T, segm_size, R;
     int tw_smem_len;        // cd slots of stage tables copied to shared memory (behind the buffer)
     int max_slots;          // ChbBigSlot entries behind the stage tables
+    int stagger_ns, first_wave;  // > 0: CTAs of the first wave on odd SMs start this much later (see k_big_fwd)
     long long nparams, segsz;
     ChbBigLoop loops[CHB_BIG_MAX_LOOPS];
 };
