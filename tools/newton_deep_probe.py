@@ -16,9 +16,14 @@ ap.add_argument("--nint", type=int, default=49152)
 ap.add_argument("--states", type=int, default=32)
 ap.add_argument("--maxiter", type=int, default=3)
 ap.add_argument("--reps", type=int, default=1)
+ap.add_argument("--no-fused", action="store_true", help="staged kernels (residue-split transforms) instead of the fused kernel")
+ap.add_argument("--split", type=int, default=0)
 a = ap.parse_args()
 T = PlanTables.load("choreographies2_b200/systems/3C.npz")
 nbs = NBodySystB200(T, a.nint)
+if a.no_fused:
+    nbs.set_fused(False)
+    nbs.set_transform_split(a.split)
 x0 = torch.from_numpy(refine.find_starts(T, a.nint, range(a.states), **refine.RANDOM_CONFIG_3C)).cuda()
 for rep in range(a.reps + 1):
     torch.cuda.synchronize()
