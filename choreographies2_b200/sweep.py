@@ -42,7 +42,8 @@ class ChunkQueue:
     """Dynamic work queue of seed chunks shared by the ranks (solves have variable iteration counts, so a rank
     that finishes early takes the next chunk instead of idling behind a static split).  The queue is ONE atomic counter in a
     ``torch.distributed.TCPStore`` on the host network (``add`` is atomic): no device collective, nothing on the data path.
-    With ``world == 1`` (or no store) it degenerates to a local counter."""
+    With ``world == 1`` (or no store) it degenerates to a local counter.  Rank 0 hosts the store: keep its ``ChunkQueue`` alive
+    until every rank has finished claiming (e.g. until after the end-of-sweep gather), or the others lose the counter."""
 
     def __init__(self, n: int, chunk: int, rank: int = 0, world: int = 1, host: str = "127.0.0.1", port: Optional[int] = None,
                  key: str = "chb_next_chunk"):

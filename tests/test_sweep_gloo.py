@@ -169,3 +169,59 @@ def test_dynamic_chunk_queue_gloo():
     from choreographies2_b200 import sweep as sw
     q1 = sw.ChunkQueue(5, 2)
     assert [q1.next(), q1.next(), q1.next(), q1.next()] == [(0, 2), (2, 4), (4, 5), None]
+
+
+def _search_worker(rank, world, port, n, chunk, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch.distributed as dist
+    from choreographies2_b200 import NBodySystB200, PlanTables, sweep as sw, refine
+    from hostsim import build_hostsim
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+        lib = build_hostsim.load()
+        cfg = dict(refine.SEARCH_CONFIG_3C)
+        cfg["n_reconverge_it_max"] = 1
+        queue = sw.ChunkQueue(n, chunk, rank, world)  # rank 0 hosts the counter: the object must outlive the other ranks' claims
+        out = sw.run_search(T, 96, n, device=None, chunk=chunk, workers=2, config=cfg, queue=queue,
+                            make_plan=lambda ni: NBodySystB200(T, ni, _lib_handle=lib))
+        rec = out["records"]
+        merged = sw.gather_records({k: rec[k] for k in ("outcome", "level", "action", "dup_of_seed")}, rec["seed"])
+        q.put((rank, int(out["chunks"]), rec["seed"].tolist(), merged))
+        del queue  # after the gather (a collective): every rank has finished claiming
+    finally:
+        dist.destroy_process_group()
+
+
+def test_run_search_two_ranks_gloo():
+    """sweep.run_search on two gloo ranks sharing the TCPStore chunk queue, two worker threads per rank: every seed is solved
+    exactly once, and the merged records equal a single-process run (no collective on the data path, gather at the end)."""
+    import multiprocessing as mp
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from choreographies2_b200 import NBodySystB200, PlanTables, refine, sweep as sw
+    from hostsim import build_hostsim
+    n, chunk, world = 12, 2, 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_search_worker, args=(r, world, port, n, chunk, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = {r: (nch, seeds, merged) for r, nch, seeds, merged in (q.get(timeout=300) for _ in range(world))}
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got[0][0] + got[1][0] == n // chunk
+    assert sorted(got[0][1] + got[1][1]) == list(range(n))
+    merged = got[0][2]
+    assert got[1][2] is None and merged["index"].tolist() == list(range(n))
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    lib = build_hostsim.load()
+    cfg = dict(refine.SEARCH_CONFIG_3C)
+    cfg["n_reconverge_it_max"] = 1
+    one = sw.run_search(T, 96, n, device=None, chunk=n, workers=1, config=cfg, make_plan=lambda ni: NBodySystB200(T, ni, _lib_handle=lib))["records"]
+    assert np.array_equal(merged["outcome"], one["outcome"]) and np.array_equal(merged["level"], one["level"])
+    saved = (one["outcome"] == refine.FOUND) | (one["outcome"] == refine.APPROX)
+    assert np.allclose(merged["action"][saved], one["action"][saved], rtol=1e-12, atol=0)
