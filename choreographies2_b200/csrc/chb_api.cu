@@ -1834,6 +1834,28 @@ k_pair_tile(ChbSys S, const double *seg, const double *dseg, double *out, double
                         globalmul, S.tile_nblk, S.tile_ngrp, xs, dxs, accA, accB, red);
 }
 
+// A/B variants of the tiled kernel for energy + gradient, uniform weights, closed-form law (knob CHB_TILE_VAR, read once):
+// 1: partner sub-blocks of 2 segments (the default since the A/B), 2: sub-blocks of 8, 3: sub-blocks of 4 -- 2 and 3 with one CTA per SM
+// and up to 255 registers
+#ifndef CHB_HOSTSIM
+template <int SBBV, int MINB>
+__global__ void __launch_bounds__(256, MINB)
+k_pair_tile_var(ChbSys S, const double *seg, const double *dseg, double *out, double *pot_part, double globalmul) {
+    CHB_CTX_DECL;
+    const long long blk = CHB_BLOCK_ID;
+    const int tile = (int)(blk % S.pair_ntiles);
+    const long long b = blk / S.pair_ntiles;
+    if (S.skip && S.skip[b]) return;
+    double *red = (double *)CHB_SMEM;
+    const size_t arr = (size_t)S.tile_nblk * CHB_TILE_SB * 32 * S.tile_ngrp;
+    cd *xs = (cd *)(red + 1024);
+    cd *accA = xs + arr, *accB = accA + arr, *dxs = accB + arr;
+    cta_pair_tile<1, true, true, SBBV>(ctx, S, seg + b * S.segsz, dseg ? dseg + b * S.segsz : (const double *)0,
+                                       out ? out + b * S.segsz : (double *)0, pot_part ? pot_part + b * S.pair_ntiles + tile : (double *)0,
+                                       tile, globalmul, S.tile_nblk, S.tile_ngrp, xs, dxs, accA, accB, red);
+}
+#endif
+
 CHB_KERNEL void k_kin(ChbSys S, const double *params, double *kin_out, int kin_stride) {
     CHB_CTX_DECL;
     const long long b = CHB_BLOCK_ID;
@@ -2219,6 +2241,16 @@ static int launch_pair_sys(chb_plan *p, const ChbSys &Sy_in, int mode, int64_t n
         const bool tu = uni && (p->sys.nsegm % CHB_TILE_SB == 0);
 #define CHB_TILE_LAUNCH2(M, U, W) CHB_LAUNCH(p, (k_pair_tile<M, U, W>), grid, p->tile_threads, p->tile_smem[M == 0 ? 0 : M], st, Sy, seg, dseg, out, pot_part, globalmul)
 #define CHB_TILE_LAUNCH(M, U) do { if (law0) CHB_TILE_LAUNCH2(M, U, true); else CHB_TILE_LAUNCH2(M, U, false); } while (0)
+#ifndef CHB_HOSTSIM
+        static const int tile_var = [] { const char *e = getenv("CHB_TILE_VAR"); return e ? atoi(e) : 0; }();
+        if (mode == 1 && tu && law0 && tile_var > 0) {
+            const size_t sm1 = p->tile_smem[1];
+            if (tile_var == 1) CHB_LAUNCH(p, (k_pair_tile_var<2, 2>), grid, p->tile_threads, sm1, st, Sy, seg, dseg, out, pot_part, globalmul);
+            else if (tile_var == 2) CHB_LAUNCH(p, (k_pair_tile_var<8, 1>), grid, p->tile_threads, sm1, st, Sy, seg, dseg, out, pot_part, globalmul);
+            else CHB_LAUNCH(p, (k_pair_tile_var<4, 1>), grid, p->tile_threads, sm1, st, Sy, seg, dseg, out, pot_part, globalmul);
+            return CHB_OK;
+        }
+#endif
         if (mode == 0) { if (tu) CHB_TILE_LAUNCH(0, true); else CHB_TILE_LAUNCH(0, false); }
         else if (mode == 1) { if (tu) CHB_TILE_LAUNCH(1, true); else CHB_TILE_LAUNCH(1, false); }
         else { if (tu) CHB_TILE_LAUNCH(2, true); else CHB_TILE_LAUNCH(2, false); }

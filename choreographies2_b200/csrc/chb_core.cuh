@@ -930,10 +930,12 @@ CHB_HD void chb_tile_eval(int law_kind, const double *law, double w, const cd &x
     }
 }
 
-template <int MODE, bool UNI, bool LAW0, class Ctx>
+template <int MODE, bool UNI, bool LAW0, int SBBV = 0, class Ctx>
 CHB_D void cta_pair_tile(Ctx &ctx, const ChbSys &S, const double *seg_b, const double *dseg_b, double *out_b, double *pot_out,
                           int tile, double globalmul, int nblk, int ngrp, cd *xs, cd *dxs, cd *accA, cd *accB, double *red) {
-    constexpr int SB = CHB_TILE_SB, SBB = (MODE == 2) ? 2 : 4;
+    // partner sub-blocks of 2 segments: fewest live registers, which is what the two resident CTAs per SM need (A/B of sub-blocks of
+    // 2 / 4 / 8 and of one CTA per SM with up to 255 registers: profiles/r02_pair_tile_variants_ab.txt); SBBV: the A/B variants
+    constexpr int SB = CHB_TILE_SB, SBB = SBBV ? SBBV : 2;
     const int store = S.segm_store, nS = S.nsegm, SP = nblk * SB, TS = 32 * ngrp, WSP = S.pair_spad;
     const int i0 = tile * TS;
     const int n = (store - i0) < TS ? (store - i0) : TS;
