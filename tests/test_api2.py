@@ -153,3 +153,32 @@ def test_api2_on_device_tensors():
     ll_h, dm_h = nbs.segm_to_path_stats(seg_h, vel_h)
     assert relerr(ll_d.cpu().numpy(), ll_h) < 1e-13 and relerr(dm_d.cpu().numpy(), dm_h) < 1e-13
     assert relerr(nbs.params_changevar(xd).cpu().numpy(), nbs.params_changevar(x)) == 0.0
+
+
+def test_noalloc_hessian_vector_host_emulation():
+    """The entry point without a workspace argument (scratch built into the library; tests/test_zz_no_alloc.py is the GPU test): same
+    numbers as the workspace variant on two calls in a row, oversize batches rejected with CHB_ERR_WORKSPACE before any work."""
+    import ctypes as C
+    from choreographies2_b200 import NBodySystB200, PlanTables
+    from hostsim import build_hostsim
+    sim = build_hostsim.load()
+    T = PlanTables.load(os.path.join(ROOT, "choreographies2_b200", "systems", "3C.npz"))
+    for fused in (True, False):
+        nbs = NBodySystB200(T, 768, _lib_handle=sim)
+        nbs.set_fused(fused)
+        rng = np.random.default_rng(2)
+        for _ in range(2):
+            x, dx = rng.random((4, nbs.nparams)), rng.random((4, nbs.nparams))
+            out = np.full_like(x, np.nan)
+            rc = sim.chb_params_to_action_hess_noalloc_dev(nbs._plan, 4, C.c_void_p(x.ctypes.data), C.c_void_p(dx.ctypes.data),
+                                                           C.c_void_p(out.ctypes.data), None)
+            assert rc == 0
+            assert np.array_equal(out, nbs.params_to_action_hess(x, dx))
+    nbs = NBodySystB200(T, 3072, _lib_handle=sim)
+    nbs.set_fused(False)
+    nbs.set_chunk(2048)
+    x = np.random.default_rng(3).random((2048, nbs.nparams))
+    out = np.full_like(x, 7.0)
+    rc = sim.chb_params_to_action_hess_noalloc_dev(nbs._plan, 2048, C.c_void_p(x.ctypes.data), C.c_void_p(x.ctypes.data), C.c_void_p(out.ctypes.data), None)
+    assert rc == 6 and b"CHB_NOALLOC_SCRATCH_BYTES" in sim.chb_last_error_string()
+    assert np.all(out == 7.0)
